@@ -1,0 +1,13 @@
+"""marginalign-trna_b200: B200-native anchor-banded pair-HMM forward-backward (posterior match probabilities and
+EM expectations) behind the cPecanRealign call sites of marginAlign / marginCaller / cPecanEm.
+
+The directory name is the project name and is not a valid Python identifier; import it as
+``marginalign_trna_b200`` (a one-file alias package at the repo root) or via __graft_entry__.load_package().
+"""
+from . import build, capi, hmm, seqio, synth  # noqa: F401
+from .hmm import Hmm  # noqa: F401
+from .pairhmm import (AlignmentParameters, DevicePlan, PairHmmEngine, PairHmmModel, Plan,  # noqa: F401
+                      PosteriorPairs)
+from .synth import AlignmentBatch  # noqa: F401
+
+__version__ = "0.1.0"

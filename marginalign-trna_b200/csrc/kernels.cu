@@ -1,0 +1,873 @@
+// kernels.cu -- sm_100a kernels of the anchor-banded pair-HMM forward-backward and
+// their launchers (the device half of include/margin_b200.h).
+//
+// Arithmetic contract (DESIGN.md "numerics"): everything the reference computes in double with its approximate
+// logAdd is reproduced in FP64 with the same polynomial, the same branch thresholds and the same accumulation
+// order, using explicit round-to-nearest intrinsics (__dadd_rn/__dmul_rn, never contracted into FMA), so forward,
+// backward and total-probability values are bit-identical to the reference's; only exp() (CUDA libm, <= 1 ulp)
+// can differ from glibc's in the last place.
+//
+// Decomposition (not the reference's interleaved loop):
+//   k_forward    one warp per split region, anti-diagonal wavefront, lanes = cells of the diagonal; the two previous
+//                diagonals live in a shared-memory ring; every diagonal is also written to HBM ([cell][S]).
+//   k_backward   one warp per *traceback* (checkpoint segment).  The backward pass of a segment does not depend on
+//                forward values, so all segments of all reads run concurrently.  The reference's scatter
+//                (doTransitionBackward) is turned into a gather that adds the terms in the scatter's order.
+//   k_totals     one thread per total-probability evaluation (every 10th diagonal of a traceback): the serial
+//                logAdd chain over the cells of a diagonal, in cell order.
+//   k_posterior_count / k_scan / k_emit   per-cell posterior, per-region counts, exclusive scan, ordered compaction.
+//   k_expect     per-cell transition/emission expectations with in-block reduction.
+#include <cuda_runtime.h>
+
+#include <algorithm>
+#include <cstdio>
+
+#include "mab_internal.h"
+
+#define WARPS_PER_BLOCK 4
+#define THREADS_PER_BLOCK (WARPS_PER_BLOCK * 32)
+#define FULL_MASK 0xffffffffu
+
+namespace {
+
+thread_local int64_t g_launches = 0;
+
+// ------------------------------------------------------------------------------------------------ logAdd
+
+// lookup() of pairwiseAligner.c:235-246.  The literals carry an `f` suffix in the reference: each coefficient is
+// the float nearest to the decimal, promoted to double.  Horner steps are separate multiply and add (no FMA).
+__device__ __forceinline__ double la_lookup(double x) {
+    double c3, c2, c1, c0;
+    if (x <= 1.00) {
+        c3 = (double) -0.009350833524763f; c2 = (double) 0.130659527668286f;
+        c1 = (double) 0.498799810682272f;  c0 = (double) 0.693203116424741f;
+    } else if (x <= 2.50) {
+        c3 = (double) -0.014532321752540f; c2 = (double) 0.139942324101744f;
+        c1 = (double) 0.495635523139337f;  c0 = (double) 0.692140569840976f;
+    } else if (x <= 4.50) {
+        c3 = (double) -0.004605031767994f; c2 = (double) 0.063427417320019f;
+        c1 = (double) 0.695956496475118f;  c0 = (double) 0.514272634594009f;
+    } else {
+        c3 = (double) -0.000458661602210f; c2 = (double) 0.009695946122598f;
+        c1 = (double) 0.930734667215156f;  c0 = (double) 0.168037164329057f;
+    }
+    double r = __dadd_rn(__dmul_rn(c3, x), c2);
+    r = __dadd_rn(__dmul_rn(r, x), c1);
+    r = __dadd_rn(__dmul_rn(r, x), c0);
+    return r;
+}
+
+// logAdd of pairwiseAligner.c:248-252.  With hi = max, lo = min: d = hi - lo is +inf when lo is -inf and NaN when
+// both are -inf; in both cases !(d < 7.5) selects hi, which is what the reference's LOG_ZERO tests return.
+__device__ __forceinline__ double la(double x, double y) {
+    const bool lt = x < y;
+    const double hi = lt ? y : x;
+    const double lo = lt ? x : y;
+    const double d = __dsub_rn(hi, lo);
+    if (!(d < 7.5)) return hi;
+    return __dadd_rn(la_lookup(d), lo);
+}
+
+__device__ __forceinline__ double neg_inf() { return __longlong_as_double(0xfff0000000000000LL); }
+
+template <int S>
+struct Cell {
+    double v[S];
+};
+
+template <int S>
+__device__ __forceinline__ Cell<S> cell_fill(double x) {
+    Cell<S> c;
+#pragma unroll
+    for (int s = 0; s < S; s++) c.v[s] = x;
+    return c;
+}
+
+template <int S>
+__device__ __forceinline__ Cell<S> cell_load(const double *p) {
+    Cell<S> c;
+#pragma unroll
+    for (int s = 0; s < S; s++) c.v[s] = p[s];
+    return c;
+}
+
+template <int S>
+__device__ __forceinline__ Cell<S> cell_load_cg(const double *p) {
+    Cell<S> c;
+#pragma unroll
+    for (int s = 0; s < S; s++) c.v[s] = __ldcg(p + s);
+    return c;
+}
+
+template <int S>
+__device__ __forceinline__ void cell_store(double *p, const Cell<S> &c) {
+#pragma unroll
+    for (int s = 0; s < S; s++) p[s] = c.v[s];
+}
+
+enum { M = 0, SX = 1, SY = 2, LX = 3, LY = 4 };
+
+// Forward cell update: cell_calculateForward over stateMachine{5,3}_cellCalculate (stateMachine.c:399-429, 636-661).
+// A missing neighbour is passed as all -inf, which leaves the affected states at -inf exactly as skipping the group
+// does.  The first term of each chain replaces logAdd(-inf, t) == t.
+template <int S>
+__device__ __forceinline__ Cell<S> forward_cell(const Cell<S> &lo, const Cell<S> &mi, const Cell<S> &up,
+                                                const double *eL, const double *eM, const double *eU);
+
+template <>
+__device__ __forceinline__ Cell<5> forward_cell<5>(const Cell<5> &lo, const Cell<5> &mi, const Cell<5> &up,
+                                                   const double *eL, const double *eM, const double *eU) {
+    Cell<5> c;
+    c.v[SX] = la(__dadd_rn(lo.v[M], eL[0]), __dadd_rn(lo.v[SX], eL[1]));
+    c.v[LX] = la(__dadd_rn(lo.v[M], eL[2]), __dadd_rn(lo.v[LX], eL[3]));
+    double m = la(__dadd_rn(mi.v[M], eM[0]), __dadd_rn(mi.v[SX], eM[1]));
+    m = la(m, __dadd_rn(mi.v[SY], eM[2]));
+    m = la(m, __dadd_rn(mi.v[LX], eM[3]));
+    c.v[M] = la(m, __dadd_rn(mi.v[LY], eM[4]));
+    c.v[SY] = la(__dadd_rn(up.v[M], eU[0]), __dadd_rn(up.v[SY], eU[1]));
+    c.v[LY] = la(__dadd_rn(up.v[M], eU[2]), __dadd_rn(up.v[LY], eU[3]));
+    return c;
+}
+
+template <>
+__device__ __forceinline__ Cell<3> forward_cell<3>(const Cell<3> &lo, const Cell<3> &mi, const Cell<3> &up,
+                                                   const double *eL, const double *eM, const double *eU) {
+    Cell<3> c;
+    c.v[SX] = la(la(__dadd_rn(lo.v[M], eL[0]), __dadd_rn(lo.v[SX], eL[1])), __dadd_rn(lo.v[SY], eL[2]));
+    c.v[M] = la(la(__dadd_rn(mi.v[M], eM[0]), __dadd_rn(mi.v[SX], eM[1])), __dadd_rn(mi.v[SY], eM[2]));
+    c.v[SY] = la(la(__dadd_rn(up.v[M], eU[0]), __dadd_rn(up.v[SY], eU[1])), __dadd_rn(up.v[SX], eU[2]));
+    return c;
+}
+
+// Backward cell as a gather.  The reference scatters (doTransitionBackward, pairwiseAligner.c:322-325): while it
+// processes diagonal d+2 the target cell T=(d,xmy) receives the match group of (d+2,xmy); while it processes d+1 in
+// ascending xmy, T receives the upper group of (d+1,xmy-1) [T is that cell's "upper"] and then the lower group of
+// (d+1,xmy+1) [T is its "lower"].  nMi/nUp/nLo are those three cells; eM/eU/eL their (eP+tP) rows.
+template <int S>
+__device__ __forceinline__ Cell<S> backward_cell(const Cell<S> &nMi, const Cell<S> &nUp, const Cell<S> &nLo,
+                                                 const double *eM, const double *eU, const double *eL);
+
+template <>
+__device__ __forceinline__ Cell<5> backward_cell<5>(const Cell<5> &nMi, const Cell<5> &nUp, const Cell<5> &nLo,
+                                                    const double *eM, const double *eU, const double *eL) {
+    Cell<5> c;
+    double m = la(__dadd_rn(nMi.v[M], eM[0]), __dadd_rn(nUp.v[SY], eU[0]));
+    m = la(m, __dadd_rn(nUp.v[LY], eU[2]));
+    m = la(m, __dadd_rn(nLo.v[SX], eL[0]));
+    c.v[M] = la(m, __dadd_rn(nLo.v[LX], eL[2]));
+    c.v[SX] = la(__dadd_rn(nMi.v[M], eM[1]), __dadd_rn(nLo.v[SX], eL[1]));
+    c.v[SY] = la(__dadd_rn(nMi.v[M], eM[2]), __dadd_rn(nUp.v[SY], eU[1]));
+    c.v[LX] = la(__dadd_rn(nMi.v[M], eM[3]), __dadd_rn(nLo.v[LX], eL[3]));
+    c.v[LY] = la(__dadd_rn(nMi.v[M], eM[4]), __dadd_rn(nUp.v[LY], eU[3]));
+    return c;
+}
+
+template <>
+__device__ __forceinline__ Cell<3> backward_cell<3>(const Cell<3> &nMi, const Cell<3> &nUp, const Cell<3> &nLo,
+                                                    const double *eM, const double *eU, const double *eL) {
+    Cell<3> c;
+    // lower: M->X(0) X->X(1) Y->X(2); middle: M->M(0) X->M(1) Y->M(2); upper: M->Y(0) Y->Y(1) X->Y(2)
+    c.v[M] = la(la(__dadd_rn(nMi.v[M], eM[0]), __dadd_rn(nUp.v[SY], eU[0])), __dadd_rn(nLo.v[SX], eL[0]));
+    c.v[SX] = la(la(__dadd_rn(nMi.v[M], eM[1]), __dadd_rn(nUp.v[SY], eU[2])), __dadd_rn(nLo.v[SX], eL[1]));
+    c.v[SY] = la(la(__dadd_rn(nMi.v[M], eM[2]), __dadd_rn(nUp.v[SY], eU[1])), __dadd_rn(nLo.v[SX], eL[2]));
+    return c;
+}
+
+// ------------------------------------------------------------------------------------------------ blob access
+
+struct Blob {
+    const BlobHeader *h;
+    const RegionDesc *regions;
+    const DiagDesc *diags;
+    const TracebackDesc *tbs;
+    const TotalDesc *totals;
+    const uint8_t *sym_x, *sym_y;
+    const int32_t *order_fwd, *order_bwd;
+    const int64_t *aln_region;
+};
+
+__host__ __device__ inline Blob blob_view(const void *base, const BlobHeader &h) {
+    const uint8_t *b = (const uint8_t *) base;
+    Blob v;
+    v.h = (const BlobHeader *) b;
+    v.regions = (const RegionDesc *) (b + h.off_regions);
+    v.diags = (const DiagDesc *) (b + h.off_diags);
+    v.tbs = (const TracebackDesc *) (b + h.off_tracebacks);
+    v.totals = (const TotalDesc *) (b + h.off_totals);
+    v.sym_x = b + h.off_sym_x;
+    v.sym_y = b + h.off_sym_y;
+    v.order_fwd = (const int32_t *) (b + h.off_order_fwd);
+    v.order_bwd = (const int32_t *) (b + h.off_order_bwd);
+    v.aln_region = (const int64_t *) (b + h.off_aln_region);
+    return v;
+}
+
+__device__ __forceinline__ int next_item(int *counter, int lane) {
+    int item = 0;
+    if (lane == 0) item = atomicAdd(counter, 1);
+    return __shfl_sync(FULL_MASK, item, 0);
+}
+
+// ------------------------------------------------------------------------------------------------ forward
+
+template <int S, bool SMEM_RING>
+__global__ void __launch_bounds__(THREADS_PER_BLOCK)
+k_forward(const __grid_constant__ DevModel model, Blob bl, int n_regions, double *__restrict__ F, int *counter,
+          int ring_w) {
+    extern __shared__ double dyn_smem[];
+    __shared__ DevModel sm;
+    for (int i = threadIdx.x; i < (int) (sizeof(DevModel) / 4); i += blockDim.x)
+        ((int32_t *) &sm)[i] = ((const int32_t *) &model)[i];
+    __syncthreads();
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    double *ring = dyn_smem + (size_t) warp * 3 * ring_w * S;
+    const double NINF = neg_inf();
+
+    for (;;) {
+        const int item = next_item(counter, lane);
+        if (item >= n_regions) break;
+        const RegionDesc rg = bl.regions[bl.order_fwd[item]];
+        const DiagDesc *dd = bl.diags + rg.diag_base;
+        const uint8_t *sx = bl.sym_x + rg.sym_x_off, *sy = bl.sym_y + rg.sym_y_off;
+        const int D = rg.lX + rg.lY;
+        // diagonal 0: dpDiagonal_initialiseValues with (ragged)startStateProb, pairwiseAligner.c:658-659
+        int64_t c_prev2 = 0, c_prev1 = dd[0].cell_off, c_cur = dd[1].cell_off;
+        int L2 = 0, L1 = dd[0].xmyL, w2 = 0, w1 = (int) (c_cur - c_prev1);
+        {
+            const double *init = (rg.flags & 1) ? sm.ragged_start : sm.start;
+            for (int j = lane; j < w1; j += 32) {
+                Cell<S> c;
+#pragma unroll
+                for (int s = 0; s < S; s++) c.v[s] = init[s];
+                cell_store<S>(F + (c_prev1 + j) * S, c);
+                if (SMEM_RING) cell_store<S>(ring + (size_t) j * S, c);
+            }
+        }
+        __syncwarp();
+        for (int d = 1; d <= D; d++) {
+            const int L = dd[d].xmyL;
+            const int64_t c_next = dd[d + 1].cell_off;
+            const int w = (int) (c_next - c_cur);
+            const int oLo = (L - 1 - L1) >> 1;  // index shift to the lower neighbour (d-1, xmy-1)
+            const int oMi = (L - L2) >> 1;      // index shift to the middle neighbour (d-2, xmy)
+            double *slot = ring + (size_t) (d % 3) * ring_w * S;
+            const double *slot1 = ring + (size_t) ((d + 2) % 3) * ring_w * S;
+            const double *slot2 = ring + (size_t) ((d + 1) % 3) * ring_w * S;
+            for (int j = lane; j < w; j += 32) {
+                const int xmy = L + 2 * j;
+                const int x = (d + xmy) >> 1, y = (d - xmy) >> 1;
+                const int cX = x > 0 ? sx[x - 1] : 4, cY = y > 0 ? sy[y - 1] : 4;
+                const int iLo = j + oLo, iUp = iLo + 1, iMi = j + oMi;
+                Cell<S> lo, mi, up;
+                if (SMEM_RING) {
+                    lo = (iLo >= 0 && iLo < w1) ? cell_load<S>(slot1 + (size_t) iLo * S) : cell_fill<S>(NINF);
+                    up = (iUp >= 0 && iUp < w1) ? cell_load<S>(slot1 + (size_t) iUp * S) : cell_fill<S>(NINF);
+                    mi = (d >= 2 && iMi >= 0 && iMi < w2) ? cell_load<S>(slot2 + (size_t) iMi * S) : cell_fill<S>(NINF);
+                } else {
+                    lo = (iLo >= 0 && iLo < w1) ? cell_load_cg<S>(F + (c_prev1 + iLo) * S) : cell_fill<S>(NINF);
+                    up = (iUp >= 0 && iUp < w1) ? cell_load_cg<S>(F + (c_prev1 + iUp) * S) : cell_fill<S>(NINF);
+                    mi = (d >= 2 && iMi >= 0 && iMi < w2) ? cell_load_cg<S>(F + (c_prev2 + iMi) * S)
+                                                          : cell_fill<S>(NINF);
+                }
+                const Cell<S> c = forward_cell<S>(lo, mi, up, sm.etp_lower[cX], sm.etp_middle[cX * 5 + cY],
+                                                  sm.etp_upper[cY]);
+                cell_store<S>(F + (c_cur + j) * S, c);
+                if (SMEM_RING) cell_store<S>(slot + (size_t) j * S, c);
+            }
+            __syncwarp();
+            c_prev2 = c_prev1;
+            c_prev1 = c_cur;
+            c_cur = c_next;
+            L2 = L1;
+            L1 = L;
+            w2 = w1;
+            w1 = w;
+        }
+    }
+}
+
+// ------------------------------------------------------------------------------------------------ backward
+
+template <int S, bool SMEM_RING>
+__global__ void __launch_bounds__(THREADS_PER_BLOCK)
+k_backward(const __grid_constant__ DevModel model, Blob bl, int n_tbs, double *__restrict__ B, int *counter,
+           int ring_w) {
+    extern __shared__ double dyn_smem[];
+    __shared__ DevModel sm;
+    for (int i = threadIdx.x; i < (int) (sizeof(DevModel) / 4); i += blockDim.x)
+        ((int32_t *) &sm)[i] = ((const int32_t *) &model)[i];
+    __syncthreads();
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    // The ring is private to the warp: the overlap diagonals (from, hi] that the reference discards must not reach
+    // B, where they would collide with the next traceback's cells.
+    double *ring = dyn_smem + (size_t) warp * 3 * ring_w * S;
+    const double NINF = neg_inf();
+
+    for (;;) {
+        const int item = next_item(counter, lane);
+        if (item >= n_tbs) break;
+        const TracebackDesc tb = bl.tbs[bl.order_bwd[item]];
+        const RegionDesc rg = bl.regions[tb.region];
+        const DiagDesc *dd = bl.diags + rg.diag_base;
+        const uint8_t *sx = bl.sym_x + rg.sym_x_off, *sy = bl.sym_y + rg.sym_y_off;
+        // diagonal hi: (ragged)endStateProb on every cell, pairwiseAligner.c:680-681
+        int L1 = dd[tb.hi].xmyL, L2 = 0;
+        int64_t c1 = dd[tb.hi].cell_off;
+        int w1 = (int) (dd[tb.hi + 1].cell_off - c1), w2 = 0;
+        {
+            const double *init = (tb.at_end && (rg.flags & 2)) ? sm.ragged_end : sm.end;
+            double *slot = ring + (size_t) (tb.hi % 3) * ring_w * S;
+            for (int j = lane; j < w1; j += 32) {
+                Cell<S> c;
+#pragma unroll
+                for (int s = 0; s < S; s++) c.v[s] = init[s];
+                cell_store<S>(slot + (size_t) j * S, c);
+                if (tb.hi <= tb.from) cell_store<S>(B + (c1 + j) * S, c);
+            }
+        }
+        __syncwarp();
+        for (int d = tb.hi - 1; d > tb.lo; d--) {
+            const int L = dd[d].xmyL;
+            const int64_t c0 = dd[d].cell_off;
+            const int w = (int) (c1 - c0);
+            const int oUp = (L - 1 - L1) >> 1;  // (d+1, xmy-1): the cell whose "upper" is T
+            const int oMi = (L - L2) >> 1;      // (d+2, xmy)
+            const bool have2 = d + 2 <= tb.hi;
+            double *slot = ring + (size_t) (d % 3) * ring_w * S;
+            const double *slot1 = ring + (size_t) ((d + 1) % 3) * ring_w * S;
+            const double *slot2 = ring + (size_t) ((d + 2) % 3) * ring_w * S;
+            const bool keep = d <= tb.from;
+            for (int j = lane; j < w; j += 32) {
+                const int xmy = L + 2 * j;
+                const int x = (d + xmy) >> 1, y = (d - xmy) >> 1;
+                // the neighbours consume X[x] and/or Y[y] (0-based); past the end they are out of band anyway
+                const int cX = x < rg.lX ? sx[x] : 4, cY = y < rg.lY ? sy[y] : 4;
+                const int iUp = j + oUp, iLo = iUp + 1, iMi = j + oMi;
+                const Cell<S> nUp = (iUp >= 0 && iUp < w1) ? cell_load<S>(slot1 + (size_t) iUp * S) : cell_fill<S>(NINF);
+                const Cell<S> nLo = (iLo >= 0 && iLo < w1) ? cell_load<S>(slot1 + (size_t) iLo * S) : cell_fill<S>(NINF);
+                const Cell<S> nMi = (have2 && iMi >= 0 && iMi < w2) ? cell_load<S>(slot2 + (size_t) iMi * S)
+                                                                     : cell_fill<S>(NINF);
+                const Cell<S> c = backward_cell<S>(nMi, nUp, nLo, sm.etp_middle[cX * 5 + cY], sm.etp_upper[cY],
+                                                   sm.etp_lower[cX]);
+                cell_store<S>(slot + (size_t) j * S, c);
+                if (keep) cell_store<S>(B + (c0 + j) * S, c);
+            }
+            __syncwarp();
+            L2 = L1;
+            L1 = L;
+            w2 = w1;
+            w1 = w;
+            c1 = c0;
+        }
+    }
+}
+
+// ------------------------------------------------------------------------------------------------ totals
+
+// diagonalCalculationTotalProbability (pairwiseAligner.c:566-583).  The "matches that jump over d" term rebuilds, in
+// the reference, a temporary diagonal d+1 holding only the match state reached from forward diagonal d-1; that value
+// is by construction identical to the match state of forward diagonal d+1, which we already have.
+template <int S>
+__global__ void k_totals(Blob bl, int n_totals, const double *__restrict__ F, const double *__restrict__ B,
+                         double *__restrict__ totals) {
+    const int t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= n_totals) return;
+    const TotalDesc td = bl.totals[t];
+    const RegionDesc &rg = bl.regions[td.region];
+    const DiagDesc *dd = bl.diags + rg.diag_base;
+    const int64_t c0 = dd[td.d].cell_off, c1 = dd[td.d + 1].cell_off;
+    double total = neg_inf();
+    for (int64_t c = c0; c < c1; c++) {
+        const double *f = F + c * S, *b = B + c * S;
+        double cd = __dadd_rn(f[0], b[0]);
+#pragma unroll
+        for (int s = 1; s < S; s++) cd = la(cd, __dadd_rn(f[s], b[s]));
+        total = la(total, cd);
+    }
+    if (td.has_through) {
+        const int64_t c2 = dd[td.d + 2].cell_off;
+        double through = neg_inf();
+        for (int64_t c = c1; c < c2; c++) through = la(through, __dadd_rn(F[c * S], B[c * S]));
+        total = la(total, through);
+    }
+    totals[t] = total;
+}
+
+// ------------------------------------------------------------------------------------------------ posteriors
+
+// diagonalCalculationPosteriorMatchProbs (pairwiseAligner.c:585-615), one warp per region.  Writes p_int (or -1)
+// per cell and the number of emitted pairs per region.
+template <int S>
+__global__ void __launch_bounds__(THREADS_PER_BLOCK)
+k_posterior_count(Blob bl, int n_regions, const double *__restrict__ F, const double *__restrict__ B,
+                  const double *__restrict__ totals, double threshold, int32_t *__restrict__ pint,
+                  int64_t *__restrict__ counts, int *counter) {
+    const int lane = threadIdx.x & 31;
+    for (;;) {
+        const int item = next_item(counter, lane);
+        if (item >= n_regions) break;
+        const int r = bl.order_fwd[item];
+        const RegionDesc rg = bl.regions[r];
+        const DiagDesc *dd = bl.diags + rg.diag_base;
+        const int D = rg.lX + rg.lY;
+        int count = 0;
+        for (int j = lane; j < (int) (dd[1].cell_off - dd[0].cell_off); j += 32) pint[dd[0].cell_off + j] = -1;
+        for (int d = 1; d <= D; d++) {
+            const DiagDesc cur = dd[d];
+            const int w = (int) (dd[d + 1].cell_off - cur.cell_off);
+            const double total = totals[cur.tot_flags & MAB_DIAG_TOT_MASK];
+            for (int j = lane; j < w; j += 32) {
+                const int xmy = cur.xmyL + 2 * j;
+                const int x = (d + xmy) >> 1, y = (d - xmy) >> 1;
+                int32_t v = -1;
+                if (x > 0 && y > 0) {
+                    const int64_t c = cur.cell_off + j;
+                    double p = exp(__dsub_rn(__dadd_rn(F[c * S], B[c * S]), total));
+                    if (p >= threshold) {
+                        if (p > 1.0) p = 1.0;
+                        v = (int32_t) floor(__dmul_rn(p, MAB_PROB_1));
+                        count++;
+                    }
+                }
+                pint[cur.cell_off + j] = v;
+            }
+        }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) count += __shfl_xor_sync(FULL_MASK, count, o);
+        if (lane == 0) counts[r] = count;
+    }
+}
+
+// Exclusive scan of the per-region counts (single block), then per-alignment offsets.
+__global__ void k_scan(int64_t *counts, int64_t n_regions, const int64_t *aln_region, int64_t n_aln,
+                       int64_t *pair_off, int64_t *n_pairs) {
+    __shared__ int64_t warp_sums[32];
+    __shared__ int64_t carry;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nw = blockDim.x >> 5;
+    if (threadIdx.x == 0) carry = 0;
+    __syncthreads();
+    for (int64_t base = 0; base < n_regions; base += blockDim.x) {
+        const int64_t i = base + threadIdx.x;
+        const int64_t v = i < n_regions ? counts[i] : 0;
+        int64_t incl = v;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const int64_t n = __shfl_up_sync(FULL_MASK, incl, o);
+            if (lane >= o) incl += n;
+        }
+        if (lane == 31) warp_sums[warp] = incl;
+        __syncthreads();
+        if (warp == 0) {
+            int64_t ws = lane < nw ? warp_sums[lane] : 0;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const int64_t n = __shfl_up_sync(FULL_MASK, ws, o);
+                if (lane >= o) ws += n;
+            }
+            warp_sums[lane] = ws;  // inclusive over warps
+        }
+        __syncthreads();
+        const int64_t before = carry + (warp > 0 ? warp_sums[warp - 1] : 0) + incl - v;
+        if (i < n_regions) counts[i] = before;
+        __syncthreads();
+        if (threadIdx.x == 0) carry += warp_sums[nw - 1];
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) {
+        counts[n_regions] = carry;
+        n_pairs[0] = carry;
+    }
+    __syncthreads();
+    for (int64_t a = threadIdx.x; a <= n_aln; a += blockDim.x) pair_off[a] = counts[aln_region[a]];
+}
+
+// Ordered compaction.  The reference appends pairs per traceback (ascending), per diagonal descending, per cell in
+// ascending x-y (:594-613, :695-733); alignedPairCoordinateCorrectionFn then pops each region's list from the tail
+// (:1167-1169), i.e. reverses it.  Net order inside a region: tracebacks descending, diagonals ascending, x-y
+// descending.  Regions are concatenated in ascending order.
+__global__ void __launch_bounds__(THREADS_PER_BLOCK)
+k_emit(Blob bl, int n_regions, const int32_t *__restrict__ pint, const int64_t *__restrict__ offsets,
+       int32_t *__restrict__ out_x, int32_t *__restrict__ out_y, int32_t *__restrict__ out_p, int64_t capacity,
+       int *counter) {
+    const int lane = threadIdx.x & 31;
+    for (;;) {
+        const int item = next_item(counter, lane);
+        if (item >= n_regions) break;
+        const int r = bl.order_fwd[item];
+        const RegionDesc rg = bl.regions[r];
+        const DiagDesc *dd = bl.diags + rg.diag_base;
+        int64_t pos = offsets[r];
+        for (int t = rg.n_tb - 1; t >= 0; t--) {
+            const TracebackDesc tb = bl.tbs[rg.tb_base + t];
+            for (int d = tb.lo + 1; d <= tb.from; d++) {
+                const DiagDesc cur = dd[d];
+                const int w = (int) (dd[d + 1].cell_off - cur.cell_off);
+                for (int j0 = 0; j0 < w; j0 += 32) {
+                    const int j = w - 1 - (j0 + lane);
+                    int32_t v = -1;
+                    if (j >= 0) v = pint[cur.cell_off + j];
+                    const unsigned ballot = __ballot_sync(FULL_MASK, v >= 0);
+                    if (v >= 0) {
+                        const int64_t at = pos + __popc(ballot & ((1u << lane) - 1));
+                        if (at < capacity) {
+                            const int xmy = cur.xmyL + 2 * j;
+                            out_x[at] = rg.x1 + ((d + xmy) >> 1) - 1;
+                            out_y[at] = rg.y1 + ((d - xmy) >> 1) - 1;
+                            out_p[at] = v;
+                        }
+                    }
+                    pos += __popc(ballot);
+                }
+            }
+        }
+    }
+}
+
+// ------------------------------------------------------------------------------------------------ expectations
+
+// diagonalCalculationExpectations + updateExpectations (pairwiseAligner.c:348-368, 617-628), one warp per region.
+// Per block: transitions / emissions / likelihood are accumulated in shared memory, then added to the global
+// accumulator with one atomic per entry.
+template <int S>
+__global__ void __launch_bounds__(THREADS_PER_BLOCK)
+k_expect(const __grid_constant__ DevModel model, Blob bl, int n_regions, const double *__restrict__ F,
+         const double *__restrict__ B, const double *__restrict__ totals, double *__restrict__ out, int *counter) {
+    constexpr int NT = S == 5 ? 13 : 9;
+    constexpr int NL = S == 5 ? 4 : 3, NM = S == 5 ? 5 : 3;
+    constexpr int NOUT = S * S + S * 16 + 1;
+    __shared__ DevModel sm;
+    __shared__ double acc[NOUT];
+    for (int i = threadIdx.x; i < (int) (sizeof(DevModel) / 4); i += blockDim.x)
+        ((int32_t *) &sm)[i] = ((const int32_t *) &model)[i];
+    for (int i = threadIdx.x; i < NOUT; i += blockDim.x) acc[i] = 0.0;
+    __syncthreads();
+    const int lane = threadIdx.x & 31;
+    const double NINF = neg_inf();
+    double tacc[NT];
+#pragma unroll
+    for (int k = 0; k < NT; k++) tacc[k] = 0.0;
+    double lik = 0.0;
+
+    for (;;) {
+        const int item = next_item(counter, lane);
+        if (item >= n_regions) break;
+        const RegionDesc rg = bl.regions[bl.order_fwd[item]];
+        const DiagDesc *dd = bl.diags + rg.diag_base;
+        const uint8_t *sx = bl.sym_x + rg.sym_x_off, *sy = bl.sym_y + rg.sym_y_off;
+        const int D = rg.lX + rg.lY;
+        for (int d = 1; d <= D; d++) {
+            const DiagDesc cur = dd[d], p1 = dd[d - 1];
+            const int w = (int) (dd[d + 1].cell_off - cur.cell_off);
+            const int w1 = (int) (cur.cell_off - p1.cell_off);
+            const double total = totals[cur.tot_flags & MAB_DIAG_TOT_MASK];
+            if (lane == 0) lik += total;  // hmmExpectations->likelihood += totalProbability, once per diagonal (:625)
+            const bool mid_ok = d >= 2 && !(cur.tot_flags & MAB_DIAG_NO_MIDDLE);
+            int64_t c2 = 0;
+            int L2 = 0, w2 = 0;
+            if (d >= 2) {
+                const DiagDesc p2 = dd[d - 2];
+                c2 = p2.cell_off;
+                L2 = p2.xmyL;
+                w2 = (int) (p1.cell_off - p2.cell_off);
+            }
+            const int oLo = (cur.xmyL - 1 - p1.xmyL) >> 1, oMi = (cur.xmyL - L2) >> 1;
+            for (int j = lane; j < w; j += 32) {
+                const int xmy = cur.xmyL + 2 * j;
+                const int x = (d + xmy) >> 1, y = (d - xmy) >> 1;
+                const int cX = x > 0 ? sx[x - 1] : 4, cY = y > 0 ? sy[y - 1] : 4;
+                const int iLo = j + oLo, iUp = iLo + 1, iMi = j + oMi;
+                const Cell<S> b = cell_load<S>(B + (cur.cell_off + j) * S);
+                const Cell<S> lo = (iLo >= 0 && iLo < w1) ? cell_load<S>(F + (p1.cell_off + iLo) * S) : cell_fill<S>(NINF);
+                const Cell<S> up = (iUp >= 0 && iUp < w1) ? cell_load<S>(F + (p1.cell_off + iUp) * S) : cell_fill<S>(NINF);
+                const Cell<S> mi = (mid_ok && iMi >= 0 && iMi < w2) ? cell_load<S>(F + (c2 + iMi) * S) : cell_fill<S>(NINF);
+                const double *eL = sm.etp_lower[cX], *eM = sm.etp_middle[cX * 5 + cY], *eU = sm.etp_upper[cY];
+                double e_to[S];
+#pragma unroll
+                for (int s = 0; s < S; s++) e_to[s] = 0.0;
+#pragma unroll
+                for (int k = 0; k < NT; k++) {
+                    const int from = sm.t_from[k], to = sm.t_to[k];
+                    double f, e;
+                    if (k < NL) {
+                        f = lo.v[0];
+#pragma unroll
+                        for (int s = 1; s < S; s++) f = from == s ? lo.v[s] : f;
+                        e = eL[k];
+                    } else if (k < NL + NM) {
+                        f = mi.v[0];
+#pragma unroll
+                        for (int s = 1; s < S; s++) f = from == s ? mi.v[s] : f;
+                        e = eM[k - NL];
+                    } else {
+                        f = up.v[0];
+#pragma unroll
+                        for (int s = 1; s < S; s++) f = from == s ? up.v[s] : f;
+                        e = eU[k - NL - NM];
+                    }
+                    double bt = b.v[0];
+#pragma unroll
+                    for (int s = 1; s < S; s++) bt = to == s ? b.v[s] : bt;
+                    // exp(fromCells[from] + toCells[to] + (eP + tP) - totalProbability), left to right (:356)
+                    const double p = exp(__dsub_rn(__dadd_rn(__dadd_rn(f, bt), e), total));
+                    tacc[k] += p;
+#pragma unroll
+                    for (int s = 0; s < S; s++) e_to[s] += to == s ? p : 0.0;
+                }
+                if (cX < 4 && cY < 4) {
+#pragma unroll
+                    for (int s = 0; s < S; s++) atomicAdd(&acc[S * S + s * 16 + cX * 4 + cY], e_to[s]);
+                }
+            }
+        }
+    }
+    // reduce the per-lane transition sums
+#pragma unroll
+    for (int k = 0; k < NT; k++) {
+        double v = tacc[k];
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(FULL_MASK, v, o);
+        if (lane == 0) atomicAdd(&acc[sm.t_from[k] * S + sm.t_to[k]], v);
+    }
+    if (lane == 0) atomicAdd(&acc[NOUT - 1], lik);
+    __syncthreads();
+    for (int i = threadIdx.x; i < NOUT; i += blockDim.x)
+        if (acc[i] != 0.0) atomicAdd(&out[i], acc[i]);
+}
+
+// ------------------------------------------------------------------------------------------------ launch helpers
+
+int check(cudaError_t e, const char *what) {
+    if (e != cudaSuccess) {
+        mab_set_error("CUDA error in %s: %s", what, cudaGetErrorString(e));
+        return MAB_E_CUDA;
+    }
+    return MAB_OK;
+}
+
+struct DeviceInfo {
+    int sm_count = 0;
+    int max_smem_optin = 0;
+    bool ok = false;
+};
+
+const DeviceInfo &device_info() {
+    static thread_local DeviceInfo info;
+    static thread_local int cached_dev = -1;
+    int dev = -1;
+    if (cudaGetDevice(&dev) != cudaSuccess) {
+        info.ok = false;
+        return info;
+    }
+    if (dev != cached_dev) {
+        cudaDeviceProp prop;
+        info.ok = cudaGetDeviceProperties(&prop, dev) == cudaSuccess;
+        info.sm_count = prop.multiProcessorCount;
+        info.max_smem_optin = (int) prop.sharedMemPerBlockOptin;
+        cached_dev = dev;
+    }
+    return info;
+}
+
+struct Workspace {
+    double *fwd, *bwd, *totals;
+    int32_t *pint;
+    int64_t *counts;
+    int *counters;
+};
+
+int carve(const mab_plan *plan, void *d_ws, int64_t ws_bytes, int S, bool expectations, Workspace *w) {
+    const WorkspaceLayout lay = mab_workspace_layout(plan->hdr, S, expectations);
+    if (ws_bytes < lay.total_bytes) {
+        mab_set_error("workspace too small: need %lld bytes, got %lld", (long long) lay.total_bytes, (long long) ws_bytes);
+        return MAB_E_CAPACITY;
+    }
+    if (((uintptr_t) d_ws & 255) != 0) {
+        mab_set_error("workspace must be 256-byte aligned");
+        return MAB_E_ARG;
+    }
+    uint8_t *b = (uint8_t *) d_ws;
+    w->counters = (int *) (b + lay.off_counters);
+    w->fwd = (double *) (b + lay.off_fwd);
+    w->bwd = (double *) (b + lay.off_bwd);
+    w->totals = (double *) (b + lay.off_totals);
+    w->pint = (int32_t *) (b + lay.off_pint);
+    w->counts = (int64_t *) (b + lay.off_counts);
+    return MAB_OK;
+}
+
+int grid_for(int64_t items, int blocks_per_sm, int warps_per_block = WARPS_PER_BLOCK) {
+    const DeviceInfo &di = device_info();
+    const int64_t want = (items + warps_per_block - 1) / warps_per_block;
+    const int64_t cap = (int64_t) di.sm_count * blocks_per_sm;
+    return (int) (want < 1 ? 1 : (want < cap ? want : cap));
+}
+
+// forward + backward + totals: shared by posterior and expectation mode
+template <int S>
+int run_dp(const DevModel &dm, const mab_plan *plan, const Blob &bl, const Workspace &w, cudaStream_t st) {
+    const BlobHeader &h = plan->hdr;
+    const DeviceInfo &di = device_info();
+    // shared-memory ring: 3 diagonals x max_width cells x S doubles per warp; fewer warps per block for wide bands
+    const int64_t ring_per_warp = (int64_t) 3 * h.max_width * S * 8;
+    const int64_t budget = (int64_t) di.max_smem_optin - (int64_t) sizeof(DevModel) - 1024;
+    const int nw = (int) std::min<int64_t>(WARPS_PER_BLOCK, budget / std::max<int64_t>(1, ring_per_warp));
+    if (nw < 1) {
+        mab_set_error("band too wide for the shared-memory ring (max width %lld cells); lower diagonalExpansion or "
+                      "splitMatrixBiggerThanThis", (long long) h.max_width);
+        return MAB_E_ARG;
+    }
+    const int64_t ring_bytes = ring_per_warp * nw;
+    const int ring_w = (int) h.max_width;
+    const int blocks_per_sm = (int) std::max<int64_t>(1, std::min<int64_t>(8, (200 * 1024) / (ring_bytes + 4096)));
+    int rc;
+    if ((rc = check(cudaMemsetAsync(w.counters, 0, 256, st), "memset counters"))) return rc;
+    if ((rc = check(cudaFuncSetAttribute(k_forward<S, true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         (int) ring_bytes), "smem attr fwd"))) return rc;
+    if ((rc = check(cudaFuncSetAttribute(k_backward<S, true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         (int) ring_bytes), "smem attr bwd"))) return rc;
+    k_forward<S, true><<<grid_for(h.n_regions, blocks_per_sm, nw), nw * 32, ring_bytes, st>>>(
+        dm, bl, (int) h.n_regions, w.fwd, w.counters + 0, ring_w);
+    g_launches++;
+    k_backward<S, true><<<grid_for(h.n_tracebacks, blocks_per_sm, nw), nw * 32, ring_bytes, st>>>(
+        dm, bl, (int) h.n_tracebacks, w.bwd, w.counters + 1, ring_w);
+    g_launches++;
+    if (h.n_totals > 0) {
+        k_totals<S><<<(int) ((h.n_totals + 127) / 128), 128, 0, st>>>(bl, (int) h.n_totals, w.fwd, w.bwd, w.totals);
+        g_launches++;
+    }
+    return check(cudaGetLastError(), "dp launch");
+}
+
+template <int S>
+int run_posteriors(const DevModel &dm, const mab_plan *plan, const void *d_blob, const Workspace &w,
+                   int64_t *d_pair_off, int64_t *d_n_pairs, cudaStream_t st) {
+    const BlobHeader &h = plan->hdr;
+    const Blob bl = blob_view(d_blob, h);
+    int rc = run_dp<S>(dm, plan, bl, w, st);
+    if (rc) return rc;
+    k_posterior_count<S><<<grid_for(h.n_regions, 8), THREADS_PER_BLOCK, 0, st>>>(
+        bl, (int) h.n_regions, w.fwd, w.bwd, w.totals, plan->params.threshold, w.pint, w.counts, w.counters + 2);
+    g_launches++;
+    k_scan<<<1, 1024, 0, st>>>(w.counts, h.n_regions, bl.aln_region, h.n_alignments, d_pair_off, d_n_pairs);
+    g_launches++;
+    return check(cudaGetLastError(), "posterior launch");
+}
+
+template <int S>
+int run_expectations(const DevModel &dm, const mab_plan *plan, const void *d_blob, const Workspace &w, double *d_out,
+                     cudaStream_t st) {
+    const BlobHeader &h = plan->hdr;
+    const Blob bl = blob_view(d_blob, h);
+    int rc = run_dp<S>(dm, plan, bl, w, st);
+    if (rc) return rc;
+    k_expect<S><<<grid_for(h.n_regions, 8), THREADS_PER_BLOCK, 0, st>>>(dm, bl, (int) h.n_regions, w.fwd, w.bwd,
+                                                                        w.totals, d_out, w.counters + 4);
+    g_launches++;
+    return check(cudaGetLastError(), "expectation launch");
+}
+
+int require_gpu() {
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess || n == 0) {
+        cudaGetLastError();
+        mab_set_error("no CUDA device: libmargin_b200 has no CPU fallback");
+        return MAB_E_NOGPU;
+    }
+    return MAB_OK;
+}
+
+}  // namespace
+
+extern "C" int mab_device_count(void) {
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess) {
+        cudaGetLastError();
+        return 0;
+    }
+    return n;
+}
+
+extern "C" int64_t mab_launch_count(int reset) {
+    const int64_t v = g_launches;
+    if (reset) g_launches = 0;
+    return v;
+}
+
+extern "C" int mab_posteriors_compute(const mab_model *m, const mab_plan *plan, const void *d_blob, void *d_ws,
+                                      int64_t ws_bytes, int64_t *d_pair_off, int64_t *d_n_pairs, void *stream) {
+    if (!m || !plan || !d_blob || !d_ws || !d_pair_off || !d_n_pairs) {
+        mab_set_error("mab_posteriors_compute: null argument");
+        return MAB_E_ARG;
+    }
+    int rc = require_gpu();
+    if (rc) return rc;
+    Workspace w;
+    if ((rc = carve(plan, d_ws, ws_bytes, MAB_MAX_S, false, &w))) return rc;
+    DevModel dm;
+    mab_model_to_device_block(m, &dm);
+    cudaStream_t st = (cudaStream_t) stream;
+    if (plan->hdr.n_regions == 0) {
+        // nothing to align: all offsets zero
+        if ((rc = check(cudaMemsetAsync(d_pair_off, 0, (plan->hdr.n_alignments + 1) * 8, st), "memset"))) return rc;
+        return check(cudaMemsetAsync(d_n_pairs, 0, 8, st), "memset");
+    }
+    return m->S == 5 ? run_posteriors<5>(dm, plan, d_blob, w, d_pair_off, d_n_pairs, st)
+                     : run_posteriors<3>(dm, plan, d_blob, w, d_pair_off, d_n_pairs, st);
+}
+
+extern "C" int mab_posteriors_emit(const mab_plan *plan, const void *d_blob, void *d_ws, int64_t ws_bytes, int32_t *d_x,
+                                   int32_t *d_y, int32_t *d_p, int64_t capacity, void *stream) {
+    if (!plan || !d_blob || !d_ws || (capacity > 0 && (!d_x || !d_y || !d_p))) {
+        mab_set_error("mab_posteriors_emit: null argument");
+        return MAB_E_ARG;
+    }
+    int rc = require_gpu();
+    if (rc) return rc;
+    Workspace w;
+    if ((rc = carve(plan, d_ws, ws_bytes, MAB_MAX_S, false, &w))) return rc;
+    const BlobHeader &h = plan->hdr;
+    if (h.n_regions == 0 || capacity == 0) return MAB_OK;
+    cudaStream_t st = (cudaStream_t) stream;
+    const Blob bl = blob_view(d_blob, h);
+    k_emit<<<grid_for(h.n_regions, 8), THREADS_PER_BLOCK, 0, st>>>(bl, (int) h.n_regions, w.pint, w.counts, d_x, d_y, d_p,
+                                                                   capacity, w.counters + 3);
+    g_launches++;
+    return check(cudaGetLastError(), "emit launch");
+}
+
+extern "C" int mab_expectations(const mab_model *m, const mab_plan *plan, const void *d_blob, void *d_ws,
+                                int64_t ws_bytes, double *d_out, void *stream) {
+    if (!m || !plan || !d_blob || !d_ws || !d_out) {
+        mab_set_error("mab_expectations: null argument");
+        return MAB_E_ARG;
+    }
+    int rc = require_gpu();
+    if (rc) return rc;
+    Workspace w;
+    if ((rc = carve(plan, d_ws, ws_bytes, MAB_MAX_S, true, &w))) return rc;
+    if (plan->hdr.n_regions == 0) return MAB_OK;
+    DevModel dm;
+    mab_model_to_device_block(m, &dm);
+    cudaStream_t st = (cudaStream_t) stream;
+    return m->S == 5 ? run_expectations<5>(dm, plan, d_blob, w, d_out, st)
+                     : run_expectations<3>(dm, plan, d_blob, w, d_out, st);
+}
+
+extern "C" int mab_debug_copy_matrices(const mab_plan *plan, const void *d_ws, double *h_fwd, double *h_bwd,
+                                       double *h_totals, void *stream) {
+    if (!plan || !d_ws) return MAB_E_ARG;
+    // the workspace is always carved for MAB_MAX_S; a 3-state run still packs its cells with stride 3 at the start
+    const WorkspaceLayout lay = mab_workspace_layout(plan->hdr, MAB_MAX_S, false);
+    const uint8_t *b = (const uint8_t *) d_ws;
+    cudaStream_t st = (cudaStream_t) stream;
+    int rc;
+    const int64_t cell_bytes = plan->hdr.n_cells * MAB_MAX_S * 8;
+    if (h_fwd && (rc = check(cudaMemcpyAsync(h_fwd, b + lay.off_fwd, cell_bytes, cudaMemcpyDeviceToHost, st), "copy fwd")))
+        return rc;
+    if (h_bwd && (rc = check(cudaMemcpyAsync(h_bwd, b + lay.off_bwd, cell_bytes, cudaMemcpyDeviceToHost, st), "copy bwd")))
+        return rc;
+    if (h_totals && (rc = check(cudaMemcpyAsync(h_totals, b + lay.off_totals, plan->hdr.n_totals * 8,
+                                                cudaMemcpyDeviceToHost, st), "copy totals")))
+        return rc;
+    return check(cudaStreamSynchronize(st), "sync");
+}

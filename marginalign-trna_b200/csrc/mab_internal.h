@@ -1,0 +1,130 @@
+// mab_internal.h -- layouts shared by the host planner (plan.cpp), the model builder (model.cpp) and the
+// CUDA kernels (kernels.cu).  Not part of the public ABI (include/margin_b200.h is).
+#pragma once
+#include <cstdint>
+#include <string>
+#include <vector>
+
+#include "../../include/margin_b200.h"
+
+#define MAB_MAX_S 5
+#define MAB_BLOB_MAGIC 0x4d41423230304231LL /* "MAB200B1" */
+#define MAB_PROB_1 10000000.0               /* PAIR_ALIGNMENT_PROB_1, cPecan/inc/pairwiseAligner.h:26 */
+
+void mab_set_error(const char *fmt, ...);
+
+// ---------------------------------------------------------------------------------------------- model
+
+// Host model: the generic ordered-transition-list form (mirrors what stateMachine{5,3}_cellCalculate hard-code).
+struct mab_model {
+    int32_t type;
+    int32_t S;
+    int32_t n_trans[3];
+    int32_t from[3][5];
+    int32_t to[3][5];
+    double tp[3][5];
+    double start[MAB_MAX_S], ragged_start[MAB_MAX_S], end[MAB_MAX_S], ragged_end[MAB_MAX_S];
+    double em_match[25];
+    double em_gap_x[5];
+    double em_gap_y[5];
+};
+
+// Device model block, passed to kernels by value (kernel parameter space) and staged into shared memory.
+// etp_* = (eP + tP), the exact sub-expression the reference forms before adding the cell value
+// (pairwiseAligner.c:314,324,356), so precomputing it keeps the DP bit-identical.
+struct DevModel {
+    int32_t S;
+    int32_t n_lower, n_middle, n_upper;  // 4,5,4 (5-state) or 3,3,3 (3-state)
+    double etp_lower[5][5];              // [cX][k]
+    double etp_middle[25][5];            // [cX*5+cY][k]
+    double etp_upper[5][5];              // [cY][k]
+    double start[MAB_MAX_S], ragged_start[MAB_MAX_S], end[MAB_MAX_S], ragged_end[MAB_MAX_S];
+    int32_t t_from[13], t_to[13];        // flattened transition list (lower, middle, upper) for the expectation kernel
+};
+void mab_model_to_device_block(const mab_model *m, DevModel *out);
+
+// ---------------------------------------------------------------------------------------------- plan blob
+
+struct BlobHeader {  // 256 bytes
+    int64_t magic;
+    int64_t n_alignments, n_regions, n_diagonals, n_cells, n_tracebacks, n_totals, n_anchors, max_width;
+    int64_t len_sym_x, len_sym_y;
+    // byte offsets of the arrays inside the blob (each 16-byte aligned)
+    int64_t off_regions;      // RegionDesc[n_regions]
+    int64_t off_diags;        // DiagDesc[n_diagonals + 1]   (last entry is a sentinel carrying n_cells)
+    int64_t off_tracebacks;   // TracebackDesc[n_tracebacks]
+    int64_t off_totals;       // TotalDesc[n_totals]
+    int64_t off_sym_x;        // uint8 symbol codes 0..4 of all X sequences, concatenated like seq_x
+    int64_t off_sym_y;
+    int64_t off_order_fwd;    // int32[n_regions]   regions, longest first
+    int64_t off_order_bwd;    // int32[n_tracebacks] tracebacks, longest first
+    int64_t off_aln_region;   // int64[n_alignments + 1] first region of each alignment
+    int64_t blob_bytes;
+    int64_t pad[11];
+};
+static_assert(sizeof(BlobHeader) == 256, "BlobHeader must be 256 bytes");
+
+struct RegionDesc {  // 64 bytes
+    int64_t sym_x_off, sym_y_off;  // start of this region's symbols inside sym_x / sym_y
+    int64_t diag_base;             // global index of this region's xay = 0 diagonal
+    int32_t lX, lY;
+    int32_t x1, y1;                // origin inside the alignment (alignedPairCoordinateCorrectionFn)
+    int32_t aln;
+    int32_t flags;                 // bit0 ragged left, bit1 ragged right (after the split rule of :1121-1122)
+    int32_t tb_base, n_tb;
+    int32_t tot_base, n_tot;
+};
+static_assert(sizeof(RegionDesc) == 64, "RegionDesc must be 64 bytes");
+
+#define MAB_DIAG_NO_MIDDLE 0x80000000u  // forward diagonal xay-2 was already freed when the reference visits xay
+#define MAB_DIAG_TOT_MASK 0x7fffffffu
+struct DiagDesc {  // 16 bytes
+    int64_t cell_off;   // global index of the first cell of this diagonal
+    int32_t xmyL;       // smallest x-y on the diagonal; cell j has x-y = xmyL + 2j
+    uint32_t tot_flags; // index of the total-probability value the reference uses on this diagonal | flags
+};
+static_assert(sizeof(DiagDesc) == 16, "DiagDesc must be 16 bytes");
+
+struct TracebackDesc {  // 32 bytes
+    int32_t region;
+    int32_t lo;     // tracedBackTo before this traceback
+    int32_t hi;     // diagonal the backward pass starts from
+    int32_t from;   // tracedBackFrom: posteriors are produced for diagonals (lo, from]
+    int32_t at_end;
+    int32_t tot_base;  // global index of this traceback's first total (at diagonal `from`)
+    int32_t n_tot;
+    int32_t pad;
+};
+static_assert(sizeof(TracebackDesc) == 32, "TracebackDesc must be 32 bytes");
+
+struct TotalDesc {  // 16 bytes
+    int32_t region;
+    int32_t d;            // diagonal (region-local xay) the total is evaluated on
+    int32_t has_through;  // backward diagonal d+1 is alive (d < hi): add matches that jump over d
+    int32_t pad;
+};
+static_assert(sizeof(TotalDesc) == 16, "TotalDesc must be 16 bytes");
+
+// ---------------------------------------------------------------------------------------------- host plan object
+
+struct mab_plan {
+    mab_params params;
+    BlobHeader hdr;
+    std::vector<RegionDesc> regions;
+    std::vector<DiagDesc> diags;
+    std::vector<TracebackDesc> tbs;
+    std::vector<TotalDesc> totals;
+    std::vector<uint8_t> sym_x, sym_y;
+    std::vector<int32_t> order_fwd, order_bwd;
+    std::vector<int64_t> aln_region;
+    // kept for introspection only
+    std::vector<int64_t> anchors;      // x,y interleaved, alignment-local
+    std::vector<int64_t> anchor_off;   // [n+1]
+};
+
+// workspace carving (device scratch); all offsets 256-byte aligned
+struct WorkspaceLayout {
+    int64_t off_fwd, off_bwd, off_totals, off_pint, off_counts, off_counters, off_partials;
+    int64_t total_bytes;
+};
+WorkspaceLayout mab_workspace_layout(const BlobHeader &h, int S, bool expectations);

@@ -1,0 +1,371 @@
+"""Host side of the B200 pair-HMM path: models, parameters, batch planning and the two public operations.
+
+These are the in-process replacements for what the reference does by spawning `cPecanRealign` once per read:
+  get_aligned_pairs_using_anchors   <- getAlignedPairsUsingAnchors   (cPecan/impl/pairwiseAligner.c:1172)
+  get_expectations_using_anchors    <- getExpectationsUsingAnchors   (cPecan/impl/pairwiseAligner.c:1201)
+applied to a whole batch of guide alignments at once.  PyTorch is used only for device/pinned buffers and streams;
+all arithmetic happens in libmargin_b200.so (CUDA, sm_100a).  There is no CPU fallback: without a CUDA device the
+operations raise RuntimeError.
+"""
+import ctypes as C
+from concurrent.futures import ThreadPoolExecutor
+from dataclasses import dataclass
+
+import numpy as np
+
+from . import capi
+from .hmm import Hmm
+from .synth import AlignmentBatch
+
+
+@dataclass
+class AlignmentParameters:
+    """PairwiseAlignmentParameters (cPecan/inc/pairwiseAligner.h:28-39) as set by cPecanRealign's flags.
+
+    split_matrix_bigger_than is the *flag value* (--splitMatrixBiggerThanThis); it is squared on the way in exactly
+    as cPecanRealign.c:459 does.  Defaults are the realign call site's (src/margin/marginAlignLib.py:315-318).
+    """
+    threshold: float = 0.01
+    min_diags_between_traceback: int = 1000
+    traceback_diagonals: int = 40
+    diagonal_expansion: int = 10
+    split_matrix_bigger_than: int = 3000
+    ragged_left: bool = True
+    ragged_right: bool = True
+
+    def to_c(self):
+        return capi.MabParams(self.threshold, self.min_diags_between_traceback, self.traceback_diagonals,
+                              self.diagonal_expansion, int(self.split_matrix_bigger_than) ** 2,
+                              int(self.ragged_left), int(self.ragged_right))
+
+
+class PairHmmModel:
+    """A loaded state machine (replaces hmm_loadFromFile + hmm_getStateMachine / stateMachine5_construct)."""
+
+    def __init__(self, handle):
+        self._h = handle
+        L = capi.load()
+        self.state_number = L.mab_model_state_number(handle)
+        self.type = L.mab_model_type(handle)
+
+    @classmethod
+    def from_hmm(cls, hmm: Hmm):
+        return cls.from_arrays(hmm._modelTypeInt(), hmm.transitions, hmm.emissions)
+
+    @classmethod
+    def from_arrays(cls, hmm_type, transitions, emissions):
+        L = capi.load()
+        S = 5 if hmm_type <= 1 else 3
+        T = np.ascontiguousarray(transitions, dtype=np.float64)
+        E = np.ascontiguousarray(emissions, dtype=np.float64)
+        if T.size != S * S or E.size != S * 16:
+            raise RuntimeError("hmm type %d needs %d transitions and %d emissions" % (hmm_type, S * S, S * 16))
+        h = capi.vp()
+        capi.check(L.mab_model_from_hmm(int(hmm_type), T.ctypes.data_as(capi.dp), E.ctypes.data_as(capi.dp),
+                                        C.byref(h)))
+        return cls(h)
+
+    @classmethod
+    def from_file(cls, path):
+        return cls.from_hmm(Hmm.loadHmm(path))
+
+    @classmethod
+    def default(cls, hmm_type=0):
+        """The built-in machine cPecanRealign uses without --loadHmm (cPecanRealign.c:526): fiveState."""
+        L = capi.load()
+        h = capi.vp()
+        capi.check(L.mab_model_default(int(hmm_type), C.byref(h)))
+        return cls(h)
+
+    def transitions(self):
+        L = capi.load()
+        out = np.zeros((13, 4))
+        n = L.mab_model_transitions(self._h, out.ctypes.data_as(capi.dp), 13)
+        return out[:n]
+
+    def boundary(self, which):
+        out = np.zeros(self.state_number)
+        capi.check(capi.load().mab_model_boundary(self._h, which, out.ctypes.data_as(capi.dp)))
+        return out
+
+    def emissions(self):
+        m, gx, gy = np.zeros(25), np.zeros(5), np.zeros(5)
+        capi.check(capi.load().mab_model_emissions(self._h, m.ctypes.data_as(capi.dp), gx.ctypes.data_as(capi.dp),
+                                                   gy.ctypes.data_as(capi.dp)))
+        return m, gx, gy
+
+    @property
+    def n_expectations(self):
+        S = self.state_number
+        return S * S + S * 16 + 1
+
+    def __del__(self):
+        try:
+            if self._h:
+                capi.load().mab_model_destroy(self._h)
+                self._h = None
+        except Exception:
+            pass
+
+
+def _ptr(a, typ):
+    return a.ctypes.data_as(typ)
+
+
+class Plan:
+    """Host work plan of one batch (regions, bands, traceback schedule); see csrc/plan.cpp."""
+
+    def __init__(self, handle):
+        self._h = handle
+        self.info = capi.MabPlanInfo()
+        capi.check(capi.load().mab_plan_get_info(handle, C.byref(self.info)))
+
+    @classmethod
+    def from_batch(cls, batch: AlignmentBatch, params: AlignmentParameters, n_threads=0):
+        L = capi.load()
+        p = params.to_c()
+        h = capi.vp()
+        sx = np.ascontiguousarray(batch.seq_x, dtype=np.uint8)
+        sy = np.ascontiguousarray(batch.seq_y, dtype=np.uint8)
+        ox = np.ascontiguousarray(batch.off_x, dtype=np.int64)
+        oy = np.ascontiguousarray(batch.off_y, dtype=np.int64)
+        ops = np.ascontiguousarray(batch.ops, dtype=np.uint8)
+        lens = np.ascontiguousarray(batch.lens, dtype=np.int32)
+        oo = np.ascontiguousarray(batch.off_ops, dtype=np.int64)
+        capi.check(L.mab_plan_from_cigars(C.byref(p), batch.n, _ptr(sx, capi.u8p), _ptr(ox, capi.i64p),
+                                          _ptr(sy, capi.u8p), _ptr(oy, capi.i64p), _ptr(ops, capi.u8p),
+                                          _ptr(lens, capi.i32p), _ptr(oo, capi.i64p), n_threads, C.byref(h)))
+        return cls(h)
+
+    @classmethod
+    def from_anchors(cls, xs, ys, anchors, params: AlignmentParameters, n_threads=0):
+        """xs, ys: list of bytes; anchors: list of (k,2) int arrays (explicit anchors instead of a cigar)."""
+        L = capi.load()
+        b = AlignmentBatch.from_lists(xs, ys, [([], [])] * len(xs))
+        anc = [np.asarray(a, dtype=np.int64).reshape(-1, 2) for a in anchors]
+        off = np.zeros(len(anc) + 1, dtype=np.int64)
+        np.cumsum([len(a) for a in anc], out=off[1:])
+        flat = np.ascontiguousarray(np.concatenate(anc) if anc else np.zeros((0, 2), np.int64))
+        p = params.to_c()
+        h = capi.vp()
+        capi.check(L.mab_plan_from_anchors(C.byref(p), b.n, _ptr(b.seq_x, capi.u8p), _ptr(b.off_x, capi.i64p),
+                                           _ptr(b.seq_y, capi.u8p), _ptr(b.off_y, capi.i64p), _ptr(flat, capi.i64p),
+                                           _ptr(off, capi.i64p), n_threads, C.byref(h)))
+        return cls(h)
+
+    # ---- introspection (tests)
+    def anchors(self, aln):
+        L = capi.load()
+        n = L.mab_plan_anchors(self._h, aln, None, 0)
+        out = np.zeros((max(n, 1), 2), dtype=np.int64)
+        L.mab_plan_anchors(self._h, aln, _ptr(out, capi.i64p), n)
+        return out[:n]
+
+    def regions(self):
+        out = np.zeros((max(self.info.n_regions, 1), 5), dtype=np.int64)
+        n = capi.load().mab_plan_regions(self._h, _ptr(out, capi.i64p), len(out))
+        return out[:n]
+
+    def band(self, region):
+        L = capi.load()
+        n = L.mab_plan_band(self._h, region, None, 0)
+        out = np.zeros((n, 2), dtype=np.int64)
+        L.mab_plan_band(self._h, region, _ptr(out, capi.i64p), n)
+        return out[:, 0].copy(), out[:, 1].copy()
+
+    def tracebacks(self):
+        out = np.zeros((max(self.info.n_tracebacks, 1), 5), dtype=np.int64)
+        n = capi.load().mab_plan_tracebacks(self._h, _ptr(out, capi.i64p), len(out))
+        return out[:n]
+
+    def write_blob(self, dst_ptr, nbytes):
+        capi.check(capi.load().mab_plan_write_blob(self._h, dst_ptr, nbytes))
+
+    def __del__(self):
+        try:
+            if self._h:
+                capi.load().mab_plan_destroy(self._h)
+                self._h = None
+        except Exception:
+            pass
+
+
+@dataclass
+class PosteriorPairs:
+    """CSR result of posterior mode: alignment i owns rows offsets[i]:offsets[i+1] of (x, y, p_int), in the order
+    the reference's getAlignedPairsUsingAnchors returns them; p_int = floor(min(p,1) * 1e7)."""
+    offsets: np.ndarray
+    x: np.ndarray
+    y: np.ndarray
+    p: np.ndarray
+
+    def pairs(self, i):
+        s = slice(self.offsets[i], self.offsets[i + 1])
+        return np.stack([self.p[s].astype(np.int64), self.x[s].astype(np.int64), self.y[s].astype(np.int64)], axis=1)
+
+
+def _torch():
+    import torch
+    return torch
+
+
+def require_cuda():
+    torch = _torch()
+    if not torch.cuda.is_available() or capi.load().mab_device_count() == 0:
+        raise RuntimeError("marginalign-trna_b200: no CUDA device; the pair-HMM path has no CPU fallback")
+    return torch
+
+
+class DevicePlan:
+    """A plan whose blob is resident in HBM, plus its scratch workspace."""
+
+    def __init__(self, plan: Plan, device, expectations=False, stream=None):
+        torch = require_cuda()
+        self.plan = plan
+        self.device = device
+        nb = plan.info.blob_bytes
+        self.h_blob = torch.empty(nb, dtype=torch.uint8, pin_memory=True)
+        plan.write_blob(self.h_blob.data_ptr(), nb)
+        self.d_blob = torch.empty(nb, dtype=torch.uint8, device=device)
+        with torch.cuda.stream(stream) if stream is not None else _null():
+            self.d_blob.copy_(self.h_blob, non_blocking=True)
+        ws = plan.info.workspace_bytes_expectations if expectations else plan.info.workspace_bytes_posteriors
+        self.ws_bytes = int(ws)
+        self.d_ws = torch.empty(self.ws_bytes + 256, dtype=torch.uint8, device=device)
+        # 256-byte aligned view of the workspace
+        self.ws_ptr = (self.d_ws.data_ptr() + 255) & ~255
+        self.h2d_bytes = nb
+
+
+class _null:
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        return False
+
+
+class PairHmmEngine:
+    """Runs batches on one GPU.  `max_cells` bounds the number of DP cells resident at once (80 B of HBM each)."""
+
+    def __init__(self, device=None, max_cells=200_000_000, plan_threads=0):
+        torch = require_cuda()
+        self.torch = torch
+        self.device = torch.device(device if device is not None else "cuda:%d" % torch.cuda.current_device())
+        self.max_cells = int(max_cells)
+        self.plan_threads = plan_threads
+        self.last_stats = {}
+
+    # ---------------------------------------------------------------- chunking
+    def _chunks(self, batch, params):
+        # cells ~ diagonals x band width; band width ~ expansion + 2 near anchors (exact count comes from the plan)
+        est = ((batch.off_x[1:] - batch.off_x[:-1]) + (batch.off_y[1:] - batch.off_y[:-1]) + 1) * (
+            params.diagonal_expansion + 4)
+        bounds, acc, start = [], 0, 0
+        for i, c in enumerate(est):
+            if acc + c > self.max_cells and i > start:
+                bounds.append((start, i))
+                start, acc = i, 0
+            acc += int(c)
+        bounds.append((start, batch.n))
+        return bounds
+
+    def _stream_ptr(self):
+        return C.c_void_p(self.torch.cuda.current_stream(self.device).cuda_stream)
+
+    # ---------------------------------------------------------------- posteriors
+    def posteriors_device(self, model, dplan):
+        """Device-resident half of posterior mode: returns (offsets, x, y, p) as torch device tensors."""
+        torch, L = self.torch, capi.load()
+        n = dplan.plan.info.n_alignments
+        d_off = torch.empty(n + 1, dtype=torch.int64, device=self.device)
+        d_np = torch.empty(1, dtype=torch.int64, device=self.device)
+        capi.check(L.mab_posteriors_compute(model._h, dplan.plan._h, dplan.d_blob.data_ptr(), dplan.ws_ptr,
+                                            dplan.ws_bytes, d_off.data_ptr(), d_np.data_ptr(), self._stream_ptr()))
+        total = int(d_np.item())  # one sync: the output size is data dependent
+        d_x = torch.empty(total, dtype=torch.int32, device=self.device)
+        d_y = torch.empty(total, dtype=torch.int32, device=self.device)
+        d_p = torch.empty(total, dtype=torch.int32, device=self.device)
+        capi.check(L.mab_posteriors_emit(dplan.plan._h, dplan.d_blob.data_ptr(), dplan.ws_ptr, dplan.ws_bytes,
+                                         d_x.data_ptr(), d_y.data_ptr(), d_p.data_ptr(), total, self._stream_ptr()))
+        return d_off, d_x, d_y, d_p
+
+    def get_aligned_pairs_using_anchors(self, model, batch, params=None):
+        """Posterior match probabilities of every alignment of `batch` (host in, host out)."""
+        params = params or AlignmentParameters()
+        torch = self.torch
+        offs, xs, ys, ps = [np.zeros(1, dtype=np.int64)], [], [], []
+        stats = dict(cells=0, regions=0, diagonals=0, h2d_bytes=0, d2h_bytes=0, chunks=0)
+        chunks = self._chunks(batch, params)
+        with torch.cuda.device(self.device), ThreadPoolExecutor(1) as pool:
+            def make(bounds):
+                sub = batch if bounds == (0, batch.n) else batch.subset(np.arange(bounds[0], bounds[1]))
+                return Plan.from_batch(sub, params, self.plan_threads)
+            fut = pool.submit(make, chunks[0])
+            for ci in range(len(chunks)):
+                plan = fut.result()
+                if ci + 1 < len(chunks):
+                    fut = pool.submit(make, chunks[ci + 1])  # plan the next chunk while the GPU works on this one
+                dplan = DevicePlan(plan, self.device)
+                d_off, d_x, d_y, d_p = self.posteriors_device(model, dplan)
+                off = d_off.cpu().numpy()
+                offs.append(off[1:] + offs[-1][-1])
+                xs.append(d_x.cpu().numpy())
+                ys.append(d_y.cpu().numpy())
+                ps.append(d_p.cpu().numpy())
+                stats["cells"] += plan.info.n_cells
+                stats["regions"] += plan.info.n_regions
+                stats["diagonals"] += plan.info.n_diagonals
+                stats["h2d_bytes"] += dplan.h2d_bytes
+                stats["d2h_bytes"] += off.nbytes + 3 * xs[-1].nbytes
+                stats["chunks"] += 1
+                del dplan
+        self.last_stats = stats
+        return PosteriorPairs(np.concatenate(offs), np.concatenate(xs), np.concatenate(ys), np.concatenate(ps))
+
+    # ---------------------------------------------------------------- expectations
+    def expectations_device(self, model, dplan, d_out):
+        capi.check(capi.load().mab_expectations(model._h, dplan.plan._h, dplan.d_blob.data_ptr(), dplan.ws_ptr,
+                                                dplan.ws_bytes, d_out.data_ptr(), self._stream_ptr()))
+
+    def get_expectations_using_anchors(self, model, batch, params=None, pseudo_count=1e-12, as_hmm=False):
+        """EM expectations summed over the batch: (transitions[S*S], emissions[S*16], likelihood).
+
+        Starts from hmm_constructEmpty(1e-12) like cPecanRealign.c:531 (pseudo-count on transitions and emissions,
+        likelihood 0)."""
+        params = params or AlignmentParameters()
+        torch = self.torch
+        S = model.state_number
+        init = np.full(model.n_expectations, pseudo_count)
+        init[-1] = 0.0
+        stats = dict(cells=0, regions=0, diagonals=0, h2d_bytes=0, d2h_bytes=0, chunks=0)
+        chunks = self._chunks(batch, params)
+        with torch.cuda.device(self.device), ThreadPoolExecutor(1) as pool:
+            d_out = torch.from_numpy(init).to(self.device)
+
+            def make(bounds):
+                sub = batch if bounds == (0, batch.n) else batch.subset(np.arange(bounds[0], bounds[1]))
+                return Plan.from_batch(sub, params, self.plan_threads)
+            fut = pool.submit(make, chunks[0])
+            for ci in range(len(chunks)):
+                plan = fut.result()
+                if ci + 1 < len(chunks):
+                    fut = pool.submit(make, chunks[ci + 1])
+                dplan = DevicePlan(plan, self.device, expectations=True)
+                self.expectations_device(model, dplan, d_out)
+                torch.cuda.current_stream(self.device).synchronize()
+                stats["cells"] += plan.info.n_cells
+                stats["regions"] += plan.info.n_regions
+                stats["diagonals"] += plan.info.n_diagonals
+                stats["h2d_bytes"] += dplan.h2d_bytes
+                stats["chunks"] += 1
+                del dplan
+            out = d_out.cpu().numpy()
+            stats["d2h_bytes"] = out.nbytes
+        self.last_stats = stats
+        T, E, lik = out[:S * S].copy(), out[S * S:S * S + S * 16].copy(), float(out[-1])
+        if as_hmm:
+            h = Hmm(model.type)
+            h.transitions, h.emissions, h.likelihood = T, E, lik
+            return h
+        return T, E, lik

@@ -1,0 +1,233 @@
+"""Parity of the CUDA path (through the C ABI) against the reference.
+
+Bars (BASELINE.json north_star): posteriors and expectations within 1e-5 relative; aligned-pair sets identical
+except for pairs whose posterior lies within tolerance of the threshold.  What we actually assert is tighter:
+  * forward / backward / total-probability values: bit-identical to the oracle by construction, so
+  * p_int differs from the reference by at most 1 unit of 1e-7 (CUDA exp vs glibc exp, last-ulp differences), and a
+    pair may appear/disappear only when its probability is within 1e-7 of the threshold;
+  * expectations: relative error <= 1e-9 on every entry (summation order differs), the spec allows 1e-5.
+"""
+import json
+import os
+
+import numpy as np
+import pytest
+
+import marginalign_trna_b200 as mab
+from conftest import GOLDEN, oracle_anchors, oracle_model, oracle_params
+from oracle import pyoracle as po
+from test_host_plan import _params
+
+pytestmark = pytest.mark.gpu
+
+P_INT_TOL = 1          # units of 1e-7
+EXP_RTOL = 1e-9        # spec: 1e-5
+
+
+@pytest.fixture(scope="module")
+def engine():
+    return mab.PairHmmEngine()
+
+
+def gpu_model(spec):
+    return mab.PairHmmModel.default(0) if spec is None else mab.PairHmmModel.from_arrays(*spec)
+
+
+def assert_pairs_match(got, want, threshold, ctx):
+    """got/want rows (p_int, x, y) in list order."""
+    if len(got) == len(want) and np.array_equal(got[:, 1:], want[:, 1:]):
+        assert np.abs(got[:, 0] - want[:, 0]).max(initial=0) <= P_INT_TOL, ctx
+        return
+    # tolerate pairs sitting on the threshold (within one p_int unit)
+    thr = int(np.floor(threshold * 1e7))
+    gd = {(int(x), int(y)): int(p) for p, x, y in got}
+    wd = {(int(x), int(y)): int(p) for p, x, y in want}
+    for k in set(gd) ^ set(wd):
+        p = gd.get(k, wd.get(k))
+        assert abs(p - thr) <= P_INT_TOL, (ctx, k, p)
+    for k in set(gd) & set(wd):
+        assert abs(gd[k] - wd[k]) <= P_INT_TOL, (ctx, k)
+    # order of the common pairs is the reference's
+    common = set(gd) & set(wd)
+    assert [tuple(r[1:]) for r in got.tolist() if tuple(r[1:]) in common] == \
+           [tuple(r[1:]) for r in want.tolist() if tuple(r[1:]) in common], ctx
+
+
+def assert_exp_match(got, want, ctx, rtol=EXP_RTOL):
+    got, want = np.asarray(got), np.asarray(want)
+    assert got.shape == want.shape, ctx
+    scale = np.maximum(np.abs(want), 1e-300)
+    err = np.abs(got - want) / scale
+    # entries that only hold the 1e-12 pseudo-count are exact
+    assert err.max() <= rtol, (ctx, int(err.argmax()), got[err.argmax()], want[err.argmax()])
+
+
+def batch_for_case(c):
+    return mab.AlignmentBatch.from_lists([c["x"]], [c["y"]], [(c["ops"], c["lens"])])
+
+
+def run_case_gpu(engine, c, model):
+    P = _params(c["params"])
+    if "anchors" in c:
+        # explicit anchors go through mab_plan_from_anchors
+        plan = mab.Plan.from_anchors([c["x"]], [c["y"]], [c["anchors"]], P)
+        dplan = mab.DevicePlan(plan, engine.device)
+        d_off, d_x, d_y, d_p = engine.posteriors_device(model, dplan)
+        pairs = np.stack([d_p.cpu().numpy(), d_x.cpu().numpy(), d_y.cpu().numpy()], axis=1).astype(np.int64)
+        import torch
+        init = np.full(model.n_expectations, 1e-12)
+        init[-1] = 0
+        d_out = torch.from_numpy(init).to(engine.device)
+        dplan2 = mab.DevicePlan(plan, engine.device, expectations=True)
+        engine.expectations_device(model, dplan2, d_out)
+        return pairs, d_out.cpu().numpy()
+    b = batch_for_case(c)
+    res = engine.get_aligned_pairs_using_anchors(model, b, P)
+    T, E, lik = engine.get_expectations_using_anchors(model, b, P)
+    return res.pairs(0), np.concatenate([T, E, [lik]])
+
+
+def test_golden_cases_against_reference_outputs(engine, golden):
+    """Every golden case (fixture reads, KAT example, all four model types, N/lower-case symbols, ragged and
+    non-ragged ends, multi-traceback, sparse/no anchors, splits, empty inputs) vs the reference C code's outputs."""
+    for c in golden.cases:
+        model = gpu_model(golden.model_arrays(c["model"]))
+        pairs, exp = run_case_gpu(engine, c, model)
+        assert_pairs_match(pairs, golden.pairs(c["name"]), c["params"]["threshold"], c["name"])
+        assert_exp_match(exp, golden.exp(c["name"]), c["name"])
+
+
+def test_dp_matrices_bit_identical_to_reference_totals(engine, golden):
+    """The likelihood entry is a plain sum of the per-diagonal total probabilities, which depend on every forward and
+    backward cell: with bit-identical DP values it matches the reference to the last few ulps of the sum."""
+    for name in ("fixture0_realign", "multi_tb", "trna_rand5sym_0", "trna_three_asym_1"):
+        c = next(k for k in golden.cases if k["name"] == name)
+        model = gpu_model(golden.model_arrays(c["model"]))
+        _, exp = run_case_gpu(engine, c, model)
+        want = golden.exp(name)[-1]
+        assert abs(exp[-1] - want) <= 1e-13 * abs(want), (name, exp[-1], want)
+
+
+def test_batched_trna_reads_against_oracle(engine, golden):
+    """A batch of 300 synthetic tRNA-length reads in ONE launch vs the oracle read by read (5- and 3-state)."""
+    b = mab.synth.make_trna_batch(300, seed=99)
+    P = mab.AlignmentParameters()
+    oP = po.make_params(expansion=10, split=3000 ** 2)
+    for key in ("fixture5asym", "three_asym"):
+        spec = golden.model_arrays(key)
+        model, om = gpu_model(spec), oracle_model(po, spec)
+        res = engine.get_aligned_pairs_using_anchors(model, b, P)
+        T, E, lik = engine.get_expectations_using_anchors(model, b, P)
+        S = om.S
+        oT, oE, olik = np.full(S * S, 1e-12), np.full(S * 16, 1e-12), 0.0
+        for i in range(b.n):
+            anc = po.anchors_from_cigar(*b.cigar(i), b.x(i), b.y(i))
+            want = po.aligned_pairs(om, b.x(i), b.y(i), anc, oP)
+            assert_pairs_match(res.pairs(i), want, 0.01, (key, i))
+            oT, oE, olik = po.expectations(om, b.x(i), b.y(i), anc, oP, T=oT, E=oE, lik=olik)
+        assert_exp_match(np.concatenate([T, E, [lik]]), np.concatenate([oT, oE, [olik]]), key)
+
+
+def test_bigmutations_reads_against_reference_digests(engine):
+    """All 30 reads of the reference's inputBigMutations fixture (294-7214 nt), marginCaller parameters
+    (expansion 10, split 100) for posteriors and EM parameters (split 300) for expectations."""
+    with open(os.path.join(GOLDEN, "bigmutations_digest.json")) as fh:
+        dig = json.load(fh)
+    with open(os.path.join(GOLDEN, "bigmutations_alignments.json")) as fh:
+        alns = json.load(fh)
+    model = mab.PairHmmModel.from_file(os.path.join(GOLDEN, "input_model.hmm"))
+    om = po.model_from_hmm(1, mab.Hmm.loadHmm(os.path.join(GOLDEN, "input_model.hmm")).transitions,
+                           mab.Hmm.loadHmm(os.path.join(GOLDEN, "input_model.hmm")).emissions)
+    b = mab.AlignmentBatch.from_lists([a["x"] for a in alns], [a["y"] for a in alns],
+                                      [(a["ops"], a["lens"]) for a in alns])
+    res = engine.get_aligned_pairs_using_anchors(model, b, mab.AlignmentParameters(split_matrix_bigger_than=100))
+    for i, d in enumerate(dig):
+        got = res.pairs(i)
+        assert abs(len(got) - d["n_pairs"]) <= 2, (i, len(got), d["n_pairs"])
+        assert abs(int(got[:, 0].sum()) - d["p_sum"]) <= len(got) + 2 * 100000, i
+        if i < 6:  # full comparison against the oracle for a few reads
+            anc = po.anchors_from_cigar(*b.cigar(i), b.x(i), b.y(i))
+            want = po.aligned_pairs(om, b.x(i), b.y(i), anc, po.make_params(expansion=10, split=100 ** 2))
+            assert_pairs_match(got, want, 0.01, i)
+    # expectations: one read at a time against the stored reference vectors, then the whole batch against their sum
+    Pem = mab.AlignmentParameters(split_matrix_bigger_than=300)
+    total = np.zeros(106)
+    for i, d in enumerate(dig):
+        want = np.array(d["exp"])
+        total += want - np.concatenate([np.full(105, 1e-12), [0.0]])
+        if i % 5 == 0:
+            T, E, lik = engine.get_expectations_using_anchors(model, b.subset([i]), Pem)
+            assert_exp_match(np.concatenate([T, E, [lik]]), want, ("exp", i))
+    T, E, lik = engine.get_expectations_using_anchors(model, b, Pem)
+    assert_exp_match(np.concatenate([T, E, [lik]]), total + np.concatenate([np.full(105, 1e-12), [0.0]]), "batch",
+                     rtol=1e-8)
+
+
+def test_chunking_does_not_change_results(golden):
+    b = mab.synth.make_trna_batch(200, seed=5)
+    model = gpu_model(golden.model_arrays("fixture5asym"))
+    one = mab.PairHmmEngine(max_cells=10 ** 9)
+    many = mab.PairHmmEngine(max_cells=50_000)
+    r1 = one.get_aligned_pairs_using_anchors(model, b)
+    r2 = many.get_aligned_pairs_using_anchors(model, b)
+    assert many.last_stats["chunks"] > 3 and one.last_stats["chunks"] == 1
+    for a in ("offsets", "x", "y", "p"):
+        assert np.array_equal(getattr(r1, a), getattr(r2, a)), a
+    e1 = one.get_expectations_using_anchors(model, b)
+    e2 = many.get_expectations_using_anchors(model, b)
+    assert_exp_match(np.concatenate([e1[0], e1[1], [e1[2]]]), np.concatenate([e2[0], e2[1], [e2[2]]]), "chunks",
+                     rtol=1e-11)
+
+
+def test_wide_band_and_long_read(engine, golden):
+    """A 3 kb read with expansion 100 (diagonals up to ~100 cells wide, several chunks of 32 lanes per diagonal and
+    multiple checkpoints)."""
+    b = mab.synth.make_long_batch(2, read_len=3000, genome_len=50_000, seed=8)
+    spec = golden.model_arrays("fixture5asym")
+    model, om = gpu_model(spec), oracle_model(po, spec)
+    P = mab.AlignmentParameters(diagonal_expansion=100, split_matrix_bigger_than=300)
+    oP = po.make_params(expansion=100, split=300 ** 2)
+    res = engine.get_aligned_pairs_using_anchors(model, b, P)
+    T, E, lik = engine.get_expectations_using_anchors(model, b, P)
+    oT, oE, olik = np.full(25, 1e-12), np.full(80, 1e-12), 0.0
+    for i in range(b.n):
+        anc = po.anchors_from_cigar(*b.cigar(i), b.x(i), b.y(i))
+        assert_pairs_match(res.pairs(i), po.aligned_pairs(om, b.x(i), b.y(i), anc, oP), 0.01, i)
+        oT, oE, olik = po.expectations(om, b.x(i), b.y(i), anc, oP, T=oT, E=oE, lik=olik)
+    assert_exp_match(np.concatenate([T, E, [lik]]), np.concatenate([oT, oE, [olik]]), "wide")
+
+
+def test_full_size_properties(engine, golden):
+    """Size-independent properties on a batch too large for the oracle (50k tRNA reads, ~140 M cells):
+    (1) every pair is in range and unique per alignment, 0 < p_int <= 1e7  (the reference's
+        test_getAlignedPairsWithBanding assertions, pairwiseAlignerTest.c:369-404);
+    (2) permuting the batch permutes the result (alignments are independent work items);
+    (3) posterior mass per read position never exceeds 1 by more than the logAdd approximation error;
+    (4) expectations are additive over a partition of the batch."""
+    n = 50_000
+    b = mab.synth.make_trna_batch(n, seed=2024)
+    model = gpu_model(golden.model_arrays("fixture5asym"))
+    res = engine.get_aligned_pairs_using_anchors(model, b)
+    assert engine.last_stats["cells"] > 100_000_000
+    lens_x = (b.off_x[1:] - b.off_x[:-1])
+    lens_y = (b.off_y[1:] - b.off_y[:-1])
+    owner = np.repeat(np.arange(n), np.diff(res.offsets))
+    assert (res.p > 0).all() and (res.p <= 10_000_000).all()
+    assert (res.x >= 0).all() and (res.x < lens_x[owner]).all()
+    assert (res.y >= 0).all() and (res.y < lens_y[owner]).all()
+    key = (owner.astype(np.int64) << 20) | (res.x.astype(np.int64) << 10) | res.y.astype(np.int64)
+    assert len(np.unique(key)) == len(key)
+    mass = np.bincount((owner.astype(np.int64) << 8) | res.y.astype(np.int64), weights=res.p / 1e7)
+    assert mass.max() < 1.01
+    perm = np.random.default_rng(0).permutation(n)[:5000]
+    sub = engine.get_aligned_pairs_using_anchors(model, b.subset(perm))
+    for k in (0, 17, 4999):
+        assert np.array_equal(sub.pairs(k), res.pairs(perm[k]))
+    half = n // 2
+    ea = engine.get_expectations_using_anchors(model, b.subset(np.arange(0, half)), pseudo_count=0.0)
+    eb = engine.get_expectations_using_anchors(model, b.subset(np.arange(half, n)), pseudo_count=0.0)
+    ec = engine.get_expectations_using_anchors(model, b, pseudo_count=0.0)
+    tot = np.concatenate([ea[0] + eb[0], ea[1] + eb[1], [ea[2] + eb[2]]])
+    assert_exp_match(np.concatenate([ec[0], ec[1], [ec[2]]]), tot, "additive", rtol=1e-9)
+    # transitions into match consume one (x,y) pair each: their expected count is bounded by min(lX, lY) summed
+    assert ec[0].reshape(5, 5)[:, 0].sum() <= np.minimum(lens_x, lens_y).sum()

@@ -1,0 +1,146 @@
+"""Host planner (csrc/plan.cpp) and model builder (csrc/model.cpp) against the oracle; C-ABI surface checks.
+No compute calls: this file runs without a GPU."""
+import ctypes as C
+import os
+import re
+
+import numpy as np
+import pytest
+
+import marginalign_trna_b200 as mab
+from conftest import ROOT, oracle_anchors, oracle_model, oracle_params
+from marginalign_trna_b200 import capi
+from oracle import pyoracle as po
+
+
+def _params(p):
+    return mab.AlignmentParameters(threshold=p["threshold"], min_diags_between_traceback=p["min_diags"],
+                                   traceback_diagonals=p["traceback_diagonals"], diagonal_expansion=p["expansion"],
+                                   split_matrix_bigger_than=p["split"], ragged_left=bool(p["ragged_left"]),
+                                   ragged_right=bool(p["ragged_right"]))
+
+
+def plan_for_case(c):
+    P = _params(c["params"])
+    if "anchors" in c:
+        return mab.Plan.from_anchors([c["x"]], [c["y"]], [c["anchors"]], P)
+    return mab.Plan.from_batch(mab.AlignmentBatch.from_lists([c["x"]], [c["y"]], [(c["ops"], c["lens"])]), P)
+
+
+def test_library_exports_every_declared_symbol():
+    hdr = open(os.path.join(ROOT, "include", "margin_b200.h")).read()
+    declared = set(re.findall(r"\b(mab_[a-z0-9_]+)\s*\(", hdr))
+    assert len(declared) >= 25
+    L = capi.load()
+    for name in sorted(declared):
+        assert hasattr(L, name), "libmargin_b200.so does not export %s" % name
+    assert declared == set(capi.SIGNATURES), declared ^ set(capi.SIGNATURES)
+    assert b"margin_b200" in L.mab_version()
+
+
+def test_plan_matches_oracle_geometry(golden):
+    for c in golden.cases:
+        plan = plan_for_case(c)
+        anc = oracle_anchors(po, c)
+        assert np.array_equal(plan.anchors(0), anc), c["name"]
+        p = c["params"]
+        sp = po.split_points(anc, len(c["x"]), len(c["y"]), p["split"] ** 2, p["ragged_left"], p["ragged_right"])
+        sp = sp[(sp[:, 2] - sp[:, 0]) + (sp[:, 3] - sp[:, 1]) > 0] if len(sp) else sp  # empty regions are dropped
+        reg = plan.regions()
+        assert np.array_equal(reg[:, 1:], sp.reshape(-1, 4)), c["name"]
+        cells = 0
+        j = 0
+        for r, (x1, y1, x2, y2) in enumerate(sp.tolist()):
+            sub = []
+            while j < len(anc) and anc[j, 0] + anc[j, 1] < x2 + y2:
+                sub.append([anc[j, 0] - x1, anc[j, 1] - y1])
+                j += 1
+            L, R = po.band(sub, x2 - x1, y2 - y1, p["expansion"])
+            bl, br = plan.band(r)
+            assert np.array_equal(bl, L) and np.array_equal(br, R), (c["name"], r)
+            cells += int(((R - L) // 2 + 1).sum())
+        assert plan.info.n_cells == cells
+        assert cells == po.count_cells(len(c["x"]), len(c["y"]), anc, oracle_params(po, p), p["ragged_left"],
+                                       p["ragged_right"])
+
+
+def test_traceback_schedule():
+    # 2000 diagonals, contiguous anchors, expansion 10: checkpoints at 1000 and 1959 (= 959 + 1000), end at 2000
+    x = "ACGT" * 250
+    plan = mab.Plan.from_anchors([x], [x], [[[i, i] for i in range(1000)]], mab.AlignmentParameters())
+    tb = plan.tracebacks()
+    assert tb.tolist() == [[0, 0, 1000, 959, 0], [0, 959, 1959, 1918, 0], [0, 1918, 2000, 2000, 1]]
+    # posterior diagonals partition 1..D; one total per 10 of them
+    assert plan.info.n_totals == sum(-(-(f - lo) // 10) for _, lo, _, f, _ in tb.tolist())
+
+
+def test_plan_is_thread_count_independent():
+    b = mab.synth.make_trna_batch(3000, seed=3)
+    P = mab.AlignmentParameters()
+    blobs = []
+    for nt in (1, 3, 8):
+        plan = mab.Plan.from_batch(b, P, n_threads=nt)
+        buf = np.zeros(plan.info.blob_bytes, dtype=np.uint8)
+        plan.write_blob(buf.ctypes.data, buf.nbytes)
+        blobs.append(buf)
+    assert np.array_equal(blobs[0], blobs[1]) and np.array_equal(blobs[0], blobs[2])
+
+
+def test_plan_rejects_bad_input():
+    P = mab.AlignmentParameters()
+    with pytest.raises(RuntimeError, match="cigar spans"):
+        mab.Plan.from_batch(mab.AlignmentBatch.from_lists(["ACGT"], ["ACGT"], [([0], [3])]), P)
+    with pytest.raises(RuntimeError, match="runs past"):
+        mab.Plan.from_batch(mab.AlignmentBatch.from_lists(["ACGT"], ["ACGT"], [([0], [9])]), P)
+    with pytest.raises(RuntimeError, match="anchor"):
+        mab.Plan.from_anchors(["ACGT"], ["ACGT"], [[[2, 2], [1, 3]]], P)
+    with pytest.raises(RuntimeError, match="invalid parameters"):
+        mab.Plan.from_anchors(["ACGT"], ["ACGT"], [[]], mab.AlignmentParameters(diagonal_expansion=3))
+    with pytest.raises(RuntimeError, match="invalid parameters"):
+        mab.Plan.from_anchors(["ACGT"], ["ACGT"], [[]], mab.AlignmentParameters(min_diags_between_traceback=41))
+
+
+def test_empty_batch_and_empty_sequences():
+    P = mab.AlignmentParameters()
+    plan = mab.Plan.from_batch(mab.AlignmentBatch.from_lists([], [], []), P)
+    assert plan.info.n_alignments == 0 and plan.info.n_regions == 0 and plan.info.n_cells == 0
+    plan = mab.Plan.from_anchors(["", "ACG"], ["", ""], [[], []], P)
+    assert plan.info.n_alignments == 2 and plan.info.n_regions == 1  # the 0x0 alignment has no diagonals
+
+
+def test_model_block_matches_oracle(golden):
+    for key in golden.models:
+        spec = golden.model_arrays(key)
+        om = oracle_model(po, spec)
+        gm = mab.PairHmmModel.default(0) if spec is None else mab.PairHmmModel.from_arrays(*spec)
+        assert gm.state_number == om.S
+        want = np.array(po.model_transitions(om))
+        assert np.array_equal(gm.transitions(), want), key
+        for which, name in enumerate(["start", "ragged_start", "end", "ragged_end"]):
+            assert np.array_equal(gm.boundary(which), np.array(getattr(om, name)[:om.S])), (key, name)
+        m, gx, gy = gm.emissions()
+        assert np.array_equal(m, np.array(om.em_match[:]))
+        assert np.array_equal(gx, np.array(om.em_gap_x[:])) and np.array_equal(gy, np.array(om.em_gap_y[:]))
+
+
+def test_model_rejects_bad_type():
+    with pytest.raises(RuntimeError):
+        mab.PairHmmModel.from_arrays(1, np.ones(9), np.ones(48))
+    L = capi.load()
+    h = capi.vp()
+    assert L.mab_model_default(7, C.byref(h)) == -1
+    assert b"bad hmm type" in L.mab_last_error()
+
+
+def test_no_cpu_fallback_without_gpu():
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("GPU present")
+    with pytest.raises(RuntimeError, match="no CPU fallback"):
+        mab.PairHmmEngine()
+    # the C ABI itself refuses too
+    L = capi.load()
+    m = mab.PairHmmModel.default(0)
+    plan = mab.Plan.from_anchors(["ACGT"], ["ACGT"], [[]], mab.AlignmentParameters())
+    rc = L.mab_posteriors_compute(m._h, plan._h, 1, 256, 1 << 30, 8, 8, None)
+    assert rc == -5 and b"no CPU fallback" in L.mab_last_error()
