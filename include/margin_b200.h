@@ -144,6 +144,13 @@ int mab_debug_copy_matrices(const mab_plan *plan, const void *d_ws, double *h_fw
         void *stream);
 /* Kernel launches issued by this library on the calling thread since the last reset (bench.py's gpu_launches). */
 int64_t mab_launch_count(int reset);
+/* Per-kernel timing for the roofline report: when enabled every launch is bracketed by CUDA events on its stream.
+ * mab_kernel_times synchronises on the recorded events and returns, per kernel id (0 .. mab_kernel_count()-1), the
+ * summed device time in milliseconds and the number of launches since the last reset. */
+int mab_kernel_timing(int enable);
+int mab_kernel_count(void);
+const char *mab_kernel_name(int kernel);
+int mab_kernel_times(double *ms, int64_t *launches, int reset);
 
 #ifdef __cplusplus
 }

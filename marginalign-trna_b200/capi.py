@@ -63,6 +63,10 @@ SIGNATURES = {
     "mab_expectations": (C.c_int, [vp, vp, vp, vp, C.c_int64, vp, vp]),
     "mab_debug_copy_matrices": (C.c_int, [vp, vp, dp, dp, dp, vp]),
     "mab_launch_count": (C.c_int64, [C.c_int]),
+    "mab_kernel_timing": (C.c_int, [C.c_int]),
+    "mab_kernel_count": (C.c_int, []),
+    "mab_kernel_name": (C.c_char_p, [C.c_int]),
+    "mab_kernel_times": (C.c_int, [dp, i64p, C.c_int]),
 }
 
 _lib = None

@@ -21,6 +21,7 @@
 
 #include <algorithm>
 #include <cstdio>
+#include <vector>
 
 #include "mab_internal.h"
 
@@ -31,6 +32,50 @@
 namespace {
 
 thread_local int64_t g_launches = 0;
+
+// Optional per-kernel timing with CUDA events on the launching stream (bench.py's roofline numbers).
+enum KernelId { K_FORWARD = 0, K_BACKWARD, K_TOTALS, K_POSTERIOR, K_SCAN, K_EMIT, K_EXPECT, K_COUNT };
+const char *const kKernelNames[K_COUNT] = {"k_forward", "k_backward", "k_totals", "k_posterior_count", "k_scan",
+                                           "k_emit", "k_expect"};
+struct TimedLaunch {
+    cudaEvent_t start, stop;
+    int kernel;
+};
+thread_local bool g_timing = false;
+thread_local std::vector<TimedLaunch> g_timed;
+thread_local std::vector<cudaEvent_t> g_event_pool;
+
+cudaEvent_t take_event() {
+    if (!g_event_pool.empty()) {
+        cudaEvent_t e = g_event_pool.back();
+        g_event_pool.pop_back();
+        return e;
+    }
+    cudaEvent_t e;
+    cudaEventCreate(&e);
+    return e;
+}
+
+struct LaunchTimer {  // records an event pair around one kernel launch when timing is on
+    cudaStream_t st;
+    TimedLaunch t;
+    bool on;
+    LaunchTimer(int kernel, cudaStream_t s) : st(s), on(g_timing) {
+        g_launches++;
+        if (on) {
+            t.kernel = kernel;
+            t.start = take_event();
+            t.stop = take_event();
+            cudaEventRecord(t.start, st);
+        }
+    }
+    ~LaunchTimer() {
+        if (on) {
+            cudaEventRecord(t.stop, st);
+            g_timed.push_back(t);
+        }
+    }
+};
 
 // ------------------------------------------------------------------------------------------------ logAdd
 
@@ -290,8 +335,8 @@ k_forward(const __grid_constant__ DevModel model, Blob bl, int n_regions, double
 
 template <int S, bool SMEM_RING>
 __global__ void __launch_bounds__(THREADS_PER_BLOCK)
-k_backward(const __grid_constant__ DevModel model, Blob bl, int n_tbs, double *__restrict__ B, int *counter,
-           int ring_w) {
+k_backward(const __grid_constant__ DevModel model, Blob bl, int n_tbs, double *__restrict__ B,
+           double *__restrict__ edge, int *counter, int ring_w) {
     extern __shared__ double dyn_smem[];
     __shared__ DevModel sm;
     for (int i = threadIdx.x; i < (int) (sizeof(DevModel) / 4); i += blockDim.x)
@@ -323,6 +368,7 @@ k_backward(const __grid_constant__ DevModel model, Blob bl, int n_tbs, double *_
                 for (int s = 0; s < S; s++) c.v[s] = init[s];
                 cell_store<S>(slot + (size_t) j * S, c);
                 if (tb.hi <= tb.from) cell_store<S>(B + (c1 + j) * S, c);
+                else if (tb.hi == tb.from + 1) edge[tb.edge_off + j] = c.v[M];
             }
         }
         __syncwarp();
@@ -351,6 +397,7 @@ k_backward(const __grid_constant__ DevModel model, Blob bl, int n_tbs, double *_
                                                    sm.etp_lower[cX]);
                 cell_store<S>(slot + (size_t) j * S, c);
                 if (keep) cell_store<S>(B + (c0 + j) * S, c);
+                else if (d == tb.from + 1) edge[tb.edge_off + j] = c.v[M];
             }
             __syncwarp();
             L2 = L1;
@@ -369,7 +416,7 @@ k_backward(const __grid_constant__ DevModel model, Blob bl, int n_tbs, double *_
 // is by construction identical to the match state of forward diagonal d+1, which we already have.
 template <int S>
 __global__ void k_totals(Blob bl, int n_totals, const double *__restrict__ F, const double *__restrict__ B,
-                         double *__restrict__ totals) {
+                         const double *__restrict__ edge, double *__restrict__ totals) {
     const int t = blockIdx.x * blockDim.x + threadIdx.x;
     if (t >= n_totals) return;
     const TotalDesc td = bl.totals[t];
@@ -387,7 +434,12 @@ __global__ void k_totals(Blob bl, int n_totals, const double *__restrict__ F, co
     if (td.has_through) {
         const int64_t c2 = dd[td.d + 2].cell_off;
         double through = neg_inf();
-        for (int64_t c = c1; c < c2; c++) through = la(through, __dadd_rn(F[c * S], B[c * S]));
+        if (td.edge_off >= 0) {  // this traceback's own backward diagonal d+1 (see TracebackDesc::edge_off)
+            const double *e = edge + td.edge_off;
+            for (int64_t c = c1; c < c2; c++) through = la(through, __dadd_rn(F[c * S], e[c - c1]));
+        } else {
+            for (int64_t c = c1; c < c2; c++) through = la(through, __dadd_rn(F[c * S], B[c * S]));
+        }
         total = la(total, through);
     }
     totals[t] = total;
@@ -669,7 +721,7 @@ const DeviceInfo &device_info() {
 }
 
 struct Workspace {
-    double *fwd, *bwd, *totals;
+    double *fwd, *bwd, *edge, *totals;
     int32_t *pint;
     int64_t *counts;
     int *counters;
@@ -689,6 +741,7 @@ int carve(const mab_plan *plan, void *d_ws, int64_t ws_bytes, int S, bool expect
     w->counters = (int *) (b + lay.off_counters);
     w->fwd = (double *) (b + lay.off_fwd);
     w->bwd = (double *) (b + lay.off_bwd);
+    w->edge = (double *) (b + lay.off_edge);
     w->totals = (double *) (b + lay.off_totals);
     w->pint = (int32_t *) (b + lay.off_pint);
     w->counts = (int64_t *) (b + lay.off_counts);
@@ -725,15 +778,21 @@ int run_dp(const DevModel &dm, const mab_plan *plan, const Blob &bl, const Works
                                          (int) ring_bytes), "smem attr fwd"))) return rc;
     if ((rc = check(cudaFuncSetAttribute(k_backward<S, true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                          (int) ring_bytes), "smem attr bwd"))) return rc;
-    k_forward<S, true><<<grid_for(h.n_regions, blocks_per_sm, nw), nw * 32, ring_bytes, st>>>(
+    {
+        LaunchTimer lt(K_FORWARD, st);
+        k_forward<S, true><<<grid_for(h.n_regions, blocks_per_sm, nw), nw * 32, ring_bytes, st>>>(
         dm, bl, (int) h.n_regions, w.fwd, w.counters + 0, ring_w);
-    g_launches++;
-    k_backward<S, true><<<grid_for(h.n_tracebacks, blocks_per_sm, nw), nw * 32, ring_bytes, st>>>(
-        dm, bl, (int) h.n_tracebacks, w.bwd, w.counters + 1, ring_w);
-    g_launches++;
+    }
+    {
+        LaunchTimer lt(K_BACKWARD, st);
+        k_backward<S, true><<<grid_for(h.n_tracebacks, blocks_per_sm, nw), nw * 32, ring_bytes, st>>>(
+        dm, bl, (int) h.n_tracebacks, w.bwd, w.edge, w.counters + 1, ring_w);
+    }
     if (h.n_totals > 0) {
-        k_totals<S><<<(int) ((h.n_totals + 127) / 128), 128, 0, st>>>(bl, (int) h.n_totals, w.fwd, w.bwd, w.totals);
-        g_launches++;
+        {
+        LaunchTimer lt(K_TOTALS, st);
+        k_totals<S><<<(int) ((h.n_totals + 127) / 128), 128, 0, st>>>(bl, (int) h.n_totals, w.fwd, w.bwd, w.edge, w.totals);
+    }
     }
     return check(cudaGetLastError(), "dp launch");
 }
@@ -745,11 +804,15 @@ int run_posteriors(const DevModel &dm, const mab_plan *plan, const void *d_blob,
     const Blob bl = blob_view(d_blob, h);
     int rc = run_dp<S>(dm, plan, bl, w, st);
     if (rc) return rc;
-    k_posterior_count<S><<<grid_for(h.n_regions, 8), THREADS_PER_BLOCK, 0, st>>>(
+    {
+        LaunchTimer lt(K_POSTERIOR, st);
+        k_posterior_count<S><<<grid_for(h.n_regions, 8), THREADS_PER_BLOCK, 0, st>>>(
         bl, (int) h.n_regions, w.fwd, w.bwd, w.totals, plan->params.threshold, w.pint, w.counts, w.counters + 2);
-    g_launches++;
-    k_scan<<<1, 1024, 0, st>>>(w.counts, h.n_regions, bl.aln_region, h.n_alignments, d_pair_off, d_n_pairs);
-    g_launches++;
+    }
+    {
+        LaunchTimer lt(K_SCAN, st);
+        k_scan<<<1, 1024, 0, st>>>(w.counts, h.n_regions, bl.aln_region, h.n_alignments, d_pair_off, d_n_pairs);
+    }
     return check(cudaGetLastError(), "posterior launch");
 }
 
@@ -760,9 +823,11 @@ int run_expectations(const DevModel &dm, const mab_plan *plan, const void *d_blo
     const Blob bl = blob_view(d_blob, h);
     int rc = run_dp<S>(dm, plan, bl, w, st);
     if (rc) return rc;
-    k_expect<S><<<grid_for(h.n_regions, 8), THREADS_PER_BLOCK, 0, st>>>(dm, bl, (int) h.n_regions, w.fwd, w.bwd,
+    {
+        LaunchTimer lt(K_EXPECT, st);
+        k_expect<S><<<grid_for(h.n_regions, 8), THREADS_PER_BLOCK, 0, st>>>(dm, bl, (int) h.n_regions, w.fwd, w.bwd,
                                                                         w.totals, d_out, w.counters + 4);
-    g_launches++;
+    }
     return check(cudaGetLastError(), "expectation launch");
 }
 
@@ -785,6 +850,39 @@ extern "C" int mab_device_count(void) {
         return 0;
     }
     return n;
+}
+
+extern "C" int mab_kernel_timing(int enable) {
+    g_timing = enable != 0;
+    return MAB_OK;
+}
+
+extern "C" int mab_kernel_count(void) { return K_COUNT; }
+
+extern "C" const char *mab_kernel_name(int kernel) {
+    return (kernel >= 0 && kernel < K_COUNT) ? kKernelNames[kernel] : "";
+}
+
+extern "C" int mab_kernel_times(double *ms, int64_t *launches, int reset) {
+    for (int k = 0; k < K_COUNT; k++) {
+        if (ms) ms[k] = 0.0;
+        if (launches) launches[k] = 0;
+    }
+    for (const TimedLaunch &t : g_timed) {
+        if (cudaEventSynchronize(t.stop) != cudaSuccess) return check(cudaGetLastError(), "event sync");
+        float v = 0.f;
+        if (cudaEventElapsedTime(&v, t.start, t.stop) != cudaSuccess) return check(cudaGetLastError(), "event time");
+        if (ms) ms[t.kernel] += v;
+        if (launches) launches[t.kernel]++;
+    }
+    if (reset) {
+        for (const TimedLaunch &t : g_timed) {
+            g_event_pool.push_back(t.start);
+            g_event_pool.push_back(t.stop);
+        }
+        g_timed.clear();
+    }
+    return MAB_OK;
 }
 
 extern "C" int64_t mab_launch_count(int reset) {
@@ -829,9 +927,11 @@ extern "C" int mab_posteriors_emit(const mab_plan *plan, const void *d_blob, voi
     if (h.n_regions == 0 || capacity == 0) return MAB_OK;
     cudaStream_t st = (cudaStream_t) stream;
     const Blob bl = blob_view(d_blob, h);
-    k_emit<<<grid_for(h.n_regions, 8), THREADS_PER_BLOCK, 0, st>>>(bl, (int) h.n_regions, w.pint, w.counts, d_x, d_y, d_p,
+    {
+        LaunchTimer lt(K_EMIT, st);
+        k_emit<<<grid_for(h.n_regions, 8), THREADS_PER_BLOCK, 0, st>>>(bl, (int) h.n_regions, w.pint, w.counts, d_x, d_y, d_p,
                                                                    capacity, w.counters + 3);
-    g_launches++;
+    }
     return check(cudaGetLastError(), "emit launch");
 }
 

@@ -60,7 +60,8 @@ struct BlobHeader {  // 256 bytes
     int64_t off_order_bwd;    // int32[n_tracebacks] tracebacks, longest first
     int64_t off_aln_region;   // int64[n_alignments + 1] first region of each alignment
     int64_t blob_bytes;
-    int64_t pad[11];
+    int64_t n_edge_cells;     // cells of the diagonals from+1 of all intermediate tracebacks (see TracebackDesc)
+    int64_t pad[10];
 };
 static_assert(sizeof(BlobHeader) == 256, "BlobHeader must be 256 bytes");
 
@@ -93,7 +94,10 @@ struct TracebackDesc {  // 32 bytes
     int32_t at_end;
     int32_t tot_base;  // global index of this traceback's first total (at diagonal `from`)
     int32_t n_tot;
-    int32_t pad;
+    // Intermediate tracebacks only: the first total (on diagonal `from`) needs THIS traceback's backward match values
+    // on diagonal from+1, which lies in the overlap the reference discards and the next traceback recomputes with
+    // different values.  They are parked in a side buffer at this cell offset (-1 for the final traceback).
+    int32_t edge_off;
 };
 static_assert(sizeof(TracebackDesc) == 32, "TracebackDesc must be 32 bytes");
 
@@ -101,7 +105,7 @@ struct TotalDesc {  // 16 bytes
     int32_t region;
     int32_t d;            // diagonal (region-local xay) the total is evaluated on
     int32_t has_through;  // backward diagonal d+1 is alive (d < hi): add matches that jump over d
-    int32_t pad;
+    int32_t edge_off;     // >= 0: take backward diagonal d+1 from the side buffer at this offset (d == from < hi)
 };
 static_assert(sizeof(TotalDesc) == 16, "TotalDesc must be 16 bytes");
 
@@ -124,7 +128,7 @@ struct mab_plan {
 
 // workspace carving (device scratch); all offsets 256-byte aligned
 struct WorkspaceLayout {
-    int64_t off_fwd, off_bwd, off_totals, off_pint, off_counts, off_counters, off_partials;
+    int64_t off_fwd, off_bwd, off_edge, off_totals, off_pint, off_counts, off_counters, off_partials;
     int64_t total_bytes;
 };
 WorkspaceLayout mab_workspace_layout(const BlobHeader &h, int S, bool expectations);

@@ -40,7 +40,7 @@ struct Piece {  // what one worker thread produces for its range of alignments (
     std::vector<TotalDesc> totals;
     std::vector<int64_t> anchors, anchor_off;  // anchor_off has one entry per alignment (start), local
     std::vector<int64_t> aln_first_region;     // per alignment, local
-    int64_t n_cells = 0, max_width = 0;
+    int64_t n_cells = 0, max_width = 0, n_edge = 0;
     std::string error;
 };
 
@@ -151,6 +151,11 @@ void plan_region(Piece &pc, const mab_params &p, int32_t aln_local, const Split 
         tb.from = (int32_t) (d - (at_end ? 0 : p.traceback_diagonals + 1));
         tb.at_end = at_end;
         tb.tot_base = (int32_t) pc.totals.size();
+        tb.edge_off = -1;
+        if (!at_end) {  // from + 1 <= hi always holds here
+            tb.edge_off = (int32_t) pc.n_edge;
+            pc.n_edge += width(tb.from + 1);
+        }
         // posterior diagonals are from, from-1, ..., lo+1; the total is refreshed on every 10th of them (:712)
         int64_t k = 0;
         for (int64_t q = tb.from; q > tb.lo; q--, k++) {
@@ -159,7 +164,7 @@ void plan_region(Piece &pc, const mab_params &p, int32_t aln_local, const Split 
                 td.region = -1;
                 td.d = (int32_t) q;
                 td.has_through = q < tb.hi ? 1 : 0;  // backward diagonal q+1 still alive (:573-575)
-                td.pad = 0;
+                td.edge_off = (q == tb.from && q < tb.hi) ? tb.edge_off : -1;
                 pc.totals.push_back(td);
             }
             uint32_t tf = (uint32_t) (pc.totals.size() - 1);
@@ -332,17 +337,18 @@ int build_plan(const mab_params *p, const BatchInput &in, int n_threads, mab_pla
     // stitch
     mab_plan *plan = new mab_plan();
     plan->params = *p;
-    int64_t nR = 0, nD = 0, nT = 0, nTot = 0, nC = 0, nA = 0, maxW = 0;
+    int64_t nR = 0, nD = 0, nT = 0, nTot = 0, nC = 0, nA = 0, maxW = 0, nE = 0;
     for (auto &pc : pieces) {
         nR += (int64_t) pc.regions.size();
         nD += (int64_t) pc.diags.size();
         nT += (int64_t) pc.tbs.size();
         nTot += (int64_t) pc.totals.size();
         nC += pc.n_cells;
+        nE += pc.n_edge;
         nA += (int64_t) pc.anchors.size() / 2;
         maxW = std::max(maxW, pc.max_width);
     }
-    if (nR > INT32_MAX || nT > INT32_MAX || nTot >= (int64_t) MAB_DIAG_TOT_MASK) {
+    if (nR > INT32_MAX || nT > INT32_MAX || nE > INT32_MAX || nTot >= (int64_t) MAB_DIAG_TOT_MASK) {
         delete plan;
         mab_set_error("mab_plan: batch too large for 32-bit region/traceback indices; split it");
         return MAB_E_ARG;
@@ -354,7 +360,7 @@ int build_plan(const mab_params *p, const BatchInput &in, int n_threads, mab_pla
     plan->anchors.reserve(2 * nA);
     plan->anchor_off.reserve(in.n + 1);
     plan->aln_region.reserve(in.n + 1);
-    int64_t bR = 0, bD = 0, bT = 0, bTot = 0, bC = 0, bA = 0;
+    int64_t bR = 0, bD = 0, bT = 0, bTot = 0, bC = 0, bA = 0, bE = 0;
     for (int t = 0; t < n_threads; t++) {
         Piece &pc = pieces[t];
         for (auto v : pc.anchor_off) plan->anchor_off.push_back(v + bA);
@@ -379,14 +385,19 @@ int build_plan(const mab_params *p, const BatchInput &in, int n_threads, mab_pla
         }
         for (auto tb : pc.tbs) {
             tb.tot_base += (int32_t) bTot;
+            if (tb.edge_off >= 0) tb.edge_off += (int32_t) bE;
             plan->tbs.push_back(tb);
         }
-        plan->totals.insert(plan->totals.end(), pc.totals.begin(), pc.totals.end());
+        for (auto td : pc.totals) {
+            if (td.edge_off >= 0) td.edge_off += (int32_t) bE;
+            plan->totals.push_back(td);
+        }
         bR += (int64_t) pc.regions.size();
         bD += (int64_t) pc.diags.size();
         bT += (int64_t) pc.tbs.size();
         bTot += (int64_t) pc.totals.size();
         bC += pc.n_cells;
+        bE += pc.n_edge;
         bA += (int64_t) pc.anchors.size() / 2;
         std::vector<DiagDesc>().swap(pc.diags);
     }
@@ -427,6 +438,7 @@ int build_plan(const mab_params *p, const BatchInput &in, int n_threads, mab_pla
     h.n_tracebacks = nT;
     h.n_totals = nTot;
     h.n_anchors = nA;
+    h.n_edge_cells = nE;
     h.max_width = maxW;
     h.len_sym_x = lenX;
     h.len_sym_y = lenY;
@@ -591,6 +603,7 @@ WorkspaceLayout mab_workspace_layout(const BlobHeader &h, int S, bool expectatio
     w.off_counters = place(256);                                  // work-queue counters
     w.off_fwd = place(h.n_cells * S * 8);                         // forward matrix [cell][S]
     w.off_bwd = place(h.n_cells * S * 8);                         // backward matrix [cell][S]
+    w.off_edge = place(h.n_edge_cells * 8);                       // match state of backward diagonals from+1
     w.off_totals = place(h.n_totals * 8);
     w.off_pint = place(expectations ? 0 : h.n_cells * 4);         // per-cell p_int or -1
     w.off_counts = place(expectations ? 0 : (h.n_regions + 1) * 8);  // per-region pair counts -> exclusive scan
