@@ -254,18 +254,24 @@ __device__ __forceinline__ int next_item(int *counter, int lane) {
 }
 
 // ------------------------------------------------------------------------------------------------ forward
+// Generic one-lane-per-cell wavefront (any state count; the 3-state path).  The 5-state path uses wavefront5.cuh.
+// FULL = true : F holds all S states of every cell ([cell][S]) -- expectation mode.
+// FULL = false: posterior mode -- F holds the match state of every cell, FT all states of the cells on diagonals that
+//               carry a total probability (TotalDesc::full_off).
 
-template <int S, bool SMEM_RING>
+#include "wavefront5.cuh"
+
+template <int S, bool FULL>
 __global__ void __launch_bounds__(THREADS_PER_BLOCK)
-k_forward(const __grid_constant__ DevModel model, Blob bl, int n_regions, double *__restrict__ F, int *counter,
-          int ring_w) {
-    extern __shared__ double dyn_smem[];
+k_forward(const __grid_constant__ DevModel model, Blob bl, int n_regions, double *__restrict__ F,
+          double *__restrict__ FT, int *counter, int ring_w) {
+    extern __shared__ __align__(16) unsigned char dyn_smem_raw[];
     __shared__ DevModel sm;
     for (int i = threadIdx.x; i < (int) (sizeof(DevModel) / 4); i += blockDim.x)
         ((int32_t *) &sm)[i] = ((const int32_t *) &model)[i];
     __syncthreads();
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    double *ring = dyn_smem + (size_t) warp * 3 * ring_w * S;
+    double *ring = reinterpret_cast<double *>(dyn_smem_raw) + (size_t) warp * 3 * ring_w * S;
     const double NINF = neg_inf();
 
     for (;;) {
@@ -276,7 +282,7 @@ k_forward(const __grid_constant__ DevModel model, Blob bl, int n_regions, double
         const uint8_t *sx = bl.sym_x + rg.sym_x_off, *sy = bl.sym_y + rg.sym_y_off;
         const int D = rg.lX + rg.lY;
         // diagonal 0: dpDiagonal_initialiseValues with (ragged)startStateProb, pairwiseAligner.c:658-659
-        int64_t c_prev2 = 0, c_prev1 = dd[0].cell_off, c_cur = dd[1].cell_off;
+        int64_t c_prev1 = dd[0].cell_off, c_cur = dd[1].cell_off;
         int L2 = 0, L1 = dd[0].xmyL, w2 = 0, w1 = (int) (c_cur - c_prev1);
         {
             const double *init = (rg.flags & 1) ? sm.ragged_start : sm.start;
@@ -284,13 +290,15 @@ k_forward(const __grid_constant__ DevModel model, Blob bl, int n_regions, double
                 Cell<S> c;
 #pragma unroll
                 for (int s = 0; s < S; s++) c.v[s] = init[s];
-                cell_store<S>(F + (c_prev1 + j) * S, c);
-                if (SMEM_RING) cell_store<S>(ring + (size_t) j * S, c);
+                if (FULL) cell_store<S>(F + (c_prev1 + j) * S, c);
+                else F[c_prev1 + j] = c.v[M];
+                cell_store<S>(ring + (size_t) j * S, c);
             }
         }
         __syncwarp();
         for (int d = 1; d <= D; d++) {
-            const int L = dd[d].xmyL;
+            const DiagDesc cur = dd[d];
+            const int L = cur.xmyL;
             const int64_t c_next = dd[d + 1].cell_off;
             const int w = (int) (c_next - c_cur);
             const int oLo = (L - 1 - L1) >> 1;  // index shift to the lower neighbour (d-1, xmy-1)
@@ -298,30 +306,28 @@ k_forward(const __grid_constant__ DevModel model, Blob bl, int n_regions, double
             double *slot = ring + (size_t) (d % 3) * ring_w * S;
             const double *slot1 = ring + (size_t) ((d + 2) % 3) * ring_w * S;
             const double *slot2 = ring + (size_t) ((d + 1) % 3) * ring_w * S;
+            double *ft = nullptr;
+            if (!FULL && (cur.tot_flags & MAB_DIAG_IS_TOTAL))
+                ft = FT + (int64_t) bl.totals[cur.tot_flags & MAB_DIAG_TOT_MASK].full_off * S;
             for (int j = lane; j < w; j += 32) {
                 const int xmy = L + 2 * j;
                 const int x = (d + xmy) >> 1, y = (d - xmy) >> 1;
                 const int cX = x > 0 ? sx[x - 1] : 4, cY = y > 0 ? sy[y - 1] : 4;
                 const int iLo = j + oLo, iUp = iLo + 1, iMi = j + oMi;
-                Cell<S> lo, mi, up;
-                if (SMEM_RING) {
-                    lo = (iLo >= 0 && iLo < w1) ? cell_load<S>(slot1 + (size_t) iLo * S) : cell_fill<S>(NINF);
-                    up = (iUp >= 0 && iUp < w1) ? cell_load<S>(slot1 + (size_t) iUp * S) : cell_fill<S>(NINF);
-                    mi = (d >= 2 && iMi >= 0 && iMi < w2) ? cell_load<S>(slot2 + (size_t) iMi * S) : cell_fill<S>(NINF);
-                } else {
-                    lo = (iLo >= 0 && iLo < w1) ? cell_load_cg<S>(F + (c_prev1 + iLo) * S) : cell_fill<S>(NINF);
-                    up = (iUp >= 0 && iUp < w1) ? cell_load_cg<S>(F + (c_prev1 + iUp) * S) : cell_fill<S>(NINF);
-                    mi = (d >= 2 && iMi >= 0 && iMi < w2) ? cell_load_cg<S>(F + (c_prev2 + iMi) * S)
-                                                          : cell_fill<S>(NINF);
-                }
+                const Cell<S> lo = (iLo >= 0 && iLo < w1) ? cell_load<S>(slot1 + (size_t) iLo * S) : cell_fill<S>(NINF);
+                const Cell<S> up = (iUp >= 0 && iUp < w1) ? cell_load<S>(slot1 + (size_t) iUp * S) : cell_fill<S>(NINF);
+                const Cell<S> mi = (d >= 2 && iMi >= 0 && iMi < w2) ? cell_load<S>(slot2 + (size_t) iMi * S)
+                                                                     : cell_fill<S>(NINF);
                 const Cell<S> c = forward_cell<S>(lo, mi, up, sm.etp_lower[cX], sm.etp_middle[cX * 5 + cY],
                                                   sm.etp_upper[cY]);
-                cell_store<S>(F + (c_cur + j) * S, c);
-                if (SMEM_RING) cell_store<S>(slot + (size_t) j * S, c);
+                if (FULL) cell_store<S>(F + (c_cur + j) * S, c);
+                else {
+                    F[c_cur + j] = c.v[M];
+                    if (ft != nullptr) cell_store<S>(ft + (int64_t) j * S, c);
+                }
+                cell_store<S>(slot + (size_t) j * S, c);
             }
             __syncwarp();
-            c_prev2 = c_prev1;
-            c_prev1 = c_cur;
             c_cur = c_next;
             L2 = L1;
             L1 = L;
@@ -333,11 +339,11 @@ k_forward(const __grid_constant__ DevModel model, Blob bl, int n_regions, double
 
 // ------------------------------------------------------------------------------------------------ backward
 
-template <int S, bool SMEM_RING>
+template <int S, bool FULL>
 __global__ void __launch_bounds__(THREADS_PER_BLOCK)
 k_backward(const __grid_constant__ DevModel model, Blob bl, int n_tbs, double *__restrict__ B,
-           double *__restrict__ edge, int *counter, int ring_w) {
-    extern __shared__ double dyn_smem[];
+           double *__restrict__ BT, double *__restrict__ edge, int *counter, int ring_w) {
+    extern __shared__ __align__(16) unsigned char dyn_smem_raw[];
     __shared__ DevModel sm;
     for (int i = threadIdx.x; i < (int) (sizeof(DevModel) / 4); i += blockDim.x)
         ((int32_t *) &sm)[i] = ((const int32_t *) &model)[i];
@@ -345,7 +351,7 @@ k_backward(const __grid_constant__ DevModel model, Blob bl, int n_tbs, double *_
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     // The ring is private to the warp: the overlap diagonals (from, hi] that the reference discards must not reach
     // B, where they would collide with the next traceback's cells.
-    double *ring = dyn_smem + (size_t) warp * 3 * ring_w * S;
+    double *ring = reinterpret_cast<double *>(dyn_smem_raw) + (size_t) warp * 3 * ring_w * S;
     const double NINF = neg_inf();
 
     for (;;) {
@@ -362,19 +368,29 @@ k_backward(const __grid_constant__ DevModel model, Blob bl, int n_tbs, double *_
         {
             const double *init = (tb.at_end && (rg.flags & 2)) ? sm.ragged_end : sm.end;
             double *slot = ring + (size_t) (tb.hi % 3) * ring_w * S;
+            const bool keep = tb.hi <= tb.from;
+            double *bt = nullptr;
+            if (!FULL && keep && (dd[tb.hi].tot_flags & MAB_DIAG_IS_TOTAL))
+                bt = BT + (int64_t) bl.totals[dd[tb.hi].tot_flags & MAB_DIAG_TOT_MASK].full_off * S;
             for (int j = lane; j < w1; j += 32) {
                 Cell<S> c;
 #pragma unroll
                 for (int s = 0; s < S; s++) c.v[s] = init[s];
                 cell_store<S>(slot + (size_t) j * S, c);
-                if (tb.hi <= tb.from) cell_store<S>(B + (c1 + j) * S, c);
-                else if (tb.hi == tb.from + 1) edge[tb.edge_off + j] = c.v[M];
+                if (keep) {
+                    if (FULL) cell_store<S>(B + (c1 + j) * S, c);
+                    else {
+                        B[c1 + j] = c.v[M];
+                        if (bt != nullptr) cell_store<S>(bt + (int64_t) j * S, c);
+                    }
+                }
             }
         }
         __syncwarp();
         for (int d = tb.hi - 1; d > tb.lo; d--) {
-            const int L = dd[d].xmyL;
-            const int64_t c0 = dd[d].cell_off;
+            const DiagDesc cur = dd[d];
+            const int L = cur.xmyL;
+            const int64_t c0 = cur.cell_off;
             const int w = (int) (c1 - c0);
             const int oUp = (L - 1 - L1) >> 1;  // (d+1, xmy-1): the cell whose "upper" is T
             const int oMi = (L - L2) >> 1;      // (d+2, xmy)
@@ -383,6 +399,9 @@ k_backward(const __grid_constant__ DevModel model, Blob bl, int n_tbs, double *_
             const double *slot1 = ring + (size_t) ((d + 1) % 3) * ring_w * S;
             const double *slot2 = ring + (size_t) ((d + 2) % 3) * ring_w * S;
             const bool keep = d <= tb.from;
+            double *bt = nullptr;
+            if (!FULL && keep && (cur.tot_flags & MAB_DIAG_IS_TOTAL))
+                bt = BT + (int64_t) bl.totals[cur.tot_flags & MAB_DIAG_TOT_MASK].full_off * S;
             for (int j = lane; j < w; j += 32) {
                 const int xmy = L + 2 * j;
                 const int x = (d + xmy) >> 1, y = (d - xmy) >> 1;
@@ -396,8 +415,15 @@ k_backward(const __grid_constant__ DevModel model, Blob bl, int n_tbs, double *_
                 const Cell<S> c = backward_cell<S>(nMi, nUp, nLo, sm.etp_middle[cX * 5 + cY], sm.etp_upper[cY],
                                                    sm.etp_lower[cX]);
                 cell_store<S>(slot + (size_t) j * S, c);
-                if (keep) cell_store<S>(B + (c0 + j) * S, c);
-                else if (d == tb.from + 1) edge[tb.edge_off + j] = c.v[M];
+                if (keep) {
+                    if (FULL) cell_store<S>(B + (c0 + j) * S, c);
+                    else {
+                        B[c0 + j] = c.v[M];
+                        if (bt != nullptr) cell_store<S>(bt + (int64_t) j * S, c);
+                    }
+                } else if (d == tb.from + 1) {
+                    edge[tb.edge_off + j] = c.v[M];
+                }
             }
             __syncwarp();
             L2 = L1;
@@ -414,8 +440,9 @@ k_backward(const __grid_constant__ DevModel model, Blob bl, int n_tbs, double *_
 // diagonalCalculationTotalProbability (pairwiseAligner.c:566-583).  The "matches that jump over d" term rebuilds, in
 // the reference, a temporary diagonal d+1 holding only the match state reached from forward diagonal d-1; that value
 // is by construction identical to the match state of forward diagonal d+1, which we already have.
-template <int S>
+template <int S, bool FULL>
 __global__ void k_totals(Blob bl, int n_totals, const double *__restrict__ F, const double *__restrict__ B,
+                         const double *__restrict__ FT, const double *__restrict__ BT,
                          const double *__restrict__ edge, double *__restrict__ totals) {
     const int t = blockIdx.x * blockDim.x + threadIdx.x;
     if (t >= n_totals) return;
@@ -423,22 +450,25 @@ __global__ void k_totals(Blob bl, int n_totals, const double *__restrict__ F, co
     const RegionDesc &rg = bl.regions[td.region];
     const DiagDesc *dd = bl.diags + rg.diag_base;
     const int64_t c0 = dd[td.d].cell_off, c1 = dd[td.d + 1].cell_off;
+    // all states of diagonal d: from the full matrices, or from the side arrays in posterior mode
+    const double *f = FULL ? F + c0 * S : FT + (int64_t) td.full_off * S;
+    const double *b = FULL ? B + c0 * S : BT + (int64_t) td.full_off * S;
     double total = neg_inf();
-    for (int64_t c = c0; c < c1; c++) {
-        const double *f = F + c * S, *b = B + c * S;
+    for (int64_t c = 0; c < c1 - c0; c++, f += S, b += S) {
         double cd = __dadd_rn(f[0], b[0]);
 #pragma unroll
         for (int s = 1; s < S; s++) cd = la(cd, __dadd_rn(f[s], b[s]));
         total = la(total, cd);
     }
-    if (td.has_through) {
+    if (td.edge_off != MAB_THROUGH_NONE) {
         const int64_t c2 = dd[td.d + 2].cell_off;
+        constexpr int STRIDE = FULL ? S : 1;  // match state of cell c: F[c*S] or the match plane F[c]
         double through = neg_inf();
         if (td.edge_off >= 0) {  // this traceback's own backward diagonal d+1 (see TracebackDesc::edge_off)
             const double *e = edge + td.edge_off;
-            for (int64_t c = c1; c < c2; c++) through = la(through, __dadd_rn(F[c * S], e[c - c1]));
+            for (int64_t c = c1; c < c2; c++) through = la(through, __dadd_rn(F[c * STRIDE], e[c - c1]));
         } else {
-            for (int64_t c = c1; c < c2; c++) through = la(through, __dadd_rn(F[c * S], B[c * S]));
+            for (int64_t c = c1; c < c2; c++) through = la(through, __dadd_rn(F[c * STRIDE], B[c * STRIDE]));
         }
         total = la(total, through);
     }
@@ -449,7 +479,6 @@ __global__ void k_totals(Blob bl, int n_totals, const double *__restrict__ F, co
 
 // diagonalCalculationPosteriorMatchProbs (pairwiseAligner.c:585-615), one warp per region.  Writes p_int (or -1)
 // per cell and the number of emitted pairs per region.
-template <int S>
 __global__ void __launch_bounds__(THREADS_PER_BLOCK)
 k_posterior_count(Blob bl, int n_regions, const double *__restrict__ F, const double *__restrict__ B,
                   const double *__restrict__ totals, double threshold, int32_t *__restrict__ pint,
@@ -474,7 +503,7 @@ k_posterior_count(Blob bl, int n_regions, const double *__restrict__ F, const do
                 int32_t v = -1;
                 if (x > 0 && y > 0) {
                     const int64_t c = cur.cell_off + j;
-                    double p = exp(__dsub_rn(__dadd_rn(F[c * S], B[c * S]), total));
+                    double p = exp(__dsub_rn(__dadd_rn(F[c], B[c]), total));
                     if (p >= threshold) {
                         if (p > 1.0) p = 1.0;
                         v = (int32_t) floor(__dmul_rn(p, MAB_PROB_1));
@@ -721,7 +750,7 @@ const DeviceInfo &device_info() {
 }
 
 struct Workspace {
-    double *fwd, *bwd, *edge, *totals;
+    double *fwd, *bwd, *fwd_tot, *bwd_tot, *edge, *totals;
     int32_t *pint;
     int64_t *counts;
     int *counters;
@@ -741,6 +770,8 @@ int carve(const mab_plan *plan, void *d_ws, int64_t ws_bytes, int S, bool expect
     w->counters = (int *) (b + lay.off_counters);
     w->fwd = (double *) (b + lay.off_fwd);
     w->bwd = (double *) (b + lay.off_bwd);
+    w->fwd_tot = (double *) (b + lay.off_fwd_tot);
+    w->bwd_tot = (double *) (b + lay.off_bwd_tot);
     w->edge = (double *) (b + lay.off_edge);
     w->totals = (double *) (b + lay.off_totals);
     w->pint = (int32_t *) (b + lay.off_pint);
@@ -755,14 +786,20 @@ int grid_for(int64_t items, int blocks_per_sm, int warps_per_block = WARPS_PER_B
     return (int) (want < 1 ? 1 : (want < cap ? want : cap));
 }
 
-// forward + backward + totals: shared by posterior and expectation mode
-template <int S>
+template <typename K>
+int allow_smem(K kernel, int64_t bytes) {
+    return check(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) bytes), "smem attribute");
+}
+
+// forward + backward + totals: shared by posterior mode (FULL = false) and expectation mode (FULL = true)
+template <int S, bool FULL>
 int run_dp(const DevModel &dm, const mab_plan *plan, const Blob &bl, const Workspace &w, cudaStream_t st) {
     const BlobHeader &h = plan->hdr;
     const DeviceInfo &di = device_info();
-    // shared-memory ring: 3 diagonals x max_width cells x S doubles per warp; fewer warps per block for wide bands
-    const int64_t ring_per_warp = (int64_t) 3 * h.max_width * S * 8;
-    const int64_t budget = (int64_t) di.max_smem_optin - (int64_t) sizeof(DevModel) - 1024;
+    // shared-memory ring per warp: 3 diagonals x (max_width + 2 guard) cells x S doubles; fewer warps per block for
+    // wide bands
+    const int64_t ring_per_warp = (int64_t) 3 * (h.max_width + 2) * S * 8;
+    const int64_t budget = (int64_t) di.max_smem_optin - 8 * 1024;
     const int nw = (int) std::min<int64_t>(WARPS_PER_BLOCK, budget / std::max<int64_t>(1, ring_per_warp));
     if (nw < 1) {
         mab_set_error("band too wide for the shared-memory ring (max width %lld cells); lower diagonalExpansion or "
@@ -771,28 +808,39 @@ int run_dp(const DevModel &dm, const mab_plan *plan, const Blob &bl, const Works
     }
     const int64_t ring_bytes = ring_per_warp * nw;
     const int ring_w = (int) h.max_width;
-    const int blocks_per_sm = (int) std::max<int64_t>(1, std::min<int64_t>(8, (200 * 1024) / (ring_bytes + 4096)));
+    const int blocks_per_sm = (int) std::max<int64_t>(1, std::min<int64_t>(8, (200 * 1024) / (ring_bytes + 8192)));
     int rc;
     if ((rc = check(cudaMemsetAsync(w.counters, 0, 256, st), "memset counters"))) return rc;
-    if ((rc = check(cudaFuncSetAttribute(k_forward<S, true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                         (int) ring_bytes), "smem attr fwd"))) return rc;
-    if ((rc = check(cudaFuncSetAttribute(k_backward<S, true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                         (int) ring_bytes), "smem attr bwd"))) return rc;
-    {
-        LaunchTimer lt(K_FORWARD, st);
-        k_forward<S, true><<<grid_for(h.n_regions, blocks_per_sm, nw), nw * 32, ring_bytes, st>>>(
-        dm, bl, (int) h.n_regions, w.fwd, w.counters + 0, ring_w);
-    }
-    {
-        LaunchTimer lt(K_BACKWARD, st);
-        k_backward<S, true><<<grid_for(h.n_tracebacks, blocks_per_sm, nw), nw * 32, ring_bytes, st>>>(
-        dm, bl, (int) h.n_tracebacks, w.bwd, w.edge, w.counters + 1, ring_w);
+    if (S == 5) {
+        if ((rc = allow_smem(k_forward5<FULL>, ring_bytes)) || (rc = allow_smem(k_backward5<FULL>, ring_bytes))) return rc;
+        {
+            LaunchTimer lt(K_FORWARD, st);
+            k_forward5<FULL><<<grid_for(h.n_regions, blocks_per_sm, nw), nw * 32, ring_bytes, st>>>(
+                dm, bl, (int) h.n_regions, w.fwd, w.fwd_tot, w.counters + 0, ring_w);
+        }
+        {
+            LaunchTimer lt(K_BACKWARD, st);
+            k_backward5<FULL><<<grid_for(h.n_tracebacks, blocks_per_sm, nw), nw * 32, ring_bytes, st>>>(
+                dm, bl, (int) h.n_tracebacks, w.bwd, w.bwd_tot, w.edge, w.counters + 1, ring_w);
+        }
+    } else {
+        if ((rc = allow_smem(k_forward<S, FULL>, ring_bytes)) || (rc = allow_smem(k_backward<S, FULL>, ring_bytes)))
+            return rc;
+        {
+            LaunchTimer lt(K_FORWARD, st);
+            k_forward<S, FULL><<<grid_for(h.n_regions, blocks_per_sm, nw), nw * 32, ring_bytes, st>>>(
+                dm, bl, (int) h.n_regions, w.fwd, w.fwd_tot, w.counters + 0, ring_w);
+        }
+        {
+            LaunchTimer lt(K_BACKWARD, st);
+            k_backward<S, FULL><<<grid_for(h.n_tracebacks, blocks_per_sm, nw), nw * 32, ring_bytes, st>>>(
+                dm, bl, (int) h.n_tracebacks, w.bwd, w.bwd_tot, w.edge, w.counters + 1, ring_w);
+        }
     }
     if (h.n_totals > 0) {
-        {
         LaunchTimer lt(K_TOTALS, st);
-        k_totals<S><<<(int) ((h.n_totals + 127) / 128), 128, 0, st>>>(bl, (int) h.n_totals, w.fwd, w.bwd, w.edge, w.totals);
-    }
+        k_totals<S, FULL><<<(int) ((h.n_totals + 127) / 128), 128, 0, st>>>(bl, (int) h.n_totals, w.fwd, w.bwd, w.fwd_tot,
+                                                                        w.bwd_tot, w.edge, w.totals);
     }
     return check(cudaGetLastError(), "dp launch");
 }
@@ -802,11 +850,11 @@ int run_posteriors(const DevModel &dm, const mab_plan *plan, const void *d_blob,
                    int64_t *d_pair_off, int64_t *d_n_pairs, cudaStream_t st) {
     const BlobHeader &h = plan->hdr;
     const Blob bl = blob_view(d_blob, h);
-    int rc = run_dp<S>(dm, plan, bl, w, st);
+    int rc = run_dp<S, false>(dm, plan, bl, w, st);
     if (rc) return rc;
     {
         LaunchTimer lt(K_POSTERIOR, st);
-        k_posterior_count<S><<<grid_for(h.n_regions, 8), THREADS_PER_BLOCK, 0, st>>>(
+        k_posterior_count<<<grid_for(h.n_regions, 8), THREADS_PER_BLOCK, 0, st>>>(
         bl, (int) h.n_regions, w.fwd, w.bwd, w.totals, plan->params.threshold, w.pint, w.counts, w.counters + 2);
     }
     {
@@ -821,7 +869,7 @@ int run_expectations(const DevModel &dm, const mab_plan *plan, const void *d_blo
                      cudaStream_t st) {
     const BlobHeader &h = plan->hdr;
     const Blob bl = blob_view(d_blob, h);
-    int rc = run_dp<S>(dm, plan, bl, w, st);
+    int rc = run_dp<S, true>(dm, plan, bl, w, st);
     if (rc) return rc;
     {
         LaunchTimer lt(K_EXPECT, st);
@@ -955,9 +1003,10 @@ extern "C" int mab_expectations(const mab_model *m, const mab_plan *plan, const 
 
 extern "C" int mab_debug_copy_matrices(const mab_plan *plan, const void *d_ws, double *h_fwd, double *h_bwd,
                                        double *h_totals, void *stream) {
+    // Expectation-mode layout: forward / backward hold [cell][5-stride] doubles (a 3-state run packs stride 3 at the
+    // start of the same space).  Only meaningful after mab_expectations.
     if (!plan || !d_ws) return MAB_E_ARG;
-    // the workspace is always carved for MAB_MAX_S; a 3-state run still packs its cells with stride 3 at the start
-    const WorkspaceLayout lay = mab_workspace_layout(plan->hdr, MAB_MAX_S, false);
+    const WorkspaceLayout lay = mab_workspace_layout(plan->hdr, MAB_MAX_S, true);
     const uint8_t *b = (const uint8_t *) d_ws;
     cudaStream_t st = (cudaStream_t) stream;
     int rc;

@@ -61,7 +61,8 @@ struct BlobHeader {  // 256 bytes
     int64_t off_aln_region;   // int64[n_alignments + 1] first region of each alignment
     int64_t blob_bytes;
     int64_t n_edge_cells;     // cells of the diagonals from+1 of all intermediate tracebacks (see TracebackDesc)
-    int64_t pad[10];
+    int64_t n_full_cells;     // cells of all diagonals that carry a total (posterior mode keeps all states there)
+    int64_t pad[9];
 };
 static_assert(sizeof(BlobHeader) == 256, "BlobHeader must be 256 bytes");
 
@@ -78,7 +79,8 @@ struct RegionDesc {  // 64 bytes
 static_assert(sizeof(RegionDesc) == 64, "RegionDesc must be 64 bytes");
 
 #define MAB_DIAG_NO_MIDDLE 0x80000000u  // forward diagonal xay-2 was already freed when the reference visits xay
-#define MAB_DIAG_TOT_MASK 0x7fffffffu
+#define MAB_DIAG_IS_TOTAL 0x40000000u   // a total probability is evaluated ON this diagonal (index = its own total)
+#define MAB_DIAG_TOT_MASK 0x3fffffffu
 struct DiagDesc {  // 16 bytes
     int64_t cell_off;   // global index of the first cell of this diagonal
     int32_t xmyL;       // smallest x-y on the diagonal; cell j has x-y = xmyL + 2j
@@ -101,11 +103,13 @@ struct TracebackDesc {  // 32 bytes
 };
 static_assert(sizeof(TracebackDesc) == 32, "TracebackDesc must be 32 bytes");
 
+#define MAB_THROUGH_NONE (-2)   // d == hi: backward diagonal d+1 does not exist, no "jump over d" term
+#define MAB_THROUGH_MATRIX (-1) // take backward diagonal d+1 from the backward matrix
 struct TotalDesc {  // 16 bytes
     int32_t region;
-    int32_t d;            // diagonal (region-local xay) the total is evaluated on
-    int32_t has_through;  // backward diagonal d+1 is alive (d < hi): add matches that jump over d
-    int32_t edge_off;     // >= 0: take backward diagonal d+1 from the side buffer at this offset (d == from < hi)
+    int32_t d;         // diagonal (region-local xay) the total is evaluated on
+    int32_t edge_off;  // >= 0: backward diagonal d+1 comes from the side buffer at this offset (d == from < hi)
+    int32_t full_off;  // posterior mode: first cell of this diagonal inside the all-states side arrays FT / BT
 };
 static_assert(sizeof(TotalDesc) == 16, "TotalDesc must be 16 bytes");
 
@@ -128,7 +132,7 @@ struct mab_plan {
 
 // workspace carving (device scratch); all offsets 256-byte aligned
 struct WorkspaceLayout {
-    int64_t off_fwd, off_bwd, off_edge, off_totals, off_pint, off_counts, off_counters, off_partials;
+    int64_t off_fwd, off_bwd, off_fwd_tot, off_bwd_tot, off_edge, off_totals, off_pint, off_counts, off_counters;
     int64_t total_bytes;
 };
 WorkspaceLayout mab_workspace_layout(const BlobHeader &h, int S, bool expectations);

@@ -40,7 +40,7 @@ struct Piece {  // what one worker thread produces for its range of alignments (
     std::vector<TotalDesc> totals;
     std::vector<int64_t> anchors, anchor_off;  // anchor_off has one entry per alignment (start), local
     std::vector<int64_t> aln_first_region;     // per alignment, local
-    int64_t n_cells = 0, max_width = 0, n_edge = 0;
+    int64_t n_cells = 0, max_width = 0, n_edge = 0, n_full = 0;
     std::string error;
 };
 
@@ -159,15 +159,19 @@ void plan_region(Piece &pc, const mab_params &p, int32_t aln_local, const Split 
         // posterior diagonals are from, from-1, ..., lo+1; the total is refreshed on every 10th of them (:712)
         int64_t k = 0;
         for (int64_t q = tb.from; q > tb.lo; q--, k++) {
-            if (k % 10 == 0) {
+            const bool is_total = k % 10 == 0;
+            if (is_total) {
                 TotalDesc td;
                 td.region = -1;
                 td.d = (int32_t) q;
-                td.has_through = q < tb.hi ? 1 : 0;  // backward diagonal q+1 still alive (:573-575)
-                td.edge_off = (q == tb.from && q < tb.hi) ? tb.edge_off : -1;
+                // backward diagonal q+1 is alive iff q < hi (:573-575); on q == from it is this traceback's own copy
+                td.edge_off = q == tb.hi ? MAB_THROUGH_NONE : (q == tb.from ? tb.edge_off : MAB_THROUGH_MATRIX);
+                td.full_off = (int32_t) pc.n_full;
+                pc.n_full += width(q);
                 pc.totals.push_back(td);
             }
             uint32_t tf = (uint32_t) (pc.totals.size() - 1);
+            if (is_total) tf |= MAB_DIAG_IS_TOTAL;
             // the forward diagonal q-2 has been deleted by the previous traceback when q-2 < lo (:725-727, :737)
             if (q - 2 < tb.lo) tf |= MAB_DIAG_NO_MIDDLE;
             pc.diags[d0 + q].tot_flags = tf;
@@ -337,7 +341,7 @@ int build_plan(const mab_params *p, const BatchInput &in, int n_threads, mab_pla
     // stitch
     mab_plan *plan = new mab_plan();
     plan->params = *p;
-    int64_t nR = 0, nD = 0, nT = 0, nTot = 0, nC = 0, nA = 0, maxW = 0, nE = 0;
+    int64_t nR = 0, nD = 0, nT = 0, nTot = 0, nC = 0, nA = 0, maxW = 0, nE = 0, nF = 0;
     for (auto &pc : pieces) {
         nR += (int64_t) pc.regions.size();
         nD += (int64_t) pc.diags.size();
@@ -345,10 +349,11 @@ int build_plan(const mab_params *p, const BatchInput &in, int n_threads, mab_pla
         nTot += (int64_t) pc.totals.size();
         nC += pc.n_cells;
         nE += pc.n_edge;
+        nF += pc.n_full;
         nA += (int64_t) pc.anchors.size() / 2;
         maxW = std::max(maxW, pc.max_width);
     }
-    if (nR > INT32_MAX || nT > INT32_MAX || nE > INT32_MAX || nTot >= (int64_t) MAB_DIAG_TOT_MASK) {
+    if (nR > INT32_MAX || nT > INT32_MAX || nE > INT32_MAX || nF > INT32_MAX || nTot >= (int64_t) MAB_DIAG_TOT_MASK) {
         delete plan;
         mab_set_error("mab_plan: batch too large for 32-bit region/traceback indices; split it");
         return MAB_E_ARG;
@@ -360,7 +365,7 @@ int build_plan(const mab_params *p, const BatchInput &in, int n_threads, mab_pla
     plan->anchors.reserve(2 * nA);
     plan->anchor_off.reserve(in.n + 1);
     plan->aln_region.reserve(in.n + 1);
-    int64_t bR = 0, bD = 0, bT = 0, bTot = 0, bC = 0, bA = 0, bE = 0;
+    int64_t bR = 0, bD = 0, bT = 0, bTot = 0, bC = 0, bA = 0, bE = 0, bF = 0;
     for (int t = 0; t < n_threads; t++) {
         Piece &pc = pieces[t];
         for (auto v : pc.anchor_off) plan->anchor_off.push_back(v + bA);
@@ -380,7 +385,7 @@ int build_plan(const mab_params *p, const BatchInput &in, int n_threads, mab_pla
         for (auto dd : pc.diags) {
             dd.cell_off += bC;
             const uint32_t idx = dd.tot_flags & MAB_DIAG_TOT_MASK;
-            if (idx != MAB_DIAG_TOT_MASK) dd.tot_flags = (dd.tot_flags & MAB_DIAG_NO_MIDDLE) | (uint32_t) (idx + bTot);
+            if (idx != MAB_DIAG_TOT_MASK) dd.tot_flags = (dd.tot_flags & ~MAB_DIAG_TOT_MASK) | (uint32_t) (idx + bTot);
             plan->diags.push_back(dd);
         }
         for (auto tb : pc.tbs) {
@@ -390,6 +395,7 @@ int build_plan(const mab_params *p, const BatchInput &in, int n_threads, mab_pla
         }
         for (auto td : pc.totals) {
             if (td.edge_off >= 0) td.edge_off += (int32_t) bE;
+            td.full_off += (int32_t) bF;
             plan->totals.push_back(td);
         }
         bR += (int64_t) pc.regions.size();
@@ -398,6 +404,7 @@ int build_plan(const mab_params *p, const BatchInput &in, int n_threads, mab_pla
         bTot += (int64_t) pc.totals.size();
         bC += pc.n_cells;
         bE += pc.n_edge;
+        bF += pc.n_full;
         bA += (int64_t) pc.anchors.size() / 2;
         std::vector<DiagDesc>().swap(pc.diags);
     }
@@ -439,6 +446,7 @@ int build_plan(const mab_params *p, const BatchInput &in, int n_threads, mab_pla
     h.n_totals = nTot;
     h.n_anchors = nA;
     h.n_edge_cells = nE;
+    h.n_full_cells = nF;
     h.max_width = maxW;
     h.len_sym_x = lenX;
     h.len_sym_y = lenY;
@@ -593,6 +601,8 @@ extern "C" int64_t mab_plan_tracebacks(const mab_plan *plan, int64_t *out5, int6
 }
 
 WorkspaceLayout mab_workspace_layout(const BlobHeader &h, int S, bool expectations) {
+    // Posterior mode keeps only what the posteriors read: the match plane of both matrices plus all states on the
+    // diagonals that carry a total (1 in 10).  Expectation mode needs every state of every cell of both matrices.
     WorkspaceLayout w;
     int64_t off = 0;
     auto place = [&](int64_t bytes) {
@@ -600,14 +610,15 @@ WorkspaceLayout mab_workspace_layout(const BlobHeader &h, int S, bool expectatio
         off = (off + bytes + 255) & ~int64_t(255);
         return at;
     };
-    w.off_counters = place(256);                                  // work-queue counters
-    w.off_fwd = place(h.n_cells * S * 8);                         // forward matrix [cell][S]
-    w.off_bwd = place(h.n_cells * S * 8);                         // backward matrix [cell][S]
-    w.off_edge = place(h.n_edge_cells * 8);                       // match state of backward diagonals from+1
+    w.off_counters = place(256);
+    w.off_fwd = place(h.n_cells * 8 * (expectations ? S : 1));
+    w.off_bwd = place(h.n_cells * 8 * (expectations ? S : 1));
+    w.off_fwd_tot = place(expectations ? 0 : h.n_full_cells * S * 8);
+    w.off_bwd_tot = place(expectations ? 0 : h.n_full_cells * S * 8);
+    w.off_edge = place(h.n_edge_cells * 8);
     w.off_totals = place(h.n_totals * 8);
-    w.off_pint = place(expectations ? 0 : h.n_cells * 4);         // per-cell p_int or -1
-    w.off_counts = place(expectations ? 0 : (h.n_regions + 1) * 8);  // per-region pair counts -> exclusive scan
-    w.off_partials = place(expectations ? 8 * 256 : 0);
+    w.off_pint = place(expectations ? 0 : h.n_cells * 4);
+    w.off_counts = place(expectations ? 0 : (h.n_regions + 1) * 8);
     w.total_bytes = off;
     return w;
 }
