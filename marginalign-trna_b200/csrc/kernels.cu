@@ -21,6 +21,7 @@
 
 #include <algorithm>
 #include <cstdio>
+#include <cstdlib>
 #include <vector>
 
 #include "mab_internal.h"
@@ -808,19 +809,22 @@ int run_dp(const DevModel &dm, const mab_plan *plan, const Blob &bl, const Works
     }
     const int64_t ring_bytes = ring_per_warp * nw;
     const int ring_w = (int) h.max_width;
-    const int blocks_per_sm = (int) std::max<int64_t>(1, std::min<int64_t>(8, (200 * 1024) / (ring_bytes + 8192)));
+    const int blocks_per_sm = (int) std::max<int64_t>(1, std::min<int64_t>(12, (200 * 1024) / (ring_bytes + 8192)));
     int rc;
     if ((rc = check(cudaMemsetAsync(w.counters, 0, 256, st), "memset counters"))) return rc;
     if (S == 5) {
-        if ((rc = allow_smem(k_forward5<FULL>, ring_bytes)) || (rc = allow_smem(k_backward5<FULL>, ring_bytes))) return rc;
+        static const bool coef_smem = getenv("MAB_COEF_SMEM") != nullptr;  // experiment switch, see wavefront5.cuh
+        auto kf = coef_smem ? k_forward5<FULL, COEF_SMEM> : k_forward5<FULL, COEF_CONST>;
+        auto kb = coef_smem ? k_backward5<FULL, COEF_SMEM> : k_backward5<FULL, COEF_CONST>;
+        if ((rc = allow_smem(kf, ring_bytes)) || (rc = allow_smem(kb, ring_bytes))) return rc;
         {
             LaunchTimer lt(K_FORWARD, st);
-            k_forward5<FULL><<<grid_for(h.n_regions, blocks_per_sm, nw), nw * 32, ring_bytes, st>>>(
+            kf<<<grid_for(h.n_regions, blocks_per_sm, nw), nw * 32, ring_bytes, st>>>(
                 dm, bl, (int) h.n_regions, w.fwd, w.fwd_tot, w.counters + 0, ring_w);
         }
         {
             LaunchTimer lt(K_BACKWARD, st);
-            k_backward5<FULL><<<grid_for(h.n_tracebacks, blocks_per_sm, nw), nw * 32, ring_bytes, st>>>(
+            kb<<<grid_for(h.n_tracebacks, blocks_per_sm, nw), nw * 32, ring_bytes, st>>>(
                 dm, bl, (int) h.n_tracebacks, w.bwd, w.bwd_tot, w.edge, w.counters + 1, ring_w);
         }
     } else {

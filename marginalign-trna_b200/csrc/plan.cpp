@@ -460,8 +460,9 @@ int build_plan(const mab_params *p, const BatchInput &in, int n_threads, mab_pla
     h.off_diags = place((nD + 1) * (int64_t) sizeof(DiagDesc));
     h.off_tracebacks = place(nT * (int64_t) sizeof(TracebackDesc));
     h.off_totals = place(nTot * (int64_t) sizeof(TotalDesc));
-    h.off_sym_x = place(lenX);
-    h.off_sym_y = place(lenY);
+    // one guard byte before and after each symbol array: the wavefront kernels read X[-1] / X[lX] (and ignore it)
+    h.off_sym_x = place(lenX + 32) + 16;
+    h.off_sym_y = place(lenY + 32) + 16;
     h.off_order_fwd = place(nR * 4);
     h.off_order_bwd = place(nT * 4);
     h.off_aln_region = place((in.n + 1) * 8);
@@ -534,6 +535,10 @@ extern "C" int mab_plan_write_blob(const mab_plan *plan, void *dst, int64_t dst_
     }
     uint8_t *b = (uint8_t *) dst;
     std::memcpy(b, &h, sizeof(h));
+    std::memset(b + h.off_sym_x - 16, 4, 16);
+    std::memset(b + h.off_sym_x + h.len_sym_x, 4, 16);
+    std::memset(b + h.off_sym_y - 16, 4, 16);
+    std::memset(b + h.off_sym_y + h.len_sym_y, 4, 16);
     auto put = [&](int64_t off, const void *src, size_t bytes) {
         if (bytes) std::memcpy(b + off, src, bytes);
     };

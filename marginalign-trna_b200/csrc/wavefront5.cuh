@@ -1,15 +1,18 @@
 // wavefront5.cuh -- the 5-state forward / backward wavefront kernels, "pair-lane" mapping.
 //
-// Why this shape (measured, profiles/r1_v1_ncu_summary.md): the first kernels mapped one lane to one cell and let
-// the compiler branch inside logAdd; ncu showed them issue-bound (85 % issue slots busy, FP64 pipe 30 %) with 9.4
-// of 32 lanes active.  Here
+// Why this shape (measured; profiles/r1_ncu_summary.md has the numbers of each step):
+//   v1  one lane per cell, compiler-branched logAdd: issue-bound (85 % issue slots, FP64 pipe 30 %), 9.4 of 32 lanes
+//       active.
+//   v2  pair-lane mapping + branch-free logAdd with a shared-memory coefficient table: shared-memory data pipe at
+//       97 % (44 % of the load wavefronts were bank-conflict replays on the 64-byte (eP+tP) rows).
+//   v3  (this file) rows padded to 80 B, coefficients moved to the constant bank (off the shared-memory pipe),
+//       rotating ring-slot pointers, per-lane sequence pointers advanced incrementally, one guard store per diagonal.
+//
 //   * every cell of a diagonal is handled by TWO adjacent lanes that execute the SAME instruction stream of four
 //     logAdds: the "match lane" runs the 5-term chain into the match state, the "gap lane" the four independent
 //     2-term sums into the gap states (5-state cellCalculate has exactly 4 + 4 logAdds, stateMachine.c:399-429).
-//     A 12-13 cell diagonal (expansion 10) therefore fills 24-26 lanes and a warp issues 4 logAdds per diagonal
-//     instead of 8;
-//   * logAdd is branch-free: the polynomial piece is picked by three compares and its coefficients come from a
-//     128-byte shared-memory table (2 x LDS.128) instead of select chains over 64-bit immediates;
+//     A 12-13 cell diagonal (expansion 10) fills 24-26 lanes and a warp issues 4 logAdds per diagonal instead of 8;
+//   * logAdd is branch-free: the polynomial piece is picked by three compares;
 //   * out-of-band neighbours are read from -inf guard cells at both ends of every ring slot (index clamp) instead of
 //     per-state selects;
 //   * the (eP + tP) rows are pre-arranged per lane role in shared memory so each lane fetches its 8 addends with
@@ -19,34 +22,41 @@
 #pragma once
 
 // ---- branch-free logAdd ------------------------------------------------------------------------------------------
-// coef: shared-memory table [4 pieces][c3, c2, c1, c0] (16-byte aligned).
-__device__ __forceinline__ double la_bf(double x, double y, const double *coef) {
+// lookup() coefficients of pairwiseAligner.c:239-245 ([piece][c3, c2, c1, c0]); float literals promoted to double.
+__constant__ double c_la_coef[16] = {
+    (double) -0.009350833524763f, (double) 0.130659527668286f, (double) 0.498799810682272f, (double) 0.693203116424741f,
+    (double) -0.014532321752540f, (double) 0.139942324101744f, (double) 0.495635523139337f, (double) 0.692140569840976f,
+    (double) -0.004605031767994f, (double) 0.063427417320019f, (double) 0.695956496475118f, (double) 0.514272634594009f,
+    (double) -0.000458661602210f, (double) 0.009695946122598f, (double) 0.930734667215156f, (double) 0.168037164329057f};
+
+enum CoefMode { COEF_CONST = 0, COEF_SMEM = 1 };
+
+template <int CM>
+__device__ __forceinline__ double la_bf(double x, double y, const double *coef_smem) {
     const bool lt = x < y;
     const double hi = lt ? y : x;
     const double lo = lt ? x : y;
     const double d = __dsub_rn(hi, lo);  // +inf if lo = -inf, NaN if both are -inf: both fail (d < 7.5) below
-    const int piece = (d > 1.00 ? 1 : 0) + (d > 2.50 ? 1 : 0) + (d > 4.50 ? 1 : 0);
-    const double2 c32 = *reinterpret_cast<const double2 *>(coef + piece * 4);
-    const double2 c10 = *reinterpret_cast<const double2 *>(coef + piece * 4 + 2);
-    double r = __dadd_rn(__dmul_rn(c32.x, d), c32.y);
-    r = __dadd_rn(__dmul_rn(r, d), c10.x);
-    r = __dadd_rn(__dmul_rn(r, d), c10.y);
+    const int piece = (d > 1.00 ? 4 : 0) + (d > 2.50 ? 4 : 0) + (d > 4.50 ? 4 : 0);
+    double c3, c2, c1, c0;
+    if (CM == COEF_CONST) {
+        c3 = c_la_coef[piece];
+        c2 = c_la_coef[piece + 1];
+        c1 = c_la_coef[piece + 2];
+        c0 = c_la_coef[piece + 3];
+    } else {
+        const double2 c32 = *reinterpret_cast<const double2 *>(coef_smem + piece);
+        const double2 c10 = *reinterpret_cast<const double2 *>(coef_smem + piece + 2);
+        c3 = c32.x;
+        c2 = c32.y;
+        c1 = c10.x;
+        c0 = c10.y;
+    }
+    double r = __dadd_rn(__dmul_rn(c3, d), c2);
+    r = __dadd_rn(__dmul_rn(r, d), c1);
+    r = __dadd_rn(__dmul_rn(r, d), c0);
     r = __dadd_rn(r, lo);
     return (d < 7.5) ? r : hi;
-}
-
-__device__ __forceinline__ void fill_logadd_coefficients(double *coef, int tid) {
-    // float-suffixed literals of lookup(), pairwiseAligner.c:239-245, promoted to double
-    if (tid == 0) {
-        coef[0] = (double) -0.009350833524763f; coef[1] = (double) 0.130659527668286f;
-        coef[2] = (double) 0.498799810682272f;  coef[3] = (double) 0.693203116424741f;
-        coef[4] = (double) -0.014532321752540f; coef[5] = (double) 0.139942324101744f;
-        coef[6] = (double) 0.495635523139337f;  coef[7] = (double) 0.692140569840976f;
-        coef[8] = (double) -0.004605031767994f; coef[9] = (double) 0.063427417320019f;
-        coef[10] = (double) 0.695956496475118f; coef[11] = (double) 0.514272634594009f;
-        coef[12] = (double) -0.000458661602210f; coef[13] = (double) 0.009695946122598f;
-        coef[14] = (double) 0.930734667215156f; coef[15] = (double) 0.168037164329057f;
-    }
 }
 
 // Four logAdds, same instruction stream for both lane roles.  Slots t1..t8 hold the addends.
@@ -55,103 +65,118 @@ __device__ __forceinline__ void fill_logadd_coefficients(double *coef, int tid) 
 struct Quad {
     double r1, r2, r3, r4;
 };
+template <int CM>
 __device__ __forceinline__ Quad four_logadds(bool chain, double t1, double t2, double t3, double t4, double t5, double t6,
                                              double t7, double t8, const double *coef) {
     Quad q;
-    q.r1 = la_bf(t1, t2, coef);
-    q.r2 = la_bf(chain ? q.r1 : t3, t4, coef);
-    q.r3 = la_bf(chain ? q.r2 : t5, t6, coef);
-    q.r4 = la_bf(chain ? q.r3 : t7, t8, coef);
+    q.r1 = la_bf<CM>(t1, t2, coef);
+    q.r2 = la_bf<CM>(chain ? q.r1 : t3, t4, coef);
+    q.r3 = la_bf<CM>(chain ? q.r2 : t5, t6, coef);
+    q.r4 = la_bf<CM>(chain ? q.r3 : t7, t8, coef);
     return q;
 }
 
-#define RING_CELL_BYTES 40  // 5 doubles per cell, [cell][state]
+#define ETP_ROW 10  // doubles per (eP+tP) row: 8 used + 2 pad.  With 16-byte accesses a row then lands on bank group
+                    // (5 * row) mod 8; the unpadded 64-byte stride put every row on group 0 or 4 (4-way conflicts).
 
 struct Wave5Shared {
     double coef[16];
-    double etp[2][25][8];  // [lane role][cX*5+cY][slot]
-    double boundary[4][5]; // start, ragged_start, end, ragged_end
+    double etp[2][25][ETP_ROW];  // [lane role][cX*5+cY][slot]
+    double boundary[4][5];       // start, ragged_start, end, ragged_end
 };
 
 // Forward tables.  Match lane: t1 = mi.M+eM0, t2 = mi.SX+eM1, t4 = mi.SY+eM2, t6 = mi.LX+eM3, t8 = mi.LY+eM4.
 // Gap lane:   t1 = lo.M+eL0, t2 = lo.SX+eL1, t3 = lo.M+eL2, t4 = lo.LX+eL3, t5 = up.M+eU0, t6 = up.SY+eU1,
 //             t7 = up.M+eU2, t8 = up.LY+eU3.
-__device__ __forceinline__ void fill_forward_tables(Wave5Shared &sh, const DevModel &m, int tid, int nthreads) {
-    for (int i = tid; i < 2 * 25 * 8; i += nthreads) {
-        const int role = i / 200, code = (i / 8) % 25, slot = i % 8, cX = code / 5, cY = code % 5;
-        double v = 0.0;
-        if (role == 0) {
-            const int map[8] = {0, 1, -1, 2, -1, 3, -1, 4};
-            if (map[slot] >= 0) v = m.etp_middle[code][map[slot]];
-        } else {
-            v = slot < 4 ? m.etp_lower[cX][slot] : m.etp_upper[cY][slot - 4];
+__device__ __forceinline__ double forward_table_entry(const DevModel &m, int role, int code, int slot) {
+    const int cX = code / 5, cY = code % 5;
+    if (role == 0) {
+        switch (slot) {
+            case 0: return m.etp_middle[code][0];
+            case 1: return m.etp_middle[code][1];
+            case 3: return m.etp_middle[code][2];
+            case 5: return m.etp_middle[code][3];
+            case 7: return m.etp_middle[code][4];
+            default: return 0.0;
         }
-        sh.etp[role][code][slot] = v;
     }
+    return slot < 4 ? m.etp_lower[cX][slot] : m.etp_upper[cY][slot - 4];
 }
 
 // Backward tables (gather form, see backward_cell<5>).  code = X[x]*5 + Y[y], the symbols the neighbours consume.
 // Match lane: t1 = nMi.M+eM0, t2 = nUp.SY+eU0, t4 = nUp.LY+eU2, t6 = nLo.SX+eL0, t8 = nLo.LX+eL2.
 // Gap lane:   t1 = nMi.M+eM1, t2 = nLo.SX+eL1 (SX); t3 = nMi.M+eM2, t4 = nUp.SY+eU1 (SY);
 //             t5 = nMi.M+eM3, t6 = nLo.LX+eL3 (LX); t7 = nMi.M+eM4, t8 = nUp.LY+eU3 (LY).
-__device__ __forceinline__ void fill_backward_tables(Wave5Shared &sh, const DevModel &m, int tid, int nthreads) {
-    for (int i = tid; i < 2 * 25 * 8; i += nthreads) {
-        const int role = i / 200, code = (i / 8) % 25, slot = i % 8, cX = code / 5, cY = code % 5;
-        const double *eM = m.etp_middle[code], *eL = m.etp_lower[cX], *eU = m.etp_upper[cY];
-        double v = 0.0;
-        if (role == 0) {
-            const double a[8] = {eM[0], eU[0], 0.0, eU[2], 0.0, eL[0], 0.0, eL[2]};
-            v = a[slot];
-        } else {
-            const double a[8] = {eM[1], eL[1], eM[2], eU[1], eM[3], eL[3], eM[4], eU[3]};
-            v = a[slot];
+__device__ __forceinline__ double backward_table_entry(const DevModel &m, int role, int code, int slot) {
+    const int cX = code / 5, cY = code % 5;
+    const double *eM = m.etp_middle[code], *eL = m.etp_lower[cX], *eU = m.etp_upper[cY];
+    if (role == 0) {
+        switch (slot) {
+            case 0: return eM[0];
+            case 1: return eU[0];
+            case 3: return eU[2];
+            case 5: return eL[0];
+            case 7: return eL[2];
+            default: return 0.0;
         }
-        sh.etp[role][code][slot] = v;
+    }
+    switch (slot) {
+        case 0: return eM[1];
+        case 1: return eL[1];
+        case 2: return eM[2];
+        case 3: return eU[1];
+        case 4: return eM[3];
+        case 5: return eL[3];
+        case 6: return eM[4];
+        default: return eU[3];
     }
 }
 
-__device__ __forceinline__ void fill_boundary(Wave5Shared &sh, const DevModel &m, int tid) {
-    if (tid < 20) {
-        const int which = tid / 5, s = tid % 5;
+template <bool FORWARD>
+__device__ __forceinline__ void fill_wave5_shared(Wave5Shared &sh, const DevModel &m, int tid, int nthreads) {
+    for (int i = tid; i < 16; i += nthreads) sh.coef[i] = c_la_coef[i];
+    for (int i = tid; i < 2 * 25 * 8; i += nthreads) {
+        const int role = i / 200, code = (i / 8) % 25, slot = i % 8;
+        sh.etp[role][code][slot] = FORWARD ? forward_table_entry(m, role, code, slot)
+                                           : backward_table_entry(m, role, code, slot);
+    }
+    for (int i = tid; i < 20; i += nthreads) {
+        const int which = i / 5, s = i % 5;
         const double *src = which == 0 ? m.start : which == 1 ? m.ragged_start : which == 2 ? m.end : m.ragged_end;
         sh.boundary[which][s] = src[s];
     }
 }
 
 // One ring slot = (ring_w + 2) cells: position 0 and position w+1 are -inf guards, cell i lives at position i+1.
+// Position 0 is written once per warp (nothing else ever stores there); position w+1 after every diagonal.
 __device__ __forceinline__ int clamp_pos(int i, int w) {  // cell index -> ring position, out-of-band -> a guard
     return min(max(i, -1), w) + 1;
 }
 
-__device__ __forceinline__ void write_guards(double *slot, int w, int lane) {
-    // lanes 0..4 write the low guard, lanes 5..9 the high guard
-    if (lane < 10) {
-        const int s = lane < 5 ? lane : lane - 5;
-        const int pos = lane < 5 ? 0 : w + 1;
-        slot[pos * 5 + s] = neg_inf();
-    }
+__device__ __forceinline__ void write_high_guard(double *slot, int w, int lane) {
+    if (lane < 5) slot[(w + 1) * 5 + lane] = neg_inf();
 }
 
 // ------------------------------------------------------------------------------------------------ forward
 // FULL = true : F holds all 5 states of every cell ([cell][5]); required by expectation mode.
-// FULL = false: posterior mode -- FM holds the match state of every cell, FT all states of the cells on the
+// FULL = false: posterior mode -- F holds the match state of every cell, FT all states of the cells on the
 //               diagonals where a total probability is evaluated (indexed through TotalDesc::full_off).
-template <bool FULL>
+template <bool FULL, int CM>
 __global__ void __launch_bounds__(THREADS_PER_BLOCK)
 k_forward5(const __grid_constant__ DevModel model, Blob bl, int n_regions, double *__restrict__ F,
            double *__restrict__ FT, int *counter, int ring_w) {
     extern __shared__ __align__(16) unsigned char dyn_smem_raw[];
     __shared__ __align__(16) Wave5Shared sh;
-    fill_logadd_coefficients(sh.coef, threadIdx.x);
-    fill_forward_tables(sh, model, threadIdx.x, blockDim.x);
-    fill_boundary(sh, model, threadIdx.x);
-    __syncthreads();
+    fill_wave5_shared<true>(sh, model, threadIdx.x, blockDim.x);
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const int role = lane & 1;       // 0 match lane, 1 gap lane
+    const int role = lane & 1;  // 0 match lane, 1 gap lane
     const bool chain = role == 0;
-    const int jl = lane >> 1;        // cell within a chunk of 16
+    const int jl = lane >> 1;   // cell within a chunk of 16
     const int slot_doubles = (ring_w + 2) * 5;
     double *ring = reinterpret_cast<double *>(dyn_smem_raw) + (size_t) warp * 3 * slot_doubles;
+    if (lane < 15) ring[(lane / 5) * slot_doubles + lane % 5] = neg_inf();  // low guards of the three slots
+    __syncthreads();
+    const double *etp_role = &sh.etp[role][0][0];
     // per-lane state picks (see table comment): v4 = c1[role ? LX : SY], v6 = c2[role ? SY : LX]
     const int s4 = role ? LX : SY, s6 = role ? SY : LX;
     const int s_out4 = role ? LY : M;  // where r4 goes
@@ -161,23 +186,26 @@ k_forward5(const __grid_constant__ DevModel model, Blob bl, int n_regions, doubl
         if (item >= n_regions) break;
         const RegionDesc rg = bl.regions[bl.order_fwd[item]];
         const DiagDesc *dd = bl.diags + rg.diag_base;
-        const uint8_t *sx = bl.sym_x + rg.sym_x_off, *sy = bl.sym_y + rg.sym_y_off;
         const int D = rg.lX + rg.lY;
         DiagDesc cur = dd[0], nxt = dd[1];
         int L1 = cur.xmyL, L2 = 0, w1 = (int) (nxt.cell_off - cur.cell_off), w2 = 0;
-        // diagonal 0 (pairwiseAligner.c:658-659); slot (-1 mod 3) = 2 is the empty "d-2" of diagonal 1
+        double *slot = ring + slot_doubles, *slot1 = ring, *slot2 = ring + 2 * slot_doubles;  // d = 1: (d, d-1, d-2)
+        // diagonal 0 (pairwiseAligner.c:658-659) goes to slot1; slot2 is the empty "d-2" of diagonal 1
         {
             const double *init = sh.boundary[(rg.flags & 1) ? 1 : 0];
-            double *slot0 = ring;
             for (int i = lane; i < w1 * 5; i += 32) {
                 const double v = init[i % 5];
-                slot0[5 + i] = v;
+                slot1[5 + i] = v;
                 if (FULL) F[cur.cell_off * 5 + i] = v;
                 else if (i % 5 == 0) F[cur.cell_off + i / 5] = v;
             }
-            write_guards(slot0, w1, lane);
-            write_guards(ring + 2 * slot_doubles, 0, lane);
+            write_high_guard(slot1, w1, lane);
+            write_high_guard(slot2, 0, lane);
         }
+        // per-lane sequence pointers: cell (x, y) of diagonal d consumes X[x-1] and Y[y-1].  For x = 0 (y = 0) the
+        // byte before the region is read and ignored: every term that uses it comes from an out-of-band neighbour.
+        int x0 = (0 + L1) >> 1, y0 = (0 - L1) >> 1;  // coordinates of cell 0 of the previous diagonal
+        const uint8_t *px = bl.sym_x + rg.sym_x_off + x0 - 1 + jl, *py = bl.sym_y + rg.sym_y_off + y0 - 1 - jl;
         __syncwarp();
         for (int d = 1; d <= D; d++) {
             cur = nxt;
@@ -185,32 +213,35 @@ k_forward5(const __grid_constant__ DevModel model, Blob bl, int n_regions, doubl
             const int L = cur.xmyL;
             const int w = (int) (nxt.cell_off - cur.cell_off);
             const int oLo = (L - 1 - L1) >> 1, oMi = (L - L2) >> 1;
-            double *slot = ring + (d % 3) * slot_doubles;
-            const double *slot1 = ring + ((d + 2) % 3) * slot_doubles;
-            const double *slot2 = ring + ((d + 1) % 3) * slot_doubles;
-            // posterior mode: does this diagonal carry a total?  (then all states go to FT)
+            const int nx0 = (d + L) >> 1, ny0 = (d - L) >> 1;
+            px += nx0 - x0;
+            py += ny0 - y0;
+            x0 = nx0;
+            y0 = ny0;
+            // per-lane neighbour geometry, branch-free: the match lane reads cell (d-2, xmy) twice, the gap lane the
+            // lower (d-1, xmy-1) and upper (d-1, xmy+1) cells
+            const double *nb_slot = chain ? slot2 : slot1;
+            const int nb_off = chain ? oMi : oLo, nb_w = chain ? w2 : w1, nb_step = chain ? 0 : 1;
+            // posterior mode: does this diagonal carry a total?  (then all states also go to FT)
             double *ft = nullptr;
             if (!FULL && (cur.tot_flags & MAB_DIAG_IS_TOTAL))
                 ft = FT + (int64_t) bl.totals[cur.tot_flags & MAB_DIAG_TOT_MASK].full_off * 5;
             for (int j0 = 0; j0 < w; j0 += 16) {
                 const int j = j0 + jl;
                 if (j < w) {
-                    const int xmy = L + 2 * j;
-                    const int x = (d + xmy) >> 1, y = (d - xmy) >> 1;
-                    const int cX = x > 0 ? __ldg(sx + x - 1) : 4, cY = y > 0 ? __ldg(sy + y - 1) : 4;
-                    const double *e = sh.etp[role][cX * 5 + cY];
-                    // neighbour cells: match lane reads (d-2, xmy) twice; gap lane reads lower and upper of d-1
-                    const int iLo = j + oLo;
-                    const double *c1 = chain ? slot2 + clamp_pos(j + oMi, w2) * 5 : slot1 + clamp_pos(iLo, w1) * 5;
-                    const double *c2 = chain ? c1 : slot1 + clamp_pos(iLo + 1, w1) * 5;
+                    const int cX = __ldg(px + j0), cY = __ldg(py - j0);
+                    const double *e = etp_role + (cX * 5 + cY) * ETP_ROW;
+                    const double *c1 = nb_slot + clamp_pos(j + nb_off, nb_w) * 5;
+                    const double *c2 = nb_slot + clamp_pos(j + nb_off + nb_step, nb_w) * 5;
                     const double v1 = c1[M], v2 = c1[SX], v4 = c1[s4], v5 = c2[M], v6 = c2[s6], v8 = c2[LY];
                     const double2 e12 = *reinterpret_cast<const double2 *>(e);
                     const double2 e34 = *reinterpret_cast<const double2 *>(e + 2);
                     const double2 e56 = *reinterpret_cast<const double2 *>(e + 4);
                     const double2 e78 = *reinterpret_cast<const double2 *>(e + 6);
-                    const Quad q = four_logadds(chain, __dadd_rn(v1, e12.x), __dadd_rn(v2, e12.y), __dadd_rn(v1, e34.x),
-                                                __dadd_rn(v4, e34.y), __dadd_rn(v5, e56.x), __dadd_rn(v6, e56.y),
-                                                __dadd_rn(v5, e78.x), __dadd_rn(v8, e78.y), sh.coef);
+                    const Quad q = four_logadds<CM>(chain, __dadd_rn(v1, e12.x), __dadd_rn(v2, e12.y),
+                                                    __dadd_rn(v1, e34.x), __dadd_rn(v4, e34.y), __dadd_rn(v5, e56.x),
+                                                    __dadd_rn(v6, e56.y), __dadd_rn(v5, e78.x), __dadd_rn(v8, e78.y),
+                                                    sh.coef);
                     double *out = slot + (j + 1) * 5;
                     out[s_out4] = q.r4;
                     if (!chain) {
@@ -240,12 +271,16 @@ k_forward5(const __grid_constant__ DevModel model, Blob bl, int n_regions, doubl
                     }
                 }
             }
-            write_guards(slot, w, lane);
+            write_high_guard(slot, w, lane);
             __syncwarp();
             L2 = L1;
             L1 = L;
             w2 = w1;
             w1 = w;
+            double *t = slot2;  // rotate (d, d-1, d-2) -> (d+1, d, d-1)
+            slot2 = slot1;
+            slot1 = slot;
+            slot = t;
         }
     }
 }
@@ -253,23 +288,26 @@ k_forward5(const __grid_constant__ DevModel model, Blob bl, int n_regions, doubl
 // ------------------------------------------------------------------------------------------------ backward
 // One warp per traceback.  FULL as above (B / BT); `edge` receives the match state of diagonal from+1 of
 // intermediate tracebacks (see TracebackDesc::edge_off).
-template <bool FULL>
+template <bool FULL, int CM>
 __global__ void __launch_bounds__(THREADS_PER_BLOCK)
 k_backward5(const __grid_constant__ DevModel model, Blob bl, int n_tbs, double *__restrict__ B,
             double *__restrict__ BT, double *__restrict__ edge, int *counter, int ring_w) {
     extern __shared__ __align__(16) unsigned char dyn_smem_raw[];
     __shared__ __align__(16) Wave5Shared sh;
-    fill_logadd_coefficients(sh.coef, threadIdx.x);
-    fill_backward_tables(sh, model, threadIdx.x, blockDim.x);
-    fill_boundary(sh, model, threadIdx.x);
-    __syncthreads();
+    fill_wave5_shared<false>(sh, model, threadIdx.x, blockDim.x);
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int role = lane & 1;
     const bool chain = role == 0;
     const int jl = lane >> 1;
     const int slot_doubles = (ring_w + 2) * 5;
     double *ring = reinterpret_cast<double *>(dyn_smem_raw) + (size_t) warp * 3 * slot_doubles;
+    if (lane < 15) ring[(lane / 5) * slot_doubles + lane % 5] = neg_inf();
+    __syncthreads();
+    const double *etp_role = &sh.etp[role][0][0];
     const int s_out4 = role ? LY : M;
+    // per-lane picks inside the neighbour cells, as byte-free state indices (see the table comment):
+    //   match lane: v2 = nUp.SY v4 = nUp.LY v6 = nLo.SX v8 = nLo.LX;  gap lane: v2 = nLo.SX v4 = nUp.SY v6 = nLo.LX v8 = nUp.LY
+    const int s2 = chain ? SY : SX, s4 = chain ? LY : SY, s6 = chain ? SX : LX, s8 = chain ? LX : LY;
 
     for (;;) {
         const int item = next_item(counter, lane);
@@ -277,20 +315,19 @@ k_backward5(const __grid_constant__ DevModel model, Blob bl, int n_tbs, double *
         const TracebackDesc tb = bl.tbs[bl.order_bwd[item]];
         const RegionDesc rg = bl.regions[tb.region];
         const DiagDesc *dd = bl.diags + rg.diag_base;
-        const uint8_t *sx = bl.sym_x + rg.sym_x_off, *sy = bl.sym_y + rg.sym_y_off;
         DiagDesc up1 = dd[tb.hi + 1], cur = dd[tb.hi];  // up1 = descriptor of diagonal d+1 while processing d
         int L1 = cur.xmyL, L2 = 0, w1 = (int) (up1.cell_off - cur.cell_off), w2 = 0;
-        // diagonal hi: (ragged)endStateProb on every cell (pairwiseAligner.c:680-681)
+        double *slot = ring + slot_doubles, *slot1 = ring, *slot2 = ring + 2 * slot_doubles;  // (d, d+1, d+2)
+        // diagonal hi: (ragged)endStateProb on every cell (pairwiseAligner.c:680-681), into slot1
         {
             const double *init = sh.boundary[(tb.at_end && (rg.flags & 2)) ? 3 : 2];
-            double *slot = ring + (tb.hi % 3) * slot_doubles;
             const bool keep = tb.hi <= tb.from;  // only the final traceback keeps its top diagonal
             double *bt = nullptr;
             if (!FULL && keep && (cur.tot_flags & MAB_DIAG_IS_TOTAL))
                 bt = BT + (int64_t) bl.totals[cur.tot_flags & MAB_DIAG_TOT_MASK].full_off * 5;
             for (int i = lane; i < w1 * 5; i += 32) {
                 const double v = init[i % 5];
-                slot[5 + i] = v;
+                slot1[5 + i] = v;
                 if (keep) {
                     if (FULL) B[cur.cell_off * 5 + i] = v;
                     else {
@@ -299,9 +336,13 @@ k_backward5(const __grid_constant__ DevModel model, Blob bl, int n_tbs, double *
                     }
                 }
             }
-            write_guards(slot, w1, lane);
-            write_guards(ring + ((tb.hi + 1) % 3) * slot_doubles, 0, lane);  // the empty "d+2" of diagonal hi-1
+            write_high_guard(slot1, w1, lane);
+            write_high_guard(slot2, 0, lane);  // the empty "d+2" of diagonal hi-1
         }
+        // the neighbours of target cell (x, y) consume X[x] and/or Y[y] (0-based); at x = lX (y = lY) the byte after
+        // the region is read and ignored: the neighbours that would use it are out of band (-inf)
+        int x0 = (tb.hi + L1) >> 1, y0 = (tb.hi - L1) >> 1;
+        const uint8_t *px = bl.sym_x + rg.sym_x_off + x0 + jl, *py = bl.sym_y + rg.sym_y_off + y0 - jl;
         __syncwarp();
         for (int d = tb.hi - 1; d > tb.lo; d--) {
             up1 = cur;
@@ -310,9 +351,11 @@ k_backward5(const __grid_constant__ DevModel model, Blob bl, int n_tbs, double *
             const int w = (int) (up1.cell_off - cur.cell_off);
             const int oUp = (L - 1 - L1) >> 1;  // (d+1, xmy-1): the cell whose "upper" is the target
             const int oMi = (L - L2) >> 1;      // (d+2, xmy)
-            double *slot = ring + (d % 3) * slot_doubles;
-            const double *slot1 = ring + ((d + 1) % 3) * slot_doubles;
-            const double *slot2 = ring + ((d + 2) % 3) * slot_doubles;
+            const int nx0 = (d + L) >> 1, ny0 = (d - L) >> 1;
+            px += nx0 - x0;
+            py += ny0 - y0;
+            x0 = nx0;
+            y0 = ny0;
             const bool keep = d <= tb.from;
             const bool to_edge = d == tb.from + 1;
             double *bt = nullptr;
@@ -321,29 +364,24 @@ k_backward5(const __grid_constant__ DevModel model, Blob bl, int n_tbs, double *
             for (int j0 = 0; j0 < w; j0 += 16) {
                 const int j = j0 + jl;
                 if (j < w) {
-                    const int xmy = L + 2 * j;
-                    const int x = (d + xmy) >> 1, y = (d - xmy) >> 1;
-                    // the neighbours consume X[x] and/or Y[y] (0-based); past the end they are out of band anyway
-                    const int cX = x < rg.lX ? __ldg(sx + x) : 4, cY = y < rg.lY ? __ldg(sy + y) : 4;
-                    const double *e = sh.etp[role][cX * 5 + cY];
+                    const int cX = __ldg(px + j0), cY = __ldg(py - j0);
+                    const double *e = etp_role + (cX * 5 + cY) * ETP_ROW;
                     const int iUp = j + oUp;
                     const double *nUp = slot1 + clamp_pos(iUp, w1) * 5;
                     const double *nLo = slot1 + clamp_pos(iUp + 1, w1) * 5;
                     const double *nMi = slot2 + clamp_pos(j + oMi, w2) * 5;
                     // match lane: (nMi.M, nUp.SY, -, nUp.LY, -, nLo.SX, -, nLo.LX)
                     // gap lane:   (nMi.M, nLo.SX, nMi.M, nUp.SY, nMi.M, nLo.LX, nMi.M, nUp.LY)
-                    const double vm = nMi[M];
-                    const double v2 = chain ? nUp[SY] : nLo[SX];
-                    const double v4 = chain ? nUp[LY] : nUp[SY];
-                    const double v6 = chain ? nLo[SX] : nLo[LX];
-                    const double v8 = chain ? nLo[LX] : nUp[LY];
+                    const double *p2 = chain ? nUp : nLo, *p4 = nUp, *p6 = nLo, *p8 = chain ? nLo : nUp;
+                    const double vm = nMi[M], v2 = p2[s2], v4 = p4[s4], v6 = p6[s6], v8 = p8[s8];
                     const double2 e12 = *reinterpret_cast<const double2 *>(e);
                     const double2 e34 = *reinterpret_cast<const double2 *>(e + 2);
                     const double2 e56 = *reinterpret_cast<const double2 *>(e + 4);
                     const double2 e78 = *reinterpret_cast<const double2 *>(e + 6);
-                    const Quad q = four_logadds(chain, __dadd_rn(vm, e12.x), __dadd_rn(v2, e12.y), __dadd_rn(vm, e34.x),
-                                                __dadd_rn(v4, e34.y), __dadd_rn(vm, e56.x), __dadd_rn(v6, e56.y),
-                                                __dadd_rn(vm, e78.x), __dadd_rn(v8, e78.y), sh.coef);
+                    const Quad q = four_logadds<CM>(chain, __dadd_rn(vm, e12.x), __dadd_rn(v2, e12.y),
+                                                    __dadd_rn(vm, e34.x), __dadd_rn(v4, e34.y), __dadd_rn(vm, e56.x),
+                                                    __dadd_rn(v6, e56.y), __dadd_rn(vm, e78.x), __dadd_rn(v8, e78.y),
+                                                    sh.coef);
                     // gap lane results: r1 = SX, r2 = SY, r3 = LX, r4 = LY
                     double *out = slot + (j + 1) * 5;
                     out[s_out4] = q.r4;
@@ -378,12 +416,16 @@ k_backward5(const __grid_constant__ DevModel model, Blob bl, int n_tbs, double *
                     }
                 }
             }
-            write_guards(slot, w, lane);
+            write_high_guard(slot, w, lane);
             __syncwarp();
             L2 = L1;
             L1 = L;
             w2 = w1;
             w1 = w;
+            double *t = slot2;  // rotate (d, d+1, d+2) -> (d-1, d, d+1)
+            slot2 = slot1;
+            slot1 = slot;
+            slot = t;
         }
     }
 }
