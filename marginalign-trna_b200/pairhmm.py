@@ -63,7 +63,9 @@ class PairHmmModel:
         h = capi.vp()
         capi.check(L.mab_model_from_hmm(int(hmm_type), T.ctypes.data_as(capi.dp), E.ctypes.data_as(capi.dp),
                                         C.byref(h)))
-        return cls(h)
+        m = cls(h)
+        m.src_transitions, m.src_emissions = T.copy(), E.copy()  # the `.hmm` numbers this machine was built from
+        return m
 
     @classmethod
     def from_file(cls, path):
