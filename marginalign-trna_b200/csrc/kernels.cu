@@ -22,6 +22,7 @@
 #include <algorithm>
 #include <cstdio>
 #include <cstdlib>
+#include <cstring>
 #include <vector>
 
 #include "mab_internal.h"
@@ -798,10 +799,13 @@ int run_dp(const DevModel &dm, const mab_plan *plan, const Blob &bl, const Works
     const BlobHeader &h = plan->hdr;
     const DeviceInfo &di = device_info();
     // shared-memory ring per warp: 3 diagonals x (max_width + 2 guard) cells x S doubles; fewer warps per block for
-    // wide bands
+    // wide bands.  The 5-state kernels also hold ~27 KB of replicated tables per block, so they use bigger blocks.
+    static const int w5_warps = getenv("MAB_W5_WARPS") ? std::max(1, std::min(32, atoi(getenv("MAB_W5_WARPS")))) : 8;
+    const int want_warps = S == 5 ? w5_warps : WARPS_PER_BLOCK;
+    const int64_t static_bytes = S == 5 ? (int64_t) sizeof(Wave5Shared) + 1024 : 8 * 1024;
     const int64_t ring_per_warp = (int64_t) 3 * (h.max_width + 2) * S * 8;
-    const int64_t budget = (int64_t) di.max_smem_optin - 8 * 1024;
-    const int nw = (int) std::min<int64_t>(WARPS_PER_BLOCK, budget / std::max<int64_t>(1, ring_per_warp));
+    const int64_t budget = (int64_t) di.max_smem_optin - static_bytes;
+    const int nw = (int) std::min<int64_t>(want_warps, budget / std::max<int64_t>(1, ring_per_warp));
     if (nw < 1) {
         mab_set_error("band too wide for the shared-memory ring (max width %lld cells); lower diagonalExpansion or "
                       "splitMatrixBiggerThanThis", (long long) h.max_width);
@@ -809,13 +813,23 @@ int run_dp(const DevModel &dm, const mab_plan *plan, const Blob &bl, const Works
     }
     const int64_t ring_bytes = ring_per_warp * nw;
     const int ring_w = (int) h.max_width;
-    const int blocks_per_sm = (int) std::max<int64_t>(1, std::min<int64_t>(12, (200 * 1024) / (ring_bytes + 8192)));
+    const int blocks_per_sm = (int) std::max<int64_t>(
+        1, std::min<int64_t>(64 / nw, (220 * 1024) / (ring_bytes + static_bytes + 1024)));
     int rc;
     if ((rc = check(cudaMemsetAsync(w.counters, 0, 256, st), "memset counters"))) return rc;
     if (S == 5) {
-        static const bool coef_smem = getenv("MAB_COEF_SMEM") != nullptr;  // experiment switch, see wavefront5.cuh
-        auto kf = coef_smem ? k_forward5<FULL, COEF_SMEM> : k_forward5<FULL, COEF_CONST>;
-        auto kb = coef_smem ? k_backward5<FULL, COEF_SMEM> : k_backward5<FULL, COEF_CONST>;
+        // where the logAdd coefficients are fetched from (wavefront5.cuh): smem (default, fastest measured) |
+        // mixed | const -- kept switchable for profiling
+        static const int cm = [] {
+            const char *e = getenv("MAB_COEF");
+            if (e && !strcmp(e, "const")) return (int) COEF_CONST;
+            if (e && !strcmp(e, "mixed")) return (int) COEF_MIXED;
+            return (int) COEF_SMEM;
+        }();
+        auto kf = cm == COEF_CONST ? k_forward5<FULL, COEF_CONST> : cm == COEF_SMEM ? k_forward5<FULL, COEF_SMEM>
+                                                                                     : k_forward5<FULL, COEF_MIXED>;
+        auto kb = cm == COEF_CONST ? k_backward5<FULL, COEF_CONST> : cm == COEF_SMEM ? k_backward5<FULL, COEF_SMEM>
+                                                                                     : k_backward5<FULL, COEF_MIXED>;
         if ((rc = allow_smem(kf, ring_bytes)) || (rc = allow_smem(kb, ring_bytes))) return rc;
         {
             LaunchTimer lt(K_FORWARD, st);

@@ -5,10 +5,15 @@
 //       active.
 //   v2  pair-lane mapping + branch-free logAdd with a shared-memory coefficient table: shared-memory data pipe at
 //       97 % (44 % of the load wavefronts were bank-conflict replays on the 64-byte (eP+tP) rows).
-//   v3  (this file) rows padded to 80 B, coefficients moved to the constant bank (off the shared-memory pipe),
-//       rotating ring-slot pointers, per-lane sequence pointers advanced incrementally, one guard store per diagonal.
+//   v3  rows padded to 80 B, coefficients moved to the constant bank, rotating ring-slot pointers: the indexed
+//       constant cache became the limiter (IDC 92 % busy: a per-lane index makes every distinct address a request),
+//       and 46 % of the shared-memory wavefronts were still conflicts.
+//   v4  (this file) the two lane roles are split by half-warp, so every 64-bit shared access phase sees one role
+//       with a conflict-free 40-byte stride; the (eP+tP) rows and the logAdd coefficients live in shared memory in
+//       8 replicas, lane l reading replica l & 7, which makes every LDS.128 conflict-free whatever rows the lanes
+//       index.  Forward 24.0 -> 13.9 ms, backward 24.4 -> 15.1 ms per 5.6e8 cells.
 //
-//   * every cell of a diagonal is handled by TWO adjacent lanes that execute the SAME instruction stream of four
+//   * every cell of a diagonal is handled by TWO lanes (l and l + 16) that execute the SAME instruction stream of four
 //     logAdds: the "match lane" runs the 5-term chain into the match state, the "gap lane" the four independent
 //     2-term sums into the gap states (5-state cellCalculate has exactly 4 + 4 logAdds, stateMachine.c:399-429).
 //     A 12-13 cell diagonal (expansion 10) fills 24-26 lanes and a warp issues 4 logAdds per diagonal instead of 8;
@@ -29,28 +34,40 @@ __constant__ double c_la_coef[16] = {
     (double) -0.004605031767994f, (double) 0.063427417320019f, (double) 0.695956496475118f, (double) 0.514272634594009f,
     (double) -0.000458661602210f, (double) 0.009695946122598f, (double) 0.930734667215156f, (double) 0.168037164329057f};
 
-enum CoefMode { COEF_CONST = 0, COEF_SMEM = 1 };
+enum CoefMode { COEF_CONST = 0, COEF_SMEM = 1, COEF_MIXED = 2 };
 
+#define W5_COPIES 8  // table replicas: lane l reads replica (l & 7), so the 8 lanes of a quarter-warp (one LDS.128
+                     // phase) always hit 8 different 16-byte bank groups, whatever rows they index
+
+// CM selects where the four cubic coefficients come from.  Measured (profiles/r1_ncu_summary.md): all four from the
+// constant bank saturates the indexed-constant cache (the index differs per lane, every distinct address is a
+// separate request: IDC 92 % busy); all four from shared memory loads the LSU instead.  COEF_MIXED splits them:
+// (c3, c2) with one conflict-free LDS.128, (c1, c0) with two LDC.64.
 template <int CM>
-__device__ __forceinline__ double la_bf(double x, double y, const double *coef_smem) {
+__device__ __forceinline__ double la_bf(double x, double y, const double2 *coef_lane) {
     const bool lt = x < y;
     const double hi = lt ? y : x;
     const double lo = lt ? x : y;
     const double d = __dsub_rn(hi, lo);  // +inf if lo = -inf, NaN if both are -inf: both fail (d < 7.5) below
-    const int piece = (d > 1.00 ? 4 : 0) + (d > 2.50 ? 4 : 0) + (d > 4.50 ? 4 : 0);
+    const int piece = (d > 1.00 ? 1 : 0) + (d > 2.50 ? 1 : 0) + (d > 4.50 ? 1 : 0);
     double c3, c2, c1, c0;
     if (CM == COEF_CONST) {
-        c3 = c_la_coef[piece];
-        c2 = c_la_coef[piece + 1];
-        c1 = c_la_coef[piece + 2];
-        c0 = c_la_coef[piece + 3];
+        c3 = c_la_coef[piece * 4];
+        c2 = c_la_coef[piece * 4 + 1];
+        c1 = c_la_coef[piece * 4 + 2];
+        c0 = c_la_coef[piece * 4 + 3];
     } else {
-        const double2 c32 = *reinterpret_cast<const double2 *>(coef_smem + piece);
-        const double2 c10 = *reinterpret_cast<const double2 *>(coef_smem + piece + 2);
+        const double2 c32 = coef_lane[piece * 2 * W5_COPIES];
         c3 = c32.x;
         c2 = c32.y;
-        c1 = c10.x;
-        c0 = c10.y;
+        if (CM == COEF_SMEM) {
+            const double2 c10 = coef_lane[(piece * 2 + 1) * W5_COPIES];
+            c1 = c10.x;
+            c0 = c10.y;
+        } else {
+            c1 = c_la_coef[piece * 4 + 2];
+            c0 = c_la_coef[piece * 4 + 3];
+        }
     }
     double r = __dadd_rn(__dmul_rn(c3, d), c2);
     r = __dadd_rn(__dmul_rn(r, d), c1);
@@ -67,7 +84,7 @@ struct Quad {
 };
 template <int CM>
 __device__ __forceinline__ Quad four_logadds(bool chain, double t1, double t2, double t3, double t4, double t5, double t6,
-                                             double t7, double t8, const double *coef) {
+                                             double t7, double t8, const double2 *coef) {
     Quad q;
     q.r1 = la_bf<CM>(t1, t2, coef);
     q.r2 = la_bf<CM>(chain ? q.r1 : t3, t4, coef);
@@ -76,13 +93,10 @@ __device__ __forceinline__ Quad four_logadds(bool chain, double t1, double t2, d
     return q;
 }
 
-#define ETP_ROW 10  // doubles per (eP+tP) row: 8 used + 2 pad.  With 16-byte accesses a row then lands on bank group
-                    // (5 * row) mod 8; the unpadded 64-byte stride put every row on group 0 or 4 (4-way conflicts).
-
 struct Wave5Shared {
-    double coef[16];
-    double etp[2][25][ETP_ROW];  // [lane role][cX*5+cY][slot]
-    double boundary[4][5];       // start, ragged_start, end, ragged_end
+    double2 etp[2][25][4][W5_COPIES];  // [lane role][cX*5+cY][slot pair][replica]: (eP + tP) addends t1..t8
+    double2 coef[4][2][W5_COPIES];     // [piece][(c3,c2) | (c1,c0)][replica]
+    double boundary[4][5];             // start, ragged_start, end, ragged_end
 };
 
 // Forward tables.  Match lane: t1 = mi.M+eM0, t2 = mi.SX+eM1, t4 = mi.SY+eM2, t6 = mi.LX+eM3, t8 = mi.LY+eM4.
@@ -134,11 +148,17 @@ __device__ __forceinline__ double backward_table_entry(const DevModel &m, int ro
 
 template <bool FORWARD>
 __device__ __forceinline__ void fill_wave5_shared(Wave5Shared &sh, const DevModel &m, int tid, int nthreads) {
-    for (int i = tid; i < 16; i += nthreads) sh.coef[i] = c_la_coef[i];
-    for (int i = tid; i < 2 * 25 * 8; i += nthreads) {
-        const int role = i / 200, code = (i / 8) % 25, slot = i % 8;
-        sh.etp[role][code][slot] = FORWARD ? forward_table_entry(m, role, code, slot)
-                                           : backward_table_entry(m, role, code, slot);
+    for (int i = tid; i < 4 * 2 * W5_COPIES; i += nthreads) {
+        const int piece = i / (2 * W5_COPIES), half = (i / W5_COPIES) % 2, rep = i % W5_COPIES;
+        sh.coef[piece][half][rep] = make_double2(c_la_coef[piece * 4 + half * 2], c_la_coef[piece * 4 + half * 2 + 1]);
+    }
+    for (int i = tid; i < 2 * 25 * 4 * W5_COPIES; i += nthreads) {
+        const int role = i / (25 * 4 * W5_COPIES), code = (i / (4 * W5_COPIES)) % 25, sp = (i / W5_COPIES) % 4,
+                  rep = i % W5_COPIES;
+        const double a = FORWARD ? forward_table_entry(m, role, code, 2 * sp) : backward_table_entry(m, role, code, 2 * sp);
+        const double b = FORWARD ? forward_table_entry(m, role, code, 2 * sp + 1)
+                                 : backward_table_entry(m, role, code, 2 * sp + 1);
+        sh.etp[role][code][sp][rep] = make_double2(a, b);
     }
     for (int i = tid; i < 20; i += nthreads) {
         const int which = i / 5, s = i % 5;
@@ -162,21 +182,24 @@ __device__ __forceinline__ void write_high_guard(double *slot, int w, int lane) 
 // FULL = false: posterior mode -- F holds the match state of every cell, FT all states of the cells on the
 //               diagonals where a total probability is evaluated (indexed through TotalDesc::full_off).
 template <bool FULL, int CM>
-__global__ void __launch_bounds__(THREADS_PER_BLOCK)
+__global__ void __launch_bounds__(1024)
 k_forward5(const __grid_constant__ DevModel model, Blob bl, int n_regions, double *__restrict__ F,
            double *__restrict__ FT, int *counter, int ring_w) {
     extern __shared__ __align__(16) unsigned char dyn_smem_raw[];
     __shared__ __align__(16) Wave5Shared sh;
     fill_wave5_shared<true>(sh, model, threadIdx.x, blockDim.x);
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const int role = lane & 1;  // 0 match lane, 1 gap lane
+    const int role = lane >> 4;  // lanes 0-15 are match lanes, 16-31 gap lanes of cells 0..15 of a chunk: a 64-bit
+                                 // shared access is served per half-warp, so each phase sees one role whose
+                                 // 40-byte cell stride is conflict-free
     const bool chain = role == 0;
-    const int jl = lane >> 1;   // cell within a chunk of 16
+    const int jl = lane & 15;    // cell within a chunk of 16
     const int slot_doubles = (ring_w + 2) * 5;
     double *ring = reinterpret_cast<double *>(dyn_smem_raw) + (size_t) warp * 3 * slot_doubles;
     if (lane < 15) ring[(lane / 5) * slot_doubles + lane % 5] = neg_inf();  // low guards of the three slots
     __syncthreads();
-    const double *etp_role = &sh.etp[role][0][0];
+    const double2 *etp_lane = &sh.etp[role][0][0][lane & (W5_COPIES - 1)];
+    const double2 *coef_lane = &sh.coef[0][0][lane & (W5_COPIES - 1)];
     // per-lane state picks (see table comment): v4 = c1[role ? LX : SY], v6 = c2[role ? SY : LX]
     const int s4 = role ? LX : SY, s6 = role ? SY : LX;
     const int s_out4 = role ? LY : M;  // where r4 goes
@@ -230,18 +253,15 @@ k_forward5(const __grid_constant__ DevModel model, Blob bl, int n_regions, doubl
                 const int j = j0 + jl;
                 if (j < w) {
                     const int cX = __ldg(px + j0), cY = __ldg(py - j0);
-                    const double *e = etp_role + (cX * 5 + cY) * ETP_ROW;
+                    const double2 *e = etp_lane + (cX * 5 + cY) * (4 * W5_COPIES);
                     const double *c1 = nb_slot + clamp_pos(j + nb_off, nb_w) * 5;
                     const double *c2 = nb_slot + clamp_pos(j + nb_off + nb_step, nb_w) * 5;
                     const double v1 = c1[M], v2 = c1[SX], v4 = c1[s4], v5 = c2[M], v6 = c2[s6], v8 = c2[LY];
-                    const double2 e12 = *reinterpret_cast<const double2 *>(e);
-                    const double2 e34 = *reinterpret_cast<const double2 *>(e + 2);
-                    const double2 e56 = *reinterpret_cast<const double2 *>(e + 4);
-                    const double2 e78 = *reinterpret_cast<const double2 *>(e + 6);
+                    const double2 e12 = e[0], e34 = e[W5_COPIES], e56 = e[2 * W5_COPIES], e78 = e[3 * W5_COPIES];
                     const Quad q = four_logadds<CM>(chain, __dadd_rn(v1, e12.x), __dadd_rn(v2, e12.y),
                                                     __dadd_rn(v1, e34.x), __dadd_rn(v4, e34.y), __dadd_rn(v5, e56.x),
                                                     __dadd_rn(v6, e56.y), __dadd_rn(v5, e78.x), __dadd_rn(v8, e78.y),
-                                                    sh.coef);
+                                                    coef_lane);
                     double *out = slot + (j + 1) * 5;
                     out[s_out4] = q.r4;
                     if (!chain) {
@@ -289,21 +309,22 @@ k_forward5(const __grid_constant__ DevModel model, Blob bl, int n_regions, doubl
 // One warp per traceback.  FULL as above (B / BT); `edge` receives the match state of diagonal from+1 of
 // intermediate tracebacks (see TracebackDesc::edge_off).
 template <bool FULL, int CM>
-__global__ void __launch_bounds__(THREADS_PER_BLOCK)
+__global__ void __launch_bounds__(1024)
 k_backward5(const __grid_constant__ DevModel model, Blob bl, int n_tbs, double *__restrict__ B,
             double *__restrict__ BT, double *__restrict__ edge, int *counter, int ring_w) {
     extern __shared__ __align__(16) unsigned char dyn_smem_raw[];
     __shared__ __align__(16) Wave5Shared sh;
     fill_wave5_shared<false>(sh, model, threadIdx.x, blockDim.x);
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const int role = lane & 1;
+    const int role = lane >> 4;
     const bool chain = role == 0;
-    const int jl = lane >> 1;
+    const int jl = lane & 15;
     const int slot_doubles = (ring_w + 2) * 5;
     double *ring = reinterpret_cast<double *>(dyn_smem_raw) + (size_t) warp * 3 * slot_doubles;
     if (lane < 15) ring[(lane / 5) * slot_doubles + lane % 5] = neg_inf();
     __syncthreads();
-    const double *etp_role = &sh.etp[role][0][0];
+    const double2 *etp_lane = &sh.etp[role][0][0][lane & (W5_COPIES - 1)];
+    const double2 *coef_lane = &sh.coef[0][0][lane & (W5_COPIES - 1)];
     const int s_out4 = role ? LY : M;
     // per-lane picks inside the neighbour cells, as byte-free state indices (see the table comment):
     //   match lane: v2 = nUp.SY v4 = nUp.LY v6 = nLo.SX v8 = nLo.LX;  gap lane: v2 = nLo.SX v4 = nUp.SY v6 = nLo.LX v8 = nUp.LY
@@ -365,7 +386,7 @@ k_backward5(const __grid_constant__ DevModel model, Blob bl, int n_tbs, double *
                 const int j = j0 + jl;
                 if (j < w) {
                     const int cX = __ldg(px + j0), cY = __ldg(py - j0);
-                    const double *e = etp_role + (cX * 5 + cY) * ETP_ROW;
+                    const double2 *e = etp_lane + (cX * 5 + cY) * (4 * W5_COPIES);
                     const int iUp = j + oUp;
                     const double *nUp = slot1 + clamp_pos(iUp, w1) * 5;
                     const double *nLo = slot1 + clamp_pos(iUp + 1, w1) * 5;
@@ -374,14 +395,11 @@ k_backward5(const __grid_constant__ DevModel model, Blob bl, int n_tbs, double *
                     // gap lane:   (nMi.M, nLo.SX, nMi.M, nUp.SY, nMi.M, nLo.LX, nMi.M, nUp.LY)
                     const double *p2 = chain ? nUp : nLo, *p4 = nUp, *p6 = nLo, *p8 = chain ? nLo : nUp;
                     const double vm = nMi[M], v2 = p2[s2], v4 = p4[s4], v6 = p6[s6], v8 = p8[s8];
-                    const double2 e12 = *reinterpret_cast<const double2 *>(e);
-                    const double2 e34 = *reinterpret_cast<const double2 *>(e + 2);
-                    const double2 e56 = *reinterpret_cast<const double2 *>(e + 4);
-                    const double2 e78 = *reinterpret_cast<const double2 *>(e + 6);
+                    const double2 e12 = e[0], e34 = e[W5_COPIES], e56 = e[2 * W5_COPIES], e78 = e[3 * W5_COPIES];
                     const Quad q = four_logadds<CM>(chain, __dadd_rn(vm, e12.x), __dadd_rn(v2, e12.y),
                                                     __dadd_rn(vm, e34.x), __dadd_rn(v4, e34.y), __dadd_rn(vm, e56.x),
                                                     __dadd_rn(v6, e56.y), __dadd_rn(vm, e78.x), __dadd_rn(v8, e78.y),
-                                                    sh.coef);
+                                                    coef_lane);
                     // gap lane results: r1 = SX, r2 = SY, r3 = LX, r4 = LY
                     double *out = slot + (j + 1) * 5;
                     out[s_out4] = q.r4;
