@@ -119,6 +119,23 @@ int64_t mab_plan_regions(const mab_plan *plan, int64_t *out5, int64_t cap_rows);
 int64_t mab_plan_band(const mab_plan *plan, int64_t region, int64_t *out2, int64_t cap_rows);
 int64_t mab_plan_tracebacks(const mab_plan *plan, int64_t *out5, int64_t cap_rows);
 
+/* ---------------------------------------------------------------- planning on the device
+ * Same plan, built in HBM from raw inputs that are ALREADY on the device (the arrays of mab_plan_from_cigars /
+ * mab_plan_from_anchors as device pointers; pass d_off_ops = NULL to use anchors).  Only bases and cigars cross PCIe
+ * (~0.4 kB per tRNA read instead of ~4.8 kB of descriptors) and nothing is planned on host cores.  Replaces the same
+ * reference code as the host planner (cigarRead .. band_construct .. the checkpoint schedule, see above).
+ * d_arena: caller-owned device memory, 256-byte aligned; the blob is laid out inside it and stays valid as long as
+ * the arena does.  mab_plan_device_arena_hint gives a first size; if the arena is too small the call returns
+ * MAB_E_CAPACITY with the exact requirement in *needed_bytes (retry with that).  The call synchronises `stream`
+ * twice (two 64-byte count read-backs).  The returned plan is used like a host-built one, with
+ * d_blob = mab_plan_device_blob(plan); its introspection getters and mab_plan_write_blob return MAB_E_ARG. */
+int64_t mab_plan_device_arena_hint(const mab_params *p, int64_t n, int64_t len_x, int64_t len_y);
+int mab_plan_build_device(const mab_params *p, int64_t n, const uint8_t *d_seq_x, const int64_t *d_off_x, int64_t len_x,
+        const uint8_t *d_seq_y, const int64_t *d_off_y, int64_t len_y, const uint8_t *d_ops, const int32_t *d_lens,
+        const int64_t *d_off_ops, const int64_t *d_anchors, const int64_t *d_off_anc, void *d_arena,
+        int64_t arena_bytes, void *stream, mab_plan **out, int64_t *needed_bytes);
+const void *mab_plan_device_blob(const mab_plan *plan);
+
 /* ---------------------------------------------------------------- device work
  * d_blob: device copy of the plan blob.  d_ws: device scratch of at least the size mab_plan_get_info reported.
  * All launches are asynchronous on `stream`.

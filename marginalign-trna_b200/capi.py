@@ -58,6 +58,10 @@ SIGNATURES = {
     "mab_plan_regions": (C.c_int64, [vp, i64p, C.c_int64]),
     "mab_plan_band": (C.c_int64, [vp, C.c_int64, i64p, C.c_int64]),
     "mab_plan_tracebacks": (C.c_int64, [vp, i64p, C.c_int64]),
+    "mab_plan_device_arena_hint": (C.c_int64, [C.POINTER(MabParams), C.c_int64, C.c_int64, C.c_int64]),
+    "mab_plan_build_device": (C.c_int, [C.POINTER(MabParams), C.c_int64, vp, vp, C.c_int64, vp, vp, C.c_int64, vp, vp,
+                                        vp, vp, vp, vp, C.c_int64, vp, C.POINTER(vp), i64p]),
+    "mab_plan_device_blob": (vp, [vp]),
     "mab_posteriors_compute": (C.c_int, [vp, vp, vp, vp, C.c_int64, vp, vp, vp]),
     "mab_posteriors_emit": (C.c_int, [vp, vp, vp, C.c_int64, vp, vp, vp, C.c_int64, vp]),
     "mab_expectations": (C.c_int, [vp, vp, vp, vp, C.c_int64, vp, vp]),

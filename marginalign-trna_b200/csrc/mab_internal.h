@@ -128,7 +128,11 @@ struct mab_plan {
     // kept for introspection only
     std::vector<int64_t> anchors;      // x,y interleaved, alignment-local
     std::vector<int64_t> anchor_off;   // [n+1]
+    // plans built by mab_plan_build_device: the blob lives in the caller's device arena and the host vectors above
+    // are empty (no introspection)
+    void *d_blob = nullptr;
 };
+int mab_params_validate(const mab_params *p);
 
 // workspace carving (device scratch); all offsets 256-byte aligned
 struct WorkspaceLayout {

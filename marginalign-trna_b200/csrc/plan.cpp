@@ -19,19 +19,14 @@
 
 #include "mab_internal.h"
 
+#include "plan_core.h"
+
 namespace {
 
-inline uint8_t symbol_of(uint8_t c) {  // symbol_convertCharToSymbol, pairwiseAligner.c:262-279
-    switch (c) {
-        case 'A': case 'a': return 0;
-        case 'C': case 'c': return 1;
-        case 'G': case 'g': return 2;
-        case 'T': case 't': return 3;
-        default: return 4;
-    }
-}
-
-inline uint8_t upper_of(uint8_t c) { return (c >= 'a' && c <= 'z') ? uint8_t(c - 32) : c; }
+using plan_core::AlnInput;
+using plan_core::AnchorStream;
+using plan_core::Split;
+using plan_core::symbol_of;
 
 struct Piece {  // what one worker thread produces for its range of alignments (all indices piece-local)
     std::vector<RegionDesc> regions;
@@ -44,44 +39,9 @@ struct Piece {  // what one worker thread produces for its range of alignments (
     std::string error;
 };
 
-inline int64_t clamp_to(int64_t z, int64_t hi) { return z < 0 ? 0 : (z > hi ? hi : z); }
-
-// band_setCurrentDiagonal (:104-122)
-inline void band_diagonal(int64_t xay, int64_t xL, int64_t yL, int64_t xU, int64_t yU, int64_t &l, int64_t &r) {
-    l = xL - yL;
-    r = xU - yU;
-    if ((xay + l) % 2 != 0) l += 1;  // band_avoidOffByOne
-    if ((xay + r) % 2 != 0) r += 1;
-    int64_t v = (xay + l) / 2;
-    if (v < xL) l += 2 * (xL - v);
-    v = (xay - l) / 2;
-    if (yL < v) l += 2 * (v - yL);
-    v = (xay + r) / 2;
-    if (xU < v) r -= 2 * (v - xU);
-    v = (xay - r) / 2;
-    if (v < yU) r -= 2 * (yU - v);
-}
-
-struct Split { int64_t x1, y1, x2, y2; };
-
-// getSplitPointsP (:1016-1038)
-inline bool split_gap(int64_t &x1, int64_t &y1, int64_t x2, int64_t y2, int64_t x3, int64_t y3, std::vector<Split> &out,
-                      int64_t limit, bool skip) {
-    const int64_t gx = x3 - x2, gy = y3 - y2;
-    if (gx * gy > limit) {
-        const int64_t cap = (int64_t) std::sqrt((double) limit);
-        const int64_t hx = gx / 2 > cap ? cap : gx / 2, hy = gy / 2 > cap ? cap : gy / 2;
-        if (!skip) out.push_back({x1, y1, x2 + hx, y2 + hy});
-        x1 = x3 - hx;
-        y1 = y3 - hy;
-        return true;
-    }
-    return false;
-}
-
-// Builds one region: band, cells, traceback schedule.  anchors are region-local.
-void plan_region(Piece &pc, const mab_params &p, int32_t aln_local, const Split &sp, const int64_t *anc, int64_t n_anc,
-                 bool ragged_left, bool ragged_right, int64_t sym_x_off, int64_t sym_y_off) {
+// Builds one region: band, cells, traceback schedule (the walks live in plan_core.h).
+void plan_region(Piece &pc, const mab_params &p, const AlnInput &in, int32_t aln_local, const Split &sp,
+                 const AnchorStream &cur, bool ragged_left, bool ragged_right, int64_t sym_x_off, int64_t sym_y_off) {
     const int64_t lX = sp.x2 - sp.x1, lY = sp.y2 - sp.y1, D = lX + lY;
     if (D == 0) return;  // getPosteriorProbsWithBanding :650-652
     RegionDesc rg;
@@ -98,88 +58,58 @@ void plan_region(Piece &pc, const mab_params &p, int32_t aln_local, const Split 
     rg.tb_base = (int32_t) pc.tbs.size();
     rg.tot_base = (int32_t) pc.totals.size();
 
-    // band_construct (:128-179)
-    const int64_t e = p.diagonal_expansion;
-    int64_t ai = 0, xay = 0, pxay = 0, pxmy = 0, nxay = 0, nxmy = 0, xL = 0, yL = 0, xU = 0, yU = 0;
     const size_t d0 = pc.diags.size();
     pc.diags.resize(d0 + D + 1);
     int64_t cell = pc.n_cells;
-    while (xay <= D) {
-        int64_t l, r;
-        band_diagonal(xay, xL, yL, xU, yU, l, r);
+    plan_core::band_walk(in, p, sp, cur, [&](int64_t xay, int64_t l, int64_t w) {
         DiagDesc &dd = pc.diags[d0 + xay];
         dd.cell_off = cell;
         dd.xmyL = (int32_t) l;
         dd.tot_flags = MAB_DIAG_TOT_MASK;  // "none" until the schedule below assigns one
-        const int64_t w = (r - l) / 2 + 1;
         cell += w;
         if (w > pc.max_width) pc.max_width = w;
-        if (nxay == xay++) {
-            pxay = nxay;
-            pxmy = nxmy;
-            int64_t x = lX, y = lY;
-            if (ai < n_anc) {
-                x = anc[2 * ai] + 1;
-                y = anc[2 * ai + 1] + 1;
-                ai++;
-            }
-            nxay = x + y;
-            nxmy = x - y;
-            xL = clamp_to((pxay + (pxmy - e)) / 2, lX);
-            yL = clamp_to((nxay - (nxmy - e)) / 2, lY);
-            xU = clamp_to((nxay + (nxmy + e)) / 2, lX);
-            yU = clamp_to((pxay - (pxmy + e)) / 2, lY);
-        }
-    }
+    });
     pc.n_cells = cell;
 
-    // traceback schedule (:664-744)
     auto width = [&](int64_t d) {
         const int64_t next = d == D ? cell : pc.diags[d0 + d + 1].cell_off;
         return next - pc.diags[d0 + d].cell_off;
     };
-    int64_t traced_to = 0;
-    for (int64_t d = 1; d <= D; d++) {
-        const bool at_end = d == D;
-        const bool tb_point = d >= traced_to + p.min_diags_between_traceback && width(d) <= e * 2 + 1;
-        if (!(at_end || tb_point)) continue;
-        TracebackDesc tb;
-        std::memset(&tb, 0, sizeof(tb));
-        tb.region = -1;  // patched when pieces are merged
-        tb.lo = (int32_t) traced_to;
-        tb.hi = (int32_t) d;
-        tb.from = (int32_t) (d - (at_end ? 0 : p.traceback_diagonals + 1));
-        tb.at_end = at_end;
-        tb.tot_base = (int32_t) pc.totals.size();
-        tb.edge_off = -1;
-        if (!at_end) {  // from + 1 <= hi always holds here
-            tb.edge_off = (int32_t) pc.n_edge;
-            pc.n_edge += width(tb.from + 1);
+    struct Sink {
+        Piece &pc;
+        size_t d0;
+        int32_t tot_base_region;
+        void total(int64_t q, int through, int64_t w) {
+            TotalDesc td;
+            td.region = -1;  // patched when pieces are merged
+            td.d = (int32_t) q;
+            td.edge_off = through == 0 ? MAB_THROUGH_NONE : (through == 1 ? (int32_t) pc.n_edge : MAB_THROUGH_MATRIX);
+            td.full_off = (int32_t) pc.n_full;
+            pc.n_full += w;
+            pc.totals.push_back(td);
         }
-        // posterior diagonals are from, from-1, ..., lo+1; the total is refreshed on every 10th of them (:712)
-        int64_t k = 0;
-        for (int64_t q = tb.from; q > tb.lo; q--, k++) {
-            const bool is_total = k % 10 == 0;
-            if (is_total) {
-                TotalDesc td;
-                td.region = -1;
-                td.d = (int32_t) q;
-                // backward diagonal q+1 is alive iff q < hi (:573-575); on q == from it is this traceback's own copy
-                td.edge_off = q == tb.hi ? MAB_THROUGH_NONE : (q == tb.from ? tb.edge_off : MAB_THROUGH_MATRIX);
-                td.full_off = (int32_t) pc.n_full;
-                pc.n_full += width(q);
-                pc.totals.push_back(td);
-            }
-            uint32_t tf = (uint32_t) (pc.totals.size() - 1);
+        void diag_flags(int64_t q, int64_t tot_in_region, bool is_total, bool no_middle) {
+            uint32_t tf = (uint32_t) (tot_base_region + tot_in_region);
             if (is_total) tf |= MAB_DIAG_IS_TOTAL;
-            // the forward diagonal q-2 has been deleted by the previous traceback when q-2 < lo (:725-727, :737)
-            if (q - 2 < tb.lo) tf |= MAB_DIAG_NO_MIDDLE;
+            if (no_middle) tf |= MAB_DIAG_NO_MIDDLE;
             pc.diags[d0 + q].tot_flags = tf;
         }
-        tb.n_tot = (int32_t) pc.totals.size() - tb.tot_base;
-        pc.tbs.push_back(tb);
-        traced_to = tb.from;
-    }
+        void traceback(int64_t lo, int64_t hi, int64_t from, bool at_end, int64_t n_tot, int64_t edge_cells) {
+            TracebackDesc tb;
+            std::memset(&tb, 0, sizeof(tb));
+            tb.region = -1;
+            tb.lo = (int32_t) lo;
+            tb.hi = (int32_t) hi;
+            tb.from = (int32_t) from;
+            tb.at_end = at_end;
+            tb.tot_base = (int32_t) ((int64_t) pc.totals.size() - n_tot);
+            tb.n_tot = (int32_t) n_tot;
+            tb.edge_off = at_end ? -1 : (int32_t) pc.n_edge;
+            pc.n_edge += edge_cells;
+            pc.tbs.push_back(tb);
+        }
+    } sink{pc, d0, rg.tot_base};
+    plan_core::schedule_walk(p, D, width, sink);
     rg.n_tb = (int32_t) pc.tbs.size() - rg.tb_base;
     rg.n_tot = (int32_t) pc.totals.size() - rg.tot_base;
     pc.regions.push_back(rg);
@@ -196,98 +126,49 @@ struct BatchInput {
 };
 
 void plan_range(Piece &pc, const mab_params &p, const BatchInput &in, int64_t a0, int64_t a1) {
-    std::vector<int64_t> anc;
-    std::vector<Split> splits;
-    std::vector<int64_t> sub;
     char msg[256];
+    static const char *const kWhy[] = {"", "a cigar op runs past the sequences", "the cigar does not span the sequences",
+                                       "an anchor is out of order or out of range", "bad sequence lengths"};
     for (int64_t a = a0; a < a1; a++) {
-        const int64_t lX = in.off_x[a + 1] - in.off_x[a], lY = in.off_y[a + 1] - in.off_y[a];
-        const uint8_t *sx = in.seq_x + in.off_x[a], *sy = in.seq_y + in.off_y[a];
-        if (lX < 0 || lY < 0 || lX > INT32_MAX / 4 || lY > INT32_MAX / 4) {
-            snprintf(msg, sizeof(msg), "alignment %lld: bad sequence lengths %lld %lld", (long long) a, (long long) lX,
-                     (long long) lY);
+        AlnInput ai;
+        ai.lX = in.off_x[a + 1] - in.off_x[a];
+        ai.lY = in.off_y[a + 1] - in.off_y[a];
+        ai.sx = in.seq_x + in.off_x[a];
+        ai.sy = in.seq_y + in.off_y[a];
+        if (in.ops != nullptr) {
+            ai.ops = in.ops + in.off_ops[a];
+            ai.lens = in.lens + in.off_ops[a];
+            ai.n_ops = in.off_ops[a + 1] - in.off_ops[a];
+            ai.anc = nullptr;
+            ai.n_anc = 0;
+        } else {
+            ai.ops = nullptr;
+            ai.lens = nullptr;
+            ai.n_ops = 0;
+            ai.anc = in.anchors + 2 * in.off_anc[a];
+            ai.n_anc = in.off_anc[a + 1] - in.off_anc[a];
+        }
+        const int bad = plan_core::validate(ai);
+        if (bad) {
+            snprintf(msg, sizeof(msg), "alignment %lld (%lld x %lld): %s", (long long) a, (long long) ai.lX,
+                     (long long) ai.lY, kWhy[bad]);
             pc.error = msg;
             return;
         }
-        anc.clear();
-        if (in.ops != nullptr) {
-            int64_t j = 0, k = 0;
-            for (int64_t o = in.off_ops[a]; o < in.off_ops[a + 1]; o++) {
-                const int op = in.ops[o];
-                const int64_t len = in.lens[o];
-                if (op > 2 || len < 0 || (op != 2 && j + len > lX) || (op != 1 && k + len > lY)) {
-                    snprintf(msg, sizeof(msg), "alignment %lld: cigar op %d len %lld runs past the sequences", (long long) a,
-                             op, (long long) len);
-                    pc.error = msg;
-                    return;
-                }
-                if (op == 0) {
-                    for (int64_t l = 0; l < len; l++) {
-                        const uint8_t cx = upper_of(sx[j + l]), cy = upper_of(sy[k + l]);
-                        if (cx == cy && cx != 'N') {
-                            anc.push_back(j + l);
-                            anc.push_back(k + l);
-                        }
-                    }
-                }
-                if (op != 2) j += len;
-                if (op != 1) k += len;
-            }
-            if (j != lX || k != lY) {  // checkPairwiseAlignment in the reference
-                snprintf(msg, sizeof(msg), "alignment %lld: cigar spans %lld x %lld but the sequences are %lld x %lld",
-                         (long long) a, (long long) j, (long long) k, (long long) lX, (long long) lY);
-                pc.error = msg;
-                return;
-            }
-        } else {
-            int64_t px = -1, py = -1;
-            for (int64_t o = in.off_anc[a]; o < in.off_anc[a + 1]; o++) {
-                const int64_t x = in.anchors[2 * o], y = in.anchors[2 * o + 1];
-                if (x <= px || y <= py || x >= lX || y >= lY) {  // band_construct's (compiled-out) asserts :159-164
-                    snprintf(msg, sizeof(msg), "alignment %lld: anchor (%lld,%lld) out of order or out of range",
-                             (long long) a, (long long) x, (long long) y);
-                    pc.error = msg;
-                    return;
-                }
-                anc.push_back(x);
-                anc.push_back(y);
-                px = x;
-                py = y;
-            }
-        }
-        const int64_t n_anc = (int64_t) anc.size() / 2;
+        // anchors, kept for introspection
         pc.anchor_off.push_back((int64_t) pc.anchors.size() / 2);
-        pc.anchors.insert(pc.anchors.end(), anc.begin(), anc.end());
-        pc.aln_first_region.push_back((int64_t) pc.regions.size());
-
-        // getSplitPoints (:1040-1067)
-        splits.clear();
         {
-            int64_t x1 = 0, y1 = 0, x2 = 0, y2 = 0;
-            for (int64_t i = 0; i < n_anc; i++) {
-                const int64_t x3 = anc[2 * i], y3 = anc[2 * i + 1];
-                split_gap(x1, y1, x2, y2, x3, y3, splits, p.split_matrix_bigger_than, p.ragged_left && i == 0);
-                x2 = x3 + 1;
-                y2 = y3 + 1;
-            }
-            if (!split_gap(x1, y1, x2, y2, lX, lY, splits, p.split_matrix_bigger_than, p.ragged_left && n_anc == 0) ||
-                !p.ragged_right) {
-                splits.push_back({x1, y1, lX, lY});
+            AnchorStream st;
+            int64_t x, y;
+            while (st.next(ai, x, y)) {
+                pc.anchors.push_back(x);
+                pc.anchors.push_back(y);
             }
         }
-        // regions (:1091-1122)
-        int64_t j = 0;
-        for (size_t i = 0; i < splits.size(); i++) {
-            const Split &sp = splits[i];
-            sub.clear();
-            while (j < n_anc && anc[2 * j] + anc[2 * j + 1] < sp.x2 + sp.y2) {
-                sub.push_back(anc[2 * j] - sp.x1);
-                sub.push_back(anc[2 * j + 1] - sp.y1);
-                j++;
-            }
-            plan_region(pc, p, (int32_t) (a - a0), sp, sub.data(), (int64_t) sub.size() / 2, p.ragged_left || i > 0,
-                        p.ragged_right || i + 1 < splits.size(), in.off_x[a], in.off_y[a]);
-        }
+        pc.aln_first_region.push_back((int64_t) pc.regions.size());
+        plan_core::for_each_region(ai, p, [&](const Split &sp, const AnchorStream &cur, bool rl, bool rr) {
+            plan_region(pc, p, ai, (int32_t) (a - a0), sp, cur, rl, rr, in.off_x[a], in.off_y[a]);
+        });
     }
 }
 
@@ -298,13 +179,9 @@ int build_plan(const mab_params *p, const BatchInput &in, int n_threads, mab_pla
         mab_set_error("mab_plan: null argument");
         return MAB_E_ARG;
     }
-    if (p->diagonal_expansion < 0 || p->diagonal_expansion % 2 != 0 || p->traceback_diagonals < 1 ||
-        p->min_diags_between_traceback < 2 || p->traceback_diagonals + 1 >= p->min_diags_between_traceback ||
-        p->split_matrix_bigger_than < 0 || !(p->threshold >= 0.0 && p->threshold <= 1.0)) {
-        // the prerequisites asserted at pairwiseAligner.c:643-647 and 588-589
-        mab_set_error("mab_plan: invalid parameters (expansion must be even and >= 0, traceback_diagonals >= 1, "
-                      "traceback_diagonals + 1 < min_diags_between_traceback, 0 <= threshold <= 1)");
-        return MAB_E_ARG;
+    {
+        const int prc = mab_params_validate(p);
+        if (prc) return prc;
     }
     if (n_threads <= 0) n_threads = (int) std::thread::hardware_concurrency();
     if (n_threads <= 0) n_threads = 1;
@@ -473,6 +350,18 @@ int build_plan(const mab_params *p, const BatchInput &in, int n_threads, mab_pla
 
 }  // namespace
 
+int mab_params_validate(const mab_params *p) {
+    if (p->diagonal_expansion < 0 || p->diagonal_expansion % 2 != 0 || p->traceback_diagonals < 1 ||
+        p->min_diags_between_traceback < 2 || p->traceback_diagonals + 1 >= p->min_diags_between_traceback ||
+        p->split_matrix_bigger_than < 0 || !(p->threshold >= 0.0 && p->threshold <= 1.0)) {
+        // the prerequisites asserted at pairwiseAligner.c:643-647 and 588-589
+        mab_set_error("mab_plan: invalid parameters (expansion must be even and >= 0, traceback_diagonals >= 1, "
+                      "traceback_diagonals + 1 < min_diags_between_traceback, 0 <= threshold <= 1)");
+        return MAB_E_ARG;
+    }
+    return MAB_OK;
+}
+
 extern "C" void mab_params_default(mab_params *p) {
     // pairwiseAlignmentBandingParameters_construct (:1144-1157) with the overrides every margin* call site applies
     p->threshold = 0.01;
@@ -528,6 +417,10 @@ extern "C" int mab_plan_get_info(const mab_plan *plan, mab_plan_info *info) {
 
 extern "C" int mab_plan_write_blob(const mab_plan *plan, void *dst, int64_t dst_bytes) {
     if (plan == nullptr || dst == nullptr) return MAB_E_ARG;
+    if (plan->d_blob != nullptr) {
+        mab_set_error("mab_plan_write_blob: this plan was built on the device; its blob is mab_plan_device_blob()");
+        return MAB_E_ARG;
+    }
     const BlobHeader &h = plan->hdr;
     if (dst_bytes < h.blob_bytes) {
         mab_set_error("mab_plan_write_blob: need %lld bytes, got %lld", (long long) h.blob_bytes, (long long) dst_bytes);
@@ -555,7 +448,7 @@ extern "C" int mab_plan_write_blob(const mab_plan *plan, void *dst, int64_t dst_
 }
 
 extern "C" int64_t mab_plan_anchors(const mab_plan *plan, int64_t aln, int64_t *out_xy, int64_t cap_pairs) {
-    if (plan == nullptr || aln < 0 || aln >= plan->hdr.n_alignments) return MAB_E_ARG;
+    if (plan == nullptr || plan->d_blob != nullptr || aln < 0 || aln >= plan->hdr.n_alignments) return MAB_E_ARG;
     const int64_t a0 = plan->anchor_off[aln], a1 = plan->anchor_off[aln + 1];
     for (int64_t i = a0; i < a1 && i - a0 < cap_pairs; i++) {
         out_xy[2 * (i - a0)] = plan->anchors[2 * i];
@@ -565,7 +458,7 @@ extern "C" int64_t mab_plan_anchors(const mab_plan *plan, int64_t aln, int64_t *
 }
 
 extern "C" int64_t mab_plan_regions(const mab_plan *plan, int64_t *out5, int64_t cap_rows) {
-    if (plan == nullptr) return MAB_E_ARG;
+    if (plan == nullptr || plan->d_blob != nullptr) return MAB_E_ARG;
     const int64_t n = (int64_t) plan->regions.size();
     for (int64_t i = 0; i < n && i < cap_rows; i++) {
         const RegionDesc &r = plan->regions[i];
@@ -579,7 +472,8 @@ extern "C" int64_t mab_plan_regions(const mab_plan *plan, int64_t *out5, int64_t
 }
 
 extern "C" int64_t mab_plan_band(const mab_plan *plan, int64_t region, int64_t *out2, int64_t cap_rows) {
-    if (plan == nullptr || region < 0 || region >= (int64_t) plan->regions.size()) return MAB_E_ARG;
+    if (plan == nullptr || plan->d_blob != nullptr || region < 0 || region >= (int64_t) plan->regions.size())
+        return MAB_E_ARG;
     const RegionDesc &r = plan->regions[region];
     const int64_t D = r.lX + r.lY;
     for (int64_t d = 0; d <= D && d < cap_rows; d++) {
@@ -592,7 +486,7 @@ extern "C" int64_t mab_plan_band(const mab_plan *plan, int64_t region, int64_t *
 }
 
 extern "C" int64_t mab_plan_tracebacks(const mab_plan *plan, int64_t *out5, int64_t cap_rows) {
-    if (plan == nullptr) return MAB_E_ARG;
+    if (plan == nullptr || plan->d_blob != nullptr) return MAB_E_ARG;
     const int64_t n = (int64_t) plan->tbs.size();
     for (int64_t i = 0; i < n && i < cap_rows; i++) {
         const TracebackDesc &t = plan->tbs[i];

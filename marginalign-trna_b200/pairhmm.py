@@ -192,18 +192,49 @@ class Plan:
             pass
 
 
-@dataclass
 class PosteriorPairs:
     """CSR result of posterior mode: alignment i owns rows offsets[i]:offsets[i+1] of (x, y, p_int), in the order
-    the reference's getAlignedPairsUsingAnchors returns them; p_int = floor(min(p,1) * 1e7)."""
-    offsets: np.ndarray
-    x: np.ndarray
-    y: np.ndarray
-    p: np.ndarray
+    the reference's getAlignedPairsUsingAnchors returns them; p_int = floor(min(p,1) * 1e7).
+
+    The engine returns one block per chunk (pinned host memory filled by D2H copies); .x / .y / .p concatenate the
+    blocks on first use, .pairs(i) reads the owning block directly."""
+
+    def __init__(self, offsets, x=None, y=None, p=None, blocks=None):
+        self.offsets = np.asarray(offsets, dtype=np.int64)
+        if blocks is None:
+            blocks = [(0, int(len(self.offsets) - 1), 0, np.asarray(x), np.asarray(y), np.asarray(p))]
+        self._blocks = blocks  # (first alignment, end alignment, first pair, x, y, p)
+        self._flat = None
+        self._starts = np.array([b[0] for b in blocks], dtype=np.int64)
+
+    def _cat(self):
+        if self._flat is None:
+            if len(self._blocks) == 1:
+                self._flat = self._blocks[0][3:6]
+            else:
+                self._flat = tuple(np.concatenate([b[k] for b in self._blocks]) for k in (3, 4, 5))
+        return self._flat
+
+    @property
+    def x(self):
+        return self._cat()[0]
+
+    @property
+    def y(self):
+        return self._cat()[1]
+
+    @property
+    def p(self):
+        return self._cat()[2]
+
+    @property
+    def n_pairs(self):
+        return int(self.offsets[-1])
 
     def pairs(self, i):
-        s = slice(self.offsets[i], self.offsets[i + 1])
-        return np.stack([self.p[s].astype(np.int64), self.x[s].astype(np.int64), self.y[s].astype(np.int64)], axis=1)
+        b = self._blocks[int(np.searchsorted(self._starts, i, side="right")) - 1]
+        s = slice(self.offsets[i] - b[2], self.offsets[i + 1] - b[2])
+        return np.stack([b[5][s].astype(np.int64), b[3][s].astype(np.int64), b[4][s].astype(np.int64)], axis=1)
 
 
 def _torch():
@@ -219,24 +250,90 @@ def require_cuda():
 
 
 class DevicePlan:
-    """A plan whose blob is resident in HBM, plus its scratch workspace."""
+    """A plan whose blob is resident in HBM, plus its scratch workspace.
 
-    def __init__(self, plan: Plan, device, expectations=False, stream=None):
+    Two ways to get one: from a host-built Plan (the blob is copied over PCIe), or DevicePlan.build_on_device, which
+    uploads only the raw inputs and runs the planner on the GPU (mab_plan_build_device)."""
+
+    def __init__(self, plan: Plan, device, expectations=False, stream=None, _resident=None):
         torch = require_cuda()
         self.plan = plan
         self.device = device
-        nb = plan.info.blob_bytes
-        self.h_blob = torch.empty(nb, dtype=torch.uint8, pin_memory=True)
-        plan.write_blob(self.h_blob.data_ptr(), nb)
-        self.d_blob = torch.empty(nb, dtype=torch.uint8, device=device)
-        with torch.cuda.stream(stream) if stream is not None else _null():
-            self.d_blob.copy_(self.h_blob, non_blocking=True)
+        if _resident is None:
+            nb = plan.info.blob_bytes
+            self.h_blob = torch.empty(nb, dtype=torch.uint8, pin_memory=True)
+            plan.write_blob(self.h_blob.data_ptr(), nb)
+            self.d_blob = torch.empty(nb, dtype=torch.uint8, device=device)
+            with torch.cuda.stream(stream) if stream is not None else _null():
+                self.d_blob.copy_(self.h_blob, non_blocking=True)
+            self.blob_ptr = self.d_blob.data_ptr()
+            self.h2d_bytes = nb
+        else:
+            self.d_blob, self.blob_ptr, self.h2d_bytes, self._inputs = _resident
         ws = plan.info.workspace_bytes_expectations if expectations else plan.info.workspace_bytes_posteriors
         self.ws_bytes = int(ws)
         self.d_ws = torch.empty(self.ws_bytes + 256, dtype=torch.uint8, device=device)
         # 256-byte aligned view of the workspace
         self.ws_ptr = (self.d_ws.data_ptr() + 255) & ~255
-        self.h2d_bytes = nb
+
+    @classmethod
+    def build_on_device(cls, batch, params, device, expectations=False, staging=None):
+        """Uploads bases + cigars of `batch` (one pinned staging buffer, one H2D copy) and plans on the GPU."""
+        torch = require_cuda()
+        L = capi.load()
+        n = batch.n
+        parts = [np.ascontiguousarray(batch.off_x, dtype=np.int64), np.ascontiguousarray(batch.off_y, dtype=np.int64),
+                 np.ascontiguousarray(batch.off_ops, dtype=np.int64), np.ascontiguousarray(batch.lens, dtype=np.int32),
+                 np.ascontiguousarray(batch.seq_x, dtype=np.uint8), np.ascontiguousarray(batch.seq_y, dtype=np.uint8),
+                 np.ascontiguousarray(batch.ops, dtype=np.uint8)]
+        offs, total = [], 0
+        for a in parts:
+            offs.append(total)
+            total = (total + a.nbytes + 255) & ~255
+        total = max(total, 256)
+        h_in = staging.pinned(total) if staging is not None else torch.empty(total, dtype=torch.uint8, pin_memory=True)
+        hv = h_in.numpy()
+        for a, o in zip(parts, offs):
+            if a.nbytes:
+                hv[o:o + a.nbytes] = a.view(np.uint8).reshape(-1)
+        d_in = torch.empty(total + 256, dtype=torch.uint8, device=device)
+        base = (d_in.data_ptr() + 255) & ~255
+        d_view = d_in[base - d_in.data_ptr():base - d_in.data_ptr() + total]
+        d_view.copy_(h_in[:total], non_blocking=True)
+        ptr = [base + o for o in offs]
+        p = params.to_c()
+        len_x, len_y = int(batch.off_x[-1]) if n else 0, int(batch.off_y[-1]) if n else 0
+        need = int(L.mab_plan_device_arena_hint(C.byref(p), n, len_x, len_y))
+        stream = C.c_void_p(torch.cuda.current_stream(device).cuda_stream)
+        for _ in range(3):
+            arena = torch.empty(need + 256, dtype=torch.uint8, device=device)
+            aptr = (arena.data_ptr() + 255) & ~255
+            h, needed = capi.vp(), C.c_int64(0)
+            rc = L.mab_plan_build_device(C.byref(p), n, ptr[4], ptr[0], len_x, ptr[5], ptr[1], len_y, ptr[6], ptr[3],
+                                         ptr[2], None, None, aptr, need, stream, C.byref(h), C.byref(needed))
+            if rc == -4 and needed.value > need:  # MAB_E_CAPACITY: retry with the exact requirement
+                need = int(needed.value)
+                del arena
+                continue
+            capi.check(rc)
+            break
+        else:
+            raise RuntimeError("mab_plan_build_device: arena sizing did not converge")
+        plan = Plan(h)
+        return cls(plan, device, expectations=expectations, _resident=(arena, aptr, total, (d_in, h_in)))
+
+
+class _Staging:
+    """Grow-only pinned host buffer reused between chunks (page-locking memory is slow; do it once)."""
+
+    def __init__(self):
+        self.buf = None
+
+    def pinned(self, nbytes):
+        torch = _torch()
+        if self.buf is None or self.buf.numel() < nbytes:
+            self.buf = torch.empty(int(nbytes * 1.25) + 4096, dtype=torch.uint8, pin_memory=True)
+        return self.buf[:nbytes]
 
 
 class _null:
@@ -248,32 +345,58 @@ class _null:
 
 
 class PairHmmEngine:
-    """Runs batches on one GPU.  `max_cells` bounds the number of DP cells resident at once (80 B of HBM each)."""
+    """Runs batches on one GPU.  `max_cells` bounds the number of DP cells resident at once (28 B of HBM each in
+    posterior mode, 80 B in expectation mode).  plan_on = "device" (default): raw inputs are uploaded and the plan is
+    built on the GPU; "host": the C++ host planner builds the blob and it is copied over PCIe."""
 
-    def __init__(self, device=None, max_cells=200_000_000, plan_threads=0):
+    def __init__(self, device=None, max_cells=400_000_000, plan_threads=0, plan_on="device"):
         torch = require_cuda()
         self.torch = torch
         self.device = torch.device(device if device is not None else "cuda:%d" % torch.cuda.current_device())
         self.max_cells = int(max_cells)
         self.plan_threads = plan_threads
+        if plan_on not in ("device", "host"):
+            raise ValueError("plan_on must be 'device' or 'host'")
+        self.plan_on = plan_on
         self.last_stats = {}
+        self._staging = _Staging()
 
     # ---------------------------------------------------------------- chunking
     def _chunks(self, batch, params):
-        # cells ~ diagonals x band width; band width ~ expansion + 2 near anchors (exact count comes from the plan)
+        """Contiguous alignment ranges of at most ~max_cells estimated DP cells (cells ~ diagonals x band width; the
+        exact count comes from the plan)."""
+        if batch.n == 0:
+            return [(0, 0)]
         est = ((batch.off_x[1:] - batch.off_x[:-1]) + (batch.off_y[1:] - batch.off_y[:-1]) + 1) * (
             params.diagonal_expansion + 4)
-        bounds, acc, start = [], 0, 0
-        for i, c in enumerate(est):
-            if acc + c > self.max_cells and i > start:
-                bounds.append((start, i))
-                start, acc = i, 0
-            acc += int(c)
-        bounds.append((start, batch.n))
+        cum = np.cumsum(est.astype(np.int64))
+        bounds, start, base = [], 0, 0
+        while start < batch.n:
+            end = int(np.searchsorted(cum, base + self.max_cells, side="right"))
+            end = max(end, start + 1)
+            bounds.append((start, min(end, batch.n)))
+            start = bounds[-1][1]
+            base = int(cum[start - 1])
         return bounds
 
     def _stream_ptr(self):
         return C.c_void_p(self.torch.cuda.current_stream(self.device).cuda_stream)
+
+    def _device_plans(self, batch, params, expectations):
+        """Yields one DevicePlan per chunk.  Host planning of chunk k+1 overlaps the GPU work on chunk k."""
+        chunks = self._chunks(batch, params)
+        if self.plan_on == "device":
+            for b in chunks:
+                yield DevicePlan.build_on_device(batch.slice(*b), params, self.device, expectations, self._staging)
+            return
+        with ThreadPoolExecutor(1) as pool:
+            make = lambda b: Plan.from_batch(batch.slice(*b), params, self.plan_threads)
+            fut = pool.submit(make, chunks[0])
+            for ci in range(len(chunks)):
+                plan = fut.result()
+                if ci + 1 < len(chunks):
+                    fut = pool.submit(make, chunks[ci + 1])
+                yield DevicePlan(plan, self.device, expectations)
 
     # ---------------------------------------------------------------- posteriors
     def posteriors_device(self, model, dplan):
@@ -282,13 +405,13 @@ class PairHmmEngine:
         n = dplan.plan.info.n_alignments
         d_off = torch.empty(n + 1, dtype=torch.int64, device=self.device)
         d_np = torch.empty(1, dtype=torch.int64, device=self.device)
-        capi.check(L.mab_posteriors_compute(model._h, dplan.plan._h, dplan.d_blob.data_ptr(), dplan.ws_ptr,
+        capi.check(L.mab_posteriors_compute(model._h, dplan.plan._h, dplan.blob_ptr, dplan.ws_ptr,
                                             dplan.ws_bytes, d_off.data_ptr(), d_np.data_ptr(), self._stream_ptr()))
         total = int(d_np.item())  # one sync: the output size is data dependent
         d_x = torch.empty(total, dtype=torch.int32, device=self.device)
         d_y = torch.empty(total, dtype=torch.int32, device=self.device)
         d_p = torch.empty(total, dtype=torch.int32, device=self.device)
-        capi.check(L.mab_posteriors_emit(dplan.plan._h, dplan.d_blob.data_ptr(), dplan.ws_ptr, dplan.ws_bytes,
+        capi.check(L.mab_posteriors_emit(dplan.plan._h, dplan.blob_ptr, dplan.ws_ptr, dplan.ws_bytes,
                                          d_x.data_ptr(), d_y.data_ptr(), d_p.data_ptr(), total, self._stream_ptr()))
         return d_off, d_x, d_y, d_p
 
@@ -296,38 +419,43 @@ class PairHmmEngine:
         """Posterior match probabilities of every alignment of `batch` (host in, host out)."""
         params = params or AlignmentParameters()
         torch = self.torch
-        offs, xs, ys, ps = [np.zeros(1, dtype=np.int64)], [], [], []
+        offs, blocks = [np.zeros(1, dtype=np.int64)], []
         stats = dict(cells=0, regions=0, diagonals=0, h2d_bytes=0, d2h_bytes=0, chunks=0)
-        chunks = self._chunks(batch, params)
-        with torch.cuda.device(self.device), ThreadPoolExecutor(1) as pool:
-            def make(bounds):
-                sub = batch if bounds == (0, batch.n) else batch.subset(np.arange(bounds[0], bounds[1]))
-                return Plan.from_batch(sub, params, self.plan_threads)
-            fut = pool.submit(make, chunks[0])
-            for ci in range(len(chunks)):
-                plan = fut.result()
-                if ci + 1 < len(chunks):
-                    fut = pool.submit(make, chunks[ci + 1])  # plan the next chunk while the GPU works on this one
-                dplan = DevicePlan(plan, self.device)
+        pending = []  # D2H copies in flight: (first alignment, n alignments, pinned tensors)
+        first = 0
+        with torch.cuda.device(self.device):
+            for dplan in self._device_plans(batch, params, False):
+                info = dplan.plan.info
                 d_off, d_x, d_y, d_p = self.posteriors_device(model, dplan)
-                off = d_off.cpu().numpy()
-                offs.append(off[1:] + offs[-1][-1])
-                xs.append(d_x.cpu().numpy())
-                ys.append(d_y.cpu().numpy())
-                ps.append(d_p.cpu().numpy())
-                stats["cells"] += plan.info.n_cells
-                stats["regions"] += plan.info.n_regions
-                stats["diagonals"] += plan.info.n_diagonals
+                # pinned host blocks (torch's pinned allocator recycles them between calls), asynchronous D2H
+                host = [torch.empty(t.shape, dtype=t.dtype, pin_memory=True) for t in (d_off, d_x, d_y, d_p)]
+                for h, t in zip(host, (d_off, d_x, d_y, d_p)):
+                    h.copy_(t, non_blocking=True)
+                ev = torch.cuda.Event()
+                ev.record(torch.cuda.current_stream(self.device))
+                pending.append((first, info.n_alignments, host, ev, (d_off, d_x, d_y, d_p)))
+                first += info.n_alignments
+                stats["cells"] += info.n_cells
+                stats["regions"] += info.n_regions
+                stats["diagonals"] += info.n_diagonals
                 stats["h2d_bytes"] += dplan.h2d_bytes
-                stats["d2h_bytes"] += off.nbytes + 3 * xs[-1].nbytes
                 stats["chunks"] += 1
                 del dplan
+            for a0, na, host, ev, _keep in pending:
+                ev.synchronize()
+                off = host[0].numpy()
+                base = int(offs[-1][-1])
+                offs.append(off[1:] + base)
+                blocks.append((a0, a0 + na, base, host[1].numpy(), host[2].numpy(), host[3].numpy()))
+                stats["d2h_bytes"] += sum(h.numel() * h.element_size() for h in host)
+        if not blocks:
+            blocks = [(0, 0, 0, np.zeros(0, np.int32), np.zeros(0, np.int32), np.zeros(0, np.int32))]
         self.last_stats = stats
-        return PosteriorPairs(np.concatenate(offs), np.concatenate(xs), np.concatenate(ys), np.concatenate(ps))
+        return PosteriorPairs(np.concatenate(offs), blocks=blocks)
 
     # ---------------------------------------------------------------- expectations
     def expectations_device(self, model, dplan, d_out):
-        capi.check(capi.load().mab_expectations(model._h, dplan.plan._h, dplan.d_blob.data_ptr(), dplan.ws_ptr,
+        capi.check(capi.load().mab_expectations(model._h, dplan.plan._h, dplan.blob_ptr, dplan.ws_ptr,
                                                 dplan.ws_bytes, d_out.data_ptr(), self._stream_ptr()))
 
     def get_expectations_using_anchors(self, model, batch, params=None, pseudo_count=1e-12, as_hmm=False):
@@ -341,24 +469,15 @@ class PairHmmEngine:
         init = np.full(model.n_expectations, pseudo_count)
         init[-1] = 0.0
         stats = dict(cells=0, regions=0, diagonals=0, h2d_bytes=0, d2h_bytes=0, chunks=0)
-        chunks = self._chunks(batch, params)
-        with torch.cuda.device(self.device), ThreadPoolExecutor(1) as pool:
+        with torch.cuda.device(self.device):
             d_out = torch.from_numpy(init).to(self.device)
-
-            def make(bounds):
-                sub = batch if bounds == (0, batch.n) else batch.subset(np.arange(bounds[0], bounds[1]))
-                return Plan.from_batch(sub, params, self.plan_threads)
-            fut = pool.submit(make, chunks[0])
-            for ci in range(len(chunks)):
-                plan = fut.result()
-                if ci + 1 < len(chunks):
-                    fut = pool.submit(make, chunks[ci + 1])
-                dplan = DevicePlan(plan, self.device, expectations=True)
+            for dplan in self._device_plans(batch, params, True):
+                info = dplan.plan.info
                 self.expectations_device(model, dplan, d_out)
                 torch.cuda.current_stream(self.device).synchronize()
-                stats["cells"] += plan.info.n_cells
-                stats["regions"] += plan.info.n_regions
-                stats["diagonals"] += plan.info.n_diagonals
+                stats["cells"] += info.n_cells
+                stats["regions"] += info.n_regions
+                stats["diagonals"] += info.n_diagonals
                 stats["h2d_bytes"] += dplan.h2d_bytes
                 stats["chunks"] += 1
                 del dplan

@@ -62,6 +62,15 @@ class AlignmentBatch:
         ln, _ = take(self.lens, self.off_ops)
         return AlignmentBatch(sx, ox, sy, oy, ops, ln, oo)
 
+    def slice(self, a, b):
+        """Alignments a..b-1 as a batch of views (no copy of the sequence data, offsets rebased)."""
+        a, b = int(a), int(b)
+        if a == 0 and b == self.n:
+            return self
+        ox, oy, oo = self.off_x[a:b + 1], self.off_y[a:b + 1], self.off_ops[a:b + 1]
+        return AlignmentBatch(self.seq_x[ox[0]:ox[-1]], ox - ox[0], self.seq_y[oy[0]:oy[-1]], oy - oy[0],
+                              self.ops[oo[0]:oo[-1]], self.lens[oo[0]:oo[-1]], oo - oo[0])
+
     @staticmethod
     def from_lists(xs, ys, cigars):
         """xs, ys: bytes/str per alignment; cigars: (ops, lens) per alignment."""

@@ -231,3 +231,78 @@ def test_full_size_properties(engine, golden):
     assert_exp_match(np.concatenate([ec[0], ec[1], [ec[2]]]), tot, "additive", rtol=1e-9)
     # transitions into match consume one (x,y) pair each: their expected count is bounded by min(lX, lY) summed
     assert ec[0].reshape(5, 5)[:, 0].sum() <= np.minimum(lens_x, lens_y).sum()
+
+
+def _blob_arrays(raw):
+    """Splits a plan blob (host bytes) into its arrays using the header offsets (csrc/mab_internal.h BlobHeader)."""
+    h = raw[:256].view(np.int64)
+    names = ["magic", "n_alignments", "n_regions", "n_diagonals", "n_cells", "n_tracebacks", "n_totals", "n_anchors",
+             "max_width", "len_sym_x", "len_sym_y", "off_regions", "off_diags", "off_tracebacks", "off_totals",
+             "off_sym_x", "off_sym_y", "off_order_fwd", "off_order_bwd", "off_aln_region", "blob_bytes", "n_edge_cells",
+             "n_full_cells"]
+    H = {k: int(h[i]) for i, k in enumerate(names)}
+    cut = lambda off, nbytes: raw[off:off + nbytes]
+    return H, {
+        "regions": cut(H["off_regions"], H["n_regions"] * 64),
+        "diags": cut(H["off_diags"], (H["n_diagonals"] + 1) * 16),
+        "tracebacks": cut(H["off_tracebacks"], H["n_tracebacks"] * 32),
+        "totals": cut(H["off_totals"], H["n_totals"] * 16),
+        "sym_x": cut(H["off_sym_x"] - 16, H["len_sym_x"] + 32),
+        "sym_y": cut(H["off_sym_y"] - 16, H["len_sym_y"] + 32),
+        "order_fwd": cut(H["off_order_fwd"], H["n_regions"] * 4),
+        "order_bwd": cut(H["off_order_bwd"], H["n_tracebacks"] * 4),
+        "aln_region": cut(H["off_aln_region"], (H["n_alignments"] + 1) * 8),
+    }
+
+
+def _assert_device_plan_equals_host_plan(batch, P, device):
+    import torch
+    hp = mab.Plan.from_batch(batch, P)
+    hb = np.zeros(hp.info.blob_bytes, dtype=np.uint8)
+    hp.write_blob(hb.ctypes.data, hb.nbytes)
+    dp = mab.DevicePlan.build_on_device(batch, P, device)
+    torch.cuda.synchronize()
+    off = dp.blob_ptr - dp.d_blob.data_ptr()
+    db = dp.d_blob[off:off + dp.plan.info.blob_bytes].cpu().numpy()
+    Hh, Ah = _blob_arrays(hb)
+    Hd, Ad = _blob_arrays(db)
+    for k in ("n_alignments", "n_regions", "n_diagonals", "n_cells", "n_tracebacks", "n_totals", "max_width",
+              "len_sym_x", "len_sym_y", "n_edge_cells", "n_full_cells"):
+        assert Hh[k] == Hd[k], (k, Hh[k], Hd[k])
+    for k in Ah:
+        assert np.array_equal(Ah[k], Ad[k]), k
+    for f in ("n_cells", "n_regions", "workspace_bytes_posteriors", "workspace_bytes_expectations"):
+        assert getattr(hp.info, f) == getattr(dp.plan.info, f), f
+
+
+def test_device_planner_matches_host_planner(engine, golden):
+    """mab_plan_build_device must produce the host planner's blob, array by array, byte for byte: tRNA batch, long reads
+    with several checkpoints, small split limit (many regions per alignment), expansion 0, N / lower-case bases, and
+    every cigar-driven golden case."""
+    dev = engine.device
+    _assert_device_plan_equals_host_plan(mab.synth.make_trna_batch(5000, seed=77), mab.AlignmentParameters(), dev)
+    long_b = mab.synth.make_long_batch(6, read_len=4000, genome_len=60_000, seed=12)
+    for P in (mab.AlignmentParameters(split_matrix_bigger_than=300),
+              mab.AlignmentParameters(split_matrix_bigger_than=3),
+              mab.AlignmentParameters(diagonal_expansion=0, split_matrix_bigger_than=1),
+              mab.AlignmentParameters(diagonal_expansion=60, split_matrix_bigger_than=100, ragged_left=False,
+                                      ragged_right=False)):
+        _assert_device_plan_equals_host_plan(long_b, P, dev)
+    cases = [c for c in golden.cases if "anchors" not in c]
+    b = mab.AlignmentBatch.from_lists([c["x"] for c in cases], [c["y"] for c in cases],
+                                      [(c["ops"], c["lens"]) for c in cases])
+    for P in (mab.AlignmentParameters(), mab.AlignmentParameters(split_matrix_bigger_than=10)):
+        _assert_device_plan_equals_host_plan(b, P, dev)
+    _assert_device_plan_equals_host_plan(mab.AlignmentBatch.from_lists([], [], []), mab.AlignmentParameters(), dev)
+    with pytest.raises(RuntimeError, match="does not span"):
+        mab.DevicePlan.build_on_device(mab.AlignmentBatch.from_lists(["ACGT"], ["ACGT"], [([0], [3])]),
+                                       mab.AlignmentParameters(), dev)
+
+
+def test_host_and_device_planned_runs_agree(golden):
+    b = mab.synth.make_trna_batch(400, seed=31)
+    model = gpu_model(golden.model_arrays("fixture5asym"))
+    r1 = mab.PairHmmEngine(plan_on="host").get_aligned_pairs_using_anchors(model, b)
+    r2 = mab.PairHmmEngine(plan_on="device", max_cells=300_000).get_aligned_pairs_using_anchors(model, b)
+    for a in ("offsets", "x", "y", "p"):
+        assert np.array_equal(getattr(r1, a), getattr(r2, a)), a

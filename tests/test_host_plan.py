@@ -88,7 +88,7 @@ def test_plan_is_thread_count_independent():
 
 def test_plan_rejects_bad_input():
     P = mab.AlignmentParameters()
-    with pytest.raises(RuntimeError, match="cigar spans"):
+    with pytest.raises(RuntimeError, match="does not span"):
         mab.Plan.from_batch(mab.AlignmentBatch.from_lists(["ACGT"], ["ACGT"], [([0], [3])]), P)
     with pytest.raises(RuntimeError, match="runs past"):
         mab.Plan.from_batch(mab.AlignmentBatch.from_lists(["ACGT"], ["ACGT"], [([0], [9])]), P)
