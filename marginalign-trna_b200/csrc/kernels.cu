@@ -15,11 +15,15 @@
 //                (doTransitionBackward) is turned into a gather that adds the terms in the scatter's order.
 //   k_totals     one thread per total-probability evaluation (every 10th diagonal of a traceback): the serial
 //                logAdd chain over the cells of a diagonal, in cell order.
-//   k_posterior_count / k_scan / k_emit   per-cell posterior, per-region counts, exclusive scan, ordered compaction.
+//   k_posterior_diag / scan / k_emit_diag   one thread per diagonal: p_int per cell and pair count, device-wide
+//                exclusive scan over the diagonals in emission order, ordered write of the pairs.
 //   k_expect     per-cell transition/emission expectations with in-block reduction.
 #include <cuda_runtime.h>
 
+#include <cub/cub.cuh>
+
 #include <algorithm>
+#include <cmath>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
@@ -37,8 +41,8 @@ thread_local int64_t g_launches = 0;
 
 // Optional per-kernel timing with CUDA events on the launching stream (bench.py's roofline numbers).
 enum KernelId { K_FORWARD = 0, K_BACKWARD, K_TOTALS, K_POSTERIOR, K_SCAN, K_EMIT, K_EXPECT, K_COUNT };
-const char *const kKernelNames[K_COUNT] = {"k_forward", "k_backward", "k_totals", "k_posterior_count", "k_scan",
-                                           "k_emit", "k_expect"};
+const char *const kKernelNames[K_COUNT] = {"k_forward", "k_backward", "k_totals", "k_posterior_diag", "scan+offsets",
+                                           "k_emit_diag", "k_expect"};
 struct TimedLaunch {
     cudaEvent_t start, stop;
     int kernel;
@@ -229,7 +233,7 @@ struct Blob {
     const TracebackDesc *tbs;
     const TotalDesc *totals;
     const uint8_t *sym_x, *sym_y;
-    const int32_t *order_fwd, *order_bwd;
+    const int32_t *order_fwd, *order_bwd, *diag_region;
     const int64_t *aln_region;
 };
 
@@ -246,6 +250,7 @@ __host__ __device__ inline Blob blob_view(const void *base, const BlobHeader &h)
     v.order_fwd = (const int32_t *) (b + h.off_order_fwd);
     v.order_bwd = (const int32_t *) (b + h.off_order_bwd);
     v.aln_region = (const int64_t *) (b + h.off_aln_region);
+    v.diag_region = (const int32_t *) (b + h.off_diag_region);
     return v;
 }
 
@@ -478,130 +483,114 @@ __global__ void k_totals(Blob bl, int n_totals, const double *__restrict__ F, co
 }
 
 // ------------------------------------------------------------------------------------------------ posteriors
+// diagonalCalculationPosteriorMatchProbs (pairwiseAligner.c:585-615) and the ordered pair list, as three flat passes
+// with one thread per DIAGONAL (a diagonal's cells are contiguous; its owner region comes from diag_region):
+//   k_posterior_diag   p_int (or -1) of every cell; number of emitted pairs of the diagonal -> counts[slot]
+//   (device-wide exclusive scan of counts, in place)
+//   k_pair_offsets     per-alignment CSR offsets; k_emit_diag writes the pairs of the diagonal at counts[slot].
+// `slot` orders the diagonals the way the reference's list is ordered: it appends per traceback (ascending), per
+// diagonal descending, per cell in ascending x-y (:594-613, :695-733); alignedPairCoordinateCorrectionFn then pops each
+// region's list from the tail (:1167-1169), i.e. reverses it.  Net order inside a region: tracebacks descending,
+// diagonals ascending, x-y descending; regions (and alignments) ascending.  So slot(d) = diag_base + 1 +
+// (D - from_t) + (d - lo_t - 1) for the traceback t that owns d >= 1, and slot(0) = diag_base (never emits).
 
-// diagonalCalculationPosteriorMatchProbs (pairwiseAligner.c:585-615), one warp per region.  Writes p_int (or -1)
-// per cell and the number of emitted pairs per region.
-__global__ void __launch_bounds__(THREADS_PER_BLOCK)
-k_posterior_count(Blob bl, int n_regions, const double *__restrict__ F, const double *__restrict__ B,
-                  const double *__restrict__ totals, double threshold, int32_t *__restrict__ pint,
-                  int64_t *__restrict__ counts, int *counter) {
-    const int lane = threadIdx.x & 31;
-    for (;;) {
-        const int item = next_item(counter, lane);
-        if (item >= n_regions) break;
-        const int r = bl.order_fwd[item];
-        const RegionDesc rg = bl.regions[r];
-        const DiagDesc *dd = bl.diags + rg.diag_base;
+struct DiagWork {
+    int64_t c0;    // first cell
+    int w;         // cells
+    int d;         // region-local diagonal
+    int xmyL;
+    int64_t slot;
+    uint32_t tot;  // index of the total the reference uses on this diagonal
+    int x1, y1;    // region origin inside the alignment
+};
+
+__device__ __forceinline__ DiagWork diag_work(const Blob &bl, int64_t g) {
+    DiagWork k;
+    const RegionDesc &rg = bl.regions[bl.diag_region[g]];
+    const DiagDesc cur = bl.diags[g];
+    k.c0 = cur.cell_off;
+    k.w = (int) (bl.diags[g + 1].cell_off - cur.cell_off);
+    k.d = (int) (g - rg.diag_base);
+    k.xmyL = cur.xmyL;
+    k.tot = cur.tot_flags & MAB_DIAG_TOT_MASK;
+    k.x1 = rg.x1;
+    k.y1 = rg.y1;
+    k.slot = rg.diag_base;
+    if (k.d >= 1) {
         const int D = rg.lX + rg.lY;
-        int count = 0;
-        for (int j = lane; j < (int) (dd[1].cell_off - dd[0].cell_off); j += 32) pint[dd[0].cell_off + j] = -1;
-        for (int d = 1; d <= D; d++) {
-            const DiagDesc cur = dd[d];
-            const int w = (int) (dd[d + 1].cell_off - cur.cell_off);
-            const double total = totals[cur.tot_flags & MAB_DIAG_TOT_MASK];
-            for (int j = lane; j < w; j += 32) {
-                const int xmy = cur.xmyL + 2 * j;
-                const int x = (d + xmy) >> 1, y = (d - xmy) >> 1;
-                int32_t v = -1;
-                if (x > 0 && y > 0) {
-                    const int64_t c = cur.cell_off + j;
-                    double p = exp(__dsub_rn(__dadd_rn(F[c], B[c]), total));
+        int t = rg.tb_base + rg.n_tb - 1;  // the last traceback owns (lo, D]; walk down to the owner of d
+        TracebackDesc tb = bl.tbs[t];
+        while (k.d <= tb.lo) tb = bl.tbs[--t];
+        k.slot = rg.diag_base + 1 + (D - tb.from) + (k.d - tb.lo - 1);
+    }
+    return k;
+}
+
+__global__ void __launch_bounds__(256)
+k_posterior_diag(Blob bl, int64_t n_diagonals, const double *__restrict__ F, const double *__restrict__ B,
+                 const double *__restrict__ totals, double threshold, double log_reject, int32_t *__restrict__ pint,
+                 int64_t *__restrict__ counts) {
+    const int64_t g = (int64_t) blockIdx.x * blockDim.x + threadIdx.x;
+    if (g > n_diagonals) return;
+    if (g == n_diagonals) {  // sentinel: the scan leaves the total number of pairs here
+        counts[g] = 0;
+        return;
+    }
+    const DiagWork k = diag_work(bl, g);
+    int64_t count = 0;
+    if (k.d >= 1) {
+        const double total = totals[k.tot];
+        for (int j = 0; j < k.w; j++) {
+            const int xmy = k.xmyL + 2 * j;
+            const int x = (k.d + xmy) >> 1, y = (k.d - xmy) >> 1;
+            int32_t v = -1;
+            if (x > 0 && y > 0) {
+                const double s = __dsub_rn(__dadd_rn(F[k.c0 + j], B[k.c0 + j]), total);
+                // exp() only where the pair can pass: s < log(threshold) - 0.1 implies exp(s) < threshold
+                if (s >= log_reject) {
+                    double p = exp(s);
                     if (p >= threshold) {
                         if (p > 1.0) p = 1.0;
                         v = (int32_t) floor(__dmul_rn(p, MAB_PROB_1));
                         count++;
                     }
                 }
-                pint[cur.cell_off + j] = v;
             }
+            pint[k.c0 + j] = v;
         }
-#pragma unroll
-        for (int o = 16; o > 0; o >>= 1) count += __shfl_xor_sync(FULL_MASK, count, o);
-        if (lane == 0) counts[r] = count;
     }
+    counts[k.slot] = count;
 }
 
-// Exclusive scan of the per-region counts (single block), then per-alignment offsets.
-__global__ void k_scan(int64_t *counts, int64_t n_regions, const int64_t *aln_region, int64_t n_aln,
-                       int64_t *pair_off, int64_t *n_pairs) {
-    __shared__ int64_t warp_sums[32];
-    __shared__ int64_t carry;
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nw = blockDim.x >> 5;
-    if (threadIdx.x == 0) carry = 0;
-    __syncthreads();
-    for (int64_t base = 0; base < n_regions; base += blockDim.x) {
-        const int64_t i = base + threadIdx.x;
-        const int64_t v = i < n_regions ? counts[i] : 0;
-        int64_t incl = v;
-#pragma unroll
-        for (int o = 1; o < 32; o <<= 1) {
-            const int64_t n = __shfl_up_sync(FULL_MASK, incl, o);
-            if (lane >= o) incl += n;
-        }
-        if (lane == 31) warp_sums[warp] = incl;
-        __syncthreads();
-        if (warp == 0) {
-            int64_t ws = lane < nw ? warp_sums[lane] : 0;
-#pragma unroll
-            for (int o = 1; o < 32; o <<= 1) {
-                const int64_t n = __shfl_up_sync(FULL_MASK, ws, o);
-                if (lane >= o) ws += n;
-            }
-            warp_sums[lane] = ws;  // inclusive over warps
-        }
-        __syncthreads();
-        const int64_t before = carry + (warp > 0 ? warp_sums[warp - 1] : 0) + incl - v;
-        if (i < n_regions) counts[i] = before;
-        __syncthreads();
-        if (threadIdx.x == 0) carry += warp_sums[nw - 1];
-        __syncthreads();
-    }
-    if (threadIdx.x == 0) {
-        counts[n_regions] = carry;
-        n_pairs[0] = carry;
-    }
-    __syncthreads();
-    for (int64_t a = threadIdx.x; a <= n_aln; a += blockDim.x) pair_off[a] = counts[aln_region[a]];
+__global__ void k_pair_offsets(Blob bl, int64_t n_aln, int64_t n_regions, int64_t n_diagonals,
+                               const int64_t *__restrict__ pos, int64_t *__restrict__ pair_off,
+                               int64_t *__restrict__ n_pairs) {
+    const int64_t a = (int64_t) blockIdx.x * blockDim.x + threadIdx.x;
+    if (a > n_aln) return;
+    const int64_t r0 = bl.aln_region[a];
+    pair_off[a] = r0 < n_regions ? pos[bl.regions[r0].diag_base] : pos[n_diagonals];
+    if (a == 0) n_pairs[0] = pos[n_diagonals];
 }
 
-// Ordered compaction.  The reference appends pairs per traceback (ascending), per diagonal descending, per cell in
-// ascending x-y (:594-613, :695-733); alignedPairCoordinateCorrectionFn then pops each region's list from the tail
-// (:1167-1169), i.e. reverses it.  Net order inside a region: tracebacks descending, diagonals ascending, x-y
-// descending.  Regions are concatenated in ascending order.
-__global__ void __launch_bounds__(THREADS_PER_BLOCK)
-k_emit(Blob bl, int n_regions, const int32_t *__restrict__ pint, const int64_t *__restrict__ offsets,
-       int32_t *__restrict__ out_x, int32_t *__restrict__ out_y, int32_t *__restrict__ out_p, int64_t capacity,
-       int *counter) {
-    const int lane = threadIdx.x & 31;
-    for (;;) {
-        const int item = next_item(counter, lane);
-        if (item >= n_regions) break;
-        const int r = bl.order_fwd[item];
-        const RegionDesc rg = bl.regions[r];
-        const DiagDesc *dd = bl.diags + rg.diag_base;
-        int64_t pos = offsets[r];
-        for (int t = rg.n_tb - 1; t >= 0; t--) {
-            const TracebackDesc tb = bl.tbs[rg.tb_base + t];
-            for (int d = tb.lo + 1; d <= tb.from; d++) {
-                const DiagDesc cur = dd[d];
-                const int w = (int) (dd[d + 1].cell_off - cur.cell_off);
-                for (int j0 = 0; j0 < w; j0 += 32) {
-                    const int j = w - 1 - (j0 + lane);
-                    int32_t v = -1;
-                    if (j >= 0) v = pint[cur.cell_off + j];
-                    const unsigned ballot = __ballot_sync(FULL_MASK, v >= 0);
-                    if (v >= 0) {
-                        const int64_t at = pos + __popc(ballot & ((1u << lane) - 1));
-                        if (at < capacity) {
-                            const int xmy = cur.xmyL + 2 * j;
-                            out_x[at] = rg.x1 + ((d + xmy) >> 1) - 1;
-                            out_y[at] = rg.y1 + ((d - xmy) >> 1) - 1;
-                            out_p[at] = v;
-                        }
-                    }
-                    pos += __popc(ballot);
-                }
+__global__ void __launch_bounds__(256)
+k_emit_diag(Blob bl, int64_t n_diagonals, const int32_t *__restrict__ pint, const int64_t *__restrict__ pos,
+            int32_t *__restrict__ out_x, int32_t *__restrict__ out_y, int32_t *__restrict__ out_p, int64_t capacity) {
+    const int64_t g = (int64_t) blockIdx.x * blockDim.x + threadIdx.x;
+    if (g >= n_diagonals) return;
+    const DiagWork k = diag_work(bl, g);
+    if (k.d < 1) return;
+    int64_t at = pos[k.slot];
+    if (pos[k.slot + 1] == at) return;  // nothing to emit on this diagonal
+    for (int j = k.w - 1; j >= 0; j--) {
+        const int32_t v = pint[k.c0 + j];
+        if (v >= 0) {
+            if (at < capacity) {
+                const int xmy = k.xmyL + 2 * j;
+                out_x[at] = k.x1 + ((k.d + xmy) >> 1) - 1;
+                out_y[at] = k.y1 + ((k.d - xmy) >> 1) - 1;
+                out_p[at] = v;
             }
+            at++;
         }
     }
 }
@@ -755,6 +744,8 @@ struct Workspace {
     double *fwd, *bwd, *fwd_tot, *bwd_tot, *edge, *totals;
     int32_t *pint;
     int64_t *counts;
+    void *scan_tmp;
+    int64_t scan_tmp_bytes;
     int *counters;
 };
 
@@ -778,6 +769,8 @@ int carve(const mab_plan *plan, void *d_ws, int64_t ws_bytes, int S, bool expect
     w->totals = (double *) (b + lay.off_totals);
     w->pint = (int32_t *) (b + lay.off_pint);
     w->counts = (int64_t *) (b + lay.off_counts);
+    w->scan_tmp = b + lay.off_scan_tmp;
+    w->scan_tmp_bytes = lay.scan_tmp_bytes;
     return MAB_OK;
 }
 
@@ -870,14 +863,27 @@ int run_posteriors(const DevModel &dm, const mab_plan *plan, const void *d_blob,
     const Blob bl = blob_view(d_blob, h);
     int rc = run_dp<S, false>(dm, plan, bl, w, st);
     if (rc) return rc;
+    const int64_t nD = h.n_diagonals;
     {
         LaunchTimer lt(K_POSTERIOR, st);
-        k_posterior_count<<<grid_for(h.n_regions, 8), THREADS_PER_BLOCK, 0, st>>>(
-        bl, (int) h.n_regions, w.fwd, w.bwd, w.totals, plan->params.threshold, w.pint, w.counts, w.counters + 2);
+        const double thr = plan->params.threshold;
+        // exp() is skipped where it cannot reach the threshold (log(0) = -inf: never skipped)
+        const double log_reject = thr > 0.0 ? std::log(thr) - 0.1 : -INFINITY;
+        k_posterior_diag<<<(unsigned) ((nD + 1 + 255) / 256), 256, 0, st>>>(bl, nD, w.fwd, w.bwd, w.totals, thr, log_reject,
+                                                                          w.pint, w.counts);
     }
     {
         LaunchTimer lt(K_SCAN, st);
-        k_scan<<<1, 1024, 0, st>>>(w.counts, h.n_regions, bl.aln_region, h.n_alignments, d_pair_off, d_n_pairs);
+        size_t need = 0;
+        cub::DeviceScan::ExclusiveSum(nullptr, need, w.counts, w.counts, nD + 1, st);
+        if ((int64_t) need > w.scan_tmp_bytes) {
+            mab_set_error("scan scratch too small: need %lld bytes, reserved %lld", (long long) need,
+                          (long long) w.scan_tmp_bytes);
+            return MAB_E_CAPACITY;
+        }
+        cub::DeviceScan::ExclusiveSum(w.scan_tmp, need, w.counts, w.counts, nD + 1, st);
+        k_pair_offsets<<<(unsigned) ((h.n_alignments + 1 + 255) / 256), 256, 0, st>>>(
+            bl, h.n_alignments, h.n_regions, nD, w.counts, d_pair_off, d_n_pairs);
     }
     return check(cudaGetLastError(), "posterior launch");
 }
@@ -995,8 +1001,8 @@ extern "C" int mab_posteriors_emit(const mab_plan *plan, const void *d_blob, voi
     const Blob bl = blob_view(d_blob, h);
     {
         LaunchTimer lt(K_EMIT, st);
-        k_emit<<<grid_for(h.n_regions, 8), THREADS_PER_BLOCK, 0, st>>>(bl, (int) h.n_regions, w.pint, w.counts, d_x, d_y, d_p,
-                                                                   capacity, w.counters + 3);
+        k_emit_diag<<<(unsigned) ((h.n_diagonals + 255) / 256), 256, 0, st>>>(bl, h.n_diagonals, w.pint, w.counts, d_x, d_y,
+                                                                            d_p, capacity);
     }
     return check(cudaGetLastError(), "emit launch");
 }

@@ -62,7 +62,8 @@ struct BlobHeader {  // 256 bytes
     int64_t blob_bytes;
     int64_t n_edge_cells;     // cells of the diagonals from+1 of all intermediate tracebacks (see TracebackDesc)
     int64_t n_full_cells;     // cells of all diagonals that carry a total (posterior mode keeps all states there)
-    int64_t pad[9];
+    int64_t off_diag_region;  // int32[n_diagonals + 1] owning region of every diagonal (sentinel: -1)
+    int64_t pad[8];
 };
 static_assert(sizeof(BlobHeader) == 256, "BlobHeader must be 256 bytes");
 
@@ -123,7 +124,7 @@ struct mab_plan {
     std::vector<TracebackDesc> tbs;
     std::vector<TotalDesc> totals;
     std::vector<uint8_t> sym_x, sym_y;
-    std::vector<int32_t> order_fwd, order_bwd;
+    std::vector<int32_t> order_fwd, order_bwd, diag_region;
     std::vector<int64_t> aln_region;
     // kept for introspection only
     std::vector<int64_t> anchors;      // x,y interleaved, alignment-local
@@ -137,6 +138,7 @@ int mab_params_validate(const mab_params *p);
 // workspace carving (device scratch); all offsets 256-byte aligned
 struct WorkspaceLayout {
     int64_t off_fwd, off_bwd, off_fwd_tot, off_bwd_tot, off_edge, off_totals, off_pint, off_counts, off_counters;
+    int64_t off_scan_tmp, scan_tmp_bytes;  // posterior mode: scratch of the device-wide scan over off_counts
     int64_t total_bytes;
 };
 WorkspaceLayout mab_workspace_layout(const BlobHeader &h, int S, bool expectations);

@@ -300,6 +300,12 @@ int build_plan(const mab_params *p, const BatchInput &in, int n_threads, mab_pla
     for (int64_t i = 0; i < lenX; i++) plan->sym_x[i] = symbol_of(in.seq_x[i]);
     for (int64_t i = 0; i < lenY; i++) plan->sym_y[i] = symbol_of(in.seq_y[i]);
 
+    plan->diag_region.assign(nD + 1, -1);
+    for (int64_t r = 0; r < nR; r++) {
+        const RegionDesc &rg = plan->regions[r];
+        for (int64_t d = 0; d <= (int64_t) rg.lX + rg.lY; d++) plan->diag_region[rg.diag_base + d] = (int32_t) r;
+    }
+
     // processing orders: longest first, so the dynamic work queue ends on short items
     plan->order_fwd.resize(nR);
     std::iota(plan->order_fwd.begin(), plan->order_fwd.end(), 0);
@@ -343,6 +349,7 @@ int build_plan(const mab_params *p, const BatchInput &in, int n_threads, mab_pla
     h.off_order_fwd = place(nR * 4);
     h.off_order_bwd = place(nT * 4);
     h.off_aln_region = place((in.n + 1) * 8);
+    h.off_diag_region = place((nD + 1) * 4);
     h.blob_bytes = off;
     *out = plan;
     return MAB_OK;
@@ -444,6 +451,7 @@ extern "C" int mab_plan_write_blob(const mab_plan *plan, void *dst, int64_t dst_
     put(h.off_order_fwd, plan->order_fwd.data(), plan->order_fwd.size() * 4);
     put(h.off_order_bwd, plan->order_bwd.data(), plan->order_bwd.size() * 4);
     put(h.off_aln_region, plan->aln_region.data(), plan->aln_region.size() * 8);
+    put(h.off_diag_region, plan->diag_region.data(), plan->diag_region.size() * 4);
     return MAB_OK;
 }
 
@@ -517,7 +525,10 @@ WorkspaceLayout mab_workspace_layout(const BlobHeader &h, int S, bool expectatio
     w.off_edge = place(h.n_edge_cells * 8);
     w.off_totals = place(h.n_totals * 8);
     w.off_pint = place(expectations ? 0 : h.n_cells * 4);
-    w.off_counts = place(expectations ? 0 : (h.n_regions + 1) * 8);
+    // per-diagonal pair counts in emission-slot order, scanned in place into output positions (+ sentinel)
+    w.off_counts = place(expectations ? 0 : (h.n_diagonals + 2) * 8);
+    w.scan_tmp_bytes = expectations ? 0 : h.n_diagonals / 32 + (1 << 20);
+    w.off_scan_tmp = place(w.scan_tmp_bytes);
     w.total_bytes = off;
     return w;
 }

@@ -156,7 +156,8 @@ struct CountSink {
 };
 
 __global__ void k_bands(DevInput in, mab_params p, int64_t n_regions, const RegionDesc *regions, const RegionTmp *tmp,
-                        const int64_t *diag_base, DiagDesc *diags, RegionCounts *counts, Status *status) {
+                        const int64_t *diag_base, DiagDesc *diags, int32_t *diag_region, RegionCounts *counts,
+                        Status *status) {
     const int64_t r = (int64_t) blockIdx.x * blockDim.x + threadIdx.x;
     if (r >= n_regions) return;
     const RegionDesc rg = regions[r];
@@ -168,6 +169,7 @@ __global__ void k_bands(DevInput in, mab_params p, int64_t n_regions, const Regi
     cur.j = t.j;
     cur.k = t.k;
     DiagDesc *dd = diags + diag_base[r];
+    int32_t *dr = diag_region + diag_base[r];
     int64_t cell = 0, max_w = 0;
     plan_core::band_walk(ai, p, Split{t.x1, t.y1, t.x2, t.y2}, cur, [&](int64_t xay, int64_t l, int64_t w) {
         DiagDesc d;
@@ -175,6 +177,7 @@ __global__ void k_bands(DevInput in, mab_params p, int64_t n_regions, const Regi
         d.xmyL = (int32_t) l;
         d.tot_flags = MAB_DIAG_TOT_MASK;
         dd[xay] = d;
+        dr[xay] = (int32_t) r;
         cell += w;
         if (w > max_w) max_w = w;
     });
@@ -386,6 +389,7 @@ extern "C" int mab_plan_build_device(const mab_params *p, int64_t n, const uint8
     h.off_diags = ar.place((nD + 1) * (int64_t) sizeof(DiagDesc));
     h.off_tracebacks = ar.place(capT * (int64_t) sizeof(TracebackDesc));
     h.off_totals = ar.place(capTot * (int64_t) sizeof(TotalDesc));
+    h.off_diag_region = ar.place((nD + 1) * 4);
     h.off_order_fwd = ar.place(nR * 4);
     h.off_order_bwd = ar.place(capT * 4);
     const int64_t at_tmp = ar.place(nR * (int64_t) sizeof(RegionTmp));
@@ -417,12 +421,14 @@ extern "C" int mab_plan_build_device(const mab_params *p, int64_t n, const uint8
     RegionCounts *d_counts = ar.ptr<RegionCounts>(at_counts), *d_bases = ar.ptr<RegionCounts>(at_bases);
     void *d_cub = ar.ptr<void>(at_cub);
     RegionCounts totals{0, 0, 0, 0, 0};
+    if ((rc = cuda_fail(cudaMemsetAsync(ar.ptr<int32_t>(h.off_diag_region) + nD, 0xff, 4, st), "memset"))) return rc;
     if (nR > 0) {
         if ((rc = cuda_fail(cudaMemsetAsync(d_diag_base + nR, 0, 8, st), "memset"))) return rc;
         if ((rc = cuda_fail(cudaMemsetAsync(d_counts + nR, 0, sizeof(RegionCounts), st), "memset"))) return rc;
         k_regions<true><<<grid(n, 128), 128, 0, st>>>(in, *p, d_aln_region, d_status, d_regions, d_tmp, d_diag_base);
         cub::DeviceScan::ExclusiveSum(d_cub, scan_tmp2, d_diag_base, d_diag_base, nR + 1, st);
-        k_bands<<<grid(nR, 128), 128, 0, st>>>(in, *p, nR, d_regions, d_tmp, d_diag_base, d_diags, d_counts, d_status);
+        k_bands<<<grid(nR, 128), 128, 0, st>>>(in, *p, nR, d_regions, d_tmp, d_diag_base, d_diags,
+                                               ar.ptr<int32_t>(h.off_diag_region), d_counts, d_status);
         cub::DeviceScan::ExclusiveScan(d_cub, scan_tmp3, d_counts, d_bases, SumCounts(), RegionCounts{0, 0, 0, 0, 0}, nR + 1,
                                        st);
         int32_t *rkey = ar.ptr<int32_t>(at_rkey), *rkey2 = ar.ptr<int32_t>(at_rkey2), *riota = ar.ptr<int32_t>(at_riota);

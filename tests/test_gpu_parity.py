@@ -239,7 +239,7 @@ def _blob_arrays(raw):
     names = ["magic", "n_alignments", "n_regions", "n_diagonals", "n_cells", "n_tracebacks", "n_totals", "n_anchors",
              "max_width", "len_sym_x", "len_sym_y", "off_regions", "off_diags", "off_tracebacks", "off_totals",
              "off_sym_x", "off_sym_y", "off_order_fwd", "off_order_bwd", "off_aln_region", "blob_bytes", "n_edge_cells",
-             "n_full_cells"]
+             "n_full_cells", "off_diag_region"]
     H = {k: int(h[i]) for i, k in enumerate(names)}
     cut = lambda off, nbytes: raw[off:off + nbytes]
     return H, {
@@ -252,6 +252,7 @@ def _blob_arrays(raw):
         "order_fwd": cut(H["off_order_fwd"], H["n_regions"] * 4),
         "order_bwd": cut(H["off_order_bwd"], H["n_tracebacks"] * 4),
         "aln_region": cut(H["off_aln_region"], (H["n_alignments"] + 1) * 8),
+        "diag_region": cut(H["off_diag_region"], (H["n_diagonals"] + 1) * 4),
     }
 
 
