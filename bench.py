@@ -357,8 +357,9 @@ def run_ours(args, rank, world, local_rank):
         dt = float(t.item())
         e2e = {"value": total_cells / dt / 1e9, "unit": "GCUPS", "h2d_bytes_per_step": int(st["h2d_bytes"]),
                "d2h_bytes_per_step": int(st["d2h_bytes"]), "ms_per_step": dt * 1e3, "steps": e2e_steps,
-               "reads_per_s": n_reads * world / dt,
-               "note": "host planning (bands/schedule) + pinned H2D of the plan + kernels + D2H of the pairs, per step"}
+               "reads_per_s": n_reads * world / dt, "host_wall_s": st.get("host_wall"),
+               "note": "packing of bases+cigars into pinned memory, H2D, planning on the GPU, DP kernels, D2H of the "
+                       "pairs into pinned host blocks, per step (rank 0 breakdown in host_wall_s)"}
 
     if rank != 0:
         return

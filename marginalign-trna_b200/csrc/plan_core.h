@@ -120,58 +120,73 @@ MAB_HD int64_t isqrt_floor(int64_t v) {
     return r;
 }
 
-// Calls sink(split, cursor_at_first_anchor, ragged_left, ragged_right) for every region of the alignment, in order.
+// Region walker: step() consumes one anchor (or, at the end of the stream, closes the alignment) and calls
+// sink(split, cursor_at_first_anchor, ragged_left, ragged_right) for every region that becomes final, in order.
 // getSplitPoints keeps, on each side of a gap box bigger than `limit`, min(gap/2, floor(sqrt(limit))) rows/columns.
-template <typename Sink>
-MAB_HD void for_each_region(const AlnInput &in, const mab_params &p, Sink &&sink) {
-    const int64_t limit = p.split_matrix_bigger_than;
-    const int64_t cap = isqrt_floor(limit);
-    AnchorStream st, region_start;  // region_start: cursor positioned before the first anchor of the open region
+// A region is only known to be the last one when the stream ends, so the sink runs one region late.
+// The walk is exposed one step at a time so that a GPU caller can keep the lanes of a warp in step with each other
+// (`while (__any_sync(mask, more)) if (more) more = w.step(sink);`); for_each_region is the plain loop.
+struct RegionWalker {
+    const AlnInput &in;
+    const mab_params &p;
+    int64_t limit, cap;
+    AnchorStream st, region_start, pend_cur;
     int64_t x1 = 0, y1 = 0, x2 = 0, y2 = 0, i = 0, n_emitted = 0;
-    // A region is only known to be the last one when the stream ends, so the sink is called one region late.
     bool have_pending = false;
     Split pend{};
-    AnchorStream pend_cur;
-    auto emit = [&](const Split &sp, const AnchorStream &cur, bool last) {
-        (void) last;
+
+    MAB_HD RegionWalker(const AlnInput &in_, const mab_params &p_)
+        : in(in_), p(p_), limit(p_.split_matrix_bigger_than), cap(isqrt_floor(p_.split_matrix_bigger_than)) {}
+
+    template <typename Sink>
+    MAB_HD void emit(const Split &sp, const AnchorStream &cur, Sink &&sink) {
         if (have_pending) {
-            sink(pend, pend_cur, p.ragged_left || n_emitted > 0, true /* not the last: i < last */);
+            sink(pend, pend_cur, p.ragged_left || n_emitted > 0, true /* not the last region */);
             n_emitted++;
         }
         pend = sp;
         pend_cur = cur;
         have_pending = true;
-    };
-    for (;;) {
-        AnchorStream before = st;
-        int64_t x3, y3;
-        if (!st.next(in, x3, y3)) break;
+    }
+
+    // getSplitPointsP (:1016-1038): cut between (x2, y2) and the next anchor / corner (x3, y3) if the box is too big
+    template <typename Sink>
+    MAB_HD bool cut(int64_t x3, int64_t y3, const AnchorStream &next_start, Sink &&sink) {
         const int64_t gx = x3 - x2, gy = y3 - y2;
-        if (gx * gy > limit) {
-            const int64_t hx = gx / 2 > cap ? cap : gx / 2, hy = gy / 2 > cap ? cap : gy / 2;
-            if (!(p.ragged_left && i == 0)) emit(Split{x1, y1, x2 + hx, y2 + hy}, region_start, false);
-            x1 = x3 - hx;
-            y1 = y3 - hy;
-            region_start = before;
-        }
-        x2 = x3 + 1;
-        y2 = y3 + 1;
-        i++;
+        if (gx * gy <= limit) return false;
+        const int64_t hx = gx / 2 > cap ? cap : gx / 2, hy = gy / 2 > cap ? cap : gy / 2;
+        if (!(p.ragged_left && i == 0)) emit(Split{x1, y1, x2 + hx, y2 + hy}, region_start, sink);
+        x1 = x3 - hx;
+        y1 = y3 - hy;
+        region_start = next_start;
+        return true;
     }
-    {
-        const int64_t gx = in.lX - x2, gy = in.lY - y2;
-        bool cut = false;
-        if (gx * gy > limit) {
-            const int64_t hx = gx / 2 > cap ? cap : gx / 2, hy = gy / 2 > cap ? cap : gy / 2;
-            if (!(p.ragged_left && i == 0)) emit(Split{x1, y1, x2 + hx, y2 + hy}, region_start, false);
-            x1 = in.lX - hx;
-            y1 = in.lY - hy;
-            region_start = st;  // exhausted: the trailing region has no anchors
-            cut = true;
+
+    template <typename Sink>
+    MAB_HD bool step(Sink &&sink) {
+        const AnchorStream before = st;
+        int64_t x3, y3;
+        if (st.next(in, x3, y3)) {
+            cut(x3, y3, before, sink);
+            x2 = x3 + 1;
+            y2 = y3 + 1;
+            i++;
+            return true;
         }
-        if (!cut || !p.ragged_right) emit(Split{x1, y1, in.lX, in.lY}, region_start, true);
+        // end of the stream (:1056-1066): the gap to the corner, then the trailing region unless it is cut off by a
+        // ragged right end; st is exhausted, so a trailing region that starts here has no anchors
+        const bool was_cut = cut(in.lX, in.lY, st, sink);
+        if (!was_cut || !p.ragged_right) emit(Split{x1, y1, in.lX, in.lY}, region_start, sink);
+        if (have_pending) sink(pend, pend_cur, p.ragged_left || n_emitted > 0, p.ragged_right /* the last region */);
+        return false;
     }
-    if (have_pending) sink(pend, pend_cur, p.ragged_left || n_emitted > 0, p.ragged_right /* the last region */);
+};
+
+template <typename Sink>
+MAB_HD void for_each_region(const AlnInput &in, const mab_params &p, Sink &&sink) {
+    RegionWalker w(in, p);
+    while (w.step(sink)) {
+    }
 }
 
 MAB_HD int64_t clamp_to(int64_t z, int64_t hi) { return z < 0 ? 0 : (z > hi ? hi : z); }
@@ -194,33 +209,38 @@ MAB_HD void band_diagonal(int64_t xay, int64_t xL, int64_t yL, int64_t xU, int64
 
 // band_construct (:128-179) for the region `sp`, anchors streamed from `cur` (absolute coordinates; the anchors of the
 // region are those with x + y < sp.x2 + sp.y2).  Calls diag(xay, xmyL, width) for xay = 0 .. lX + lY.
+//
+// The reference walks diagonal by diagonal and steps to the next anchor whenever it reaches the current one.  The
+// same sequence is produced here anchor by anchor -- diagonal 0 with the all-zero initial rectangle, then for each
+// successive pair (previous anchor P, next anchor N; the last N is the corner (lX, lY)) the diagonals P.xay+1 .. N.xay
+// with the rectangle of (P, N) -- because on a GPU the lanes of a warp then fetch their k-th anchor together instead
+// of each lane branching into the anchor fetch at its own diagonal.
 template <typename DiagSink>
 MAB_HD void band_walk(const AlnInput &in, const mab_params &p, const Split &sp, AnchorStream cur, DiagSink &&diag) {
     const int64_t lX = sp.x2 - sp.x1, lY = sp.y2 - sp.y1, D = lX + lY, e = p.diagonal_expansion;
     const int64_t end_xay = sp.x2 + sp.y2;
-    int64_t xay = 0, pxay = 0, pxmy = 0, nxay = 0, nxmy = 0, xL = 0, yL = 0, xU = 0, yU = 0;
+    int64_t l, r;
+    band_diagonal(0, 0, 0, 0, 0, l, r);
+    diag(0, l, (r - l) / 2 + 1);
+    int64_t xay = 1, pxay = 0, pxmy = 0;
     bool more = true;
     while (xay <= D) {
-        int64_t l, r;
-        band_diagonal(xay, xL, yL, xU, yU, l, r);
-        diag(xay, l, (r - l) / 2 + 1);
-        if (nxay == xay++) {
-            pxay = nxay;
-            pxmy = nxmy;
-            int64_t x = lX, y = lY, ax, ay;
-            if (more && cur.next(in, ax, ay) && ax + ay < end_xay) {
-                x = ax - sp.x1 + 1;
-                y = ay - sp.y1 + 1;
-            } else {
-                more = false;
-            }
-            nxay = x + y;
-            nxmy = x - y;
-            xL = clamp_to((pxay + (pxmy - e)) / 2, lX);
-            yL = clamp_to((nxay - (nxmy - e)) / 2, lY);
-            xU = clamp_to((nxay + (nxmy + e)) / 2, lX);
-            yU = clamp_to((pxay - (pxmy + e)) / 2, lY);
+        int64_t x = lX, y = lY, ax, ay;
+        if (more && cur.next(in, ax, ay) && ax + ay < end_xay) {
+            x = ax - sp.x1 + 1;
+            y = ay - sp.y1 + 1;
+        } else {
+            more = false;
         }
+        const int64_t nxay = x + y, nxmy = x - y;
+        const int64_t xL = clamp_to((pxay + (pxmy - e)) / 2, lX), yL = clamp_to((nxay - (nxmy - e)) / 2, lY);
+        const int64_t xU = clamp_to((nxay + (nxmy + e)) / 2, lX), yU = clamp_to((pxay - (pxmy + e)) / 2, lY);
+        for (; xay <= nxay; xay++) {
+            band_diagonal(xay, xL, yL, xU, yU, l, r);
+            diag(xay, l, (r - l) / 2 + 1);
+        }
+        pxay = nxay;
+        pxmy = nxmy;
     }
 }
 
@@ -233,11 +253,15 @@ MAB_HD void band_walk(const AlnInput &in, const mab_params &p, const Split &sp, 
 template <typename WidthFn, typename Sink>
 MAB_HD void schedule_walk(const mab_params &p, int64_t D, WidthFn &&width, Sink &&sink) {
     const int64_t e = p.diagonal_expansion;
-    int64_t traced_to = 0, n_tot_region = 0;
-    for (int64_t d = 1; d <= D; d++) {
+    int64_t traced_to = 0, n_tot_region = 0, d = 1;
+    while (d <= D) {
+        // scan to the next traceback point: the end, or >= min_diags past the last one on a narrow diagonal (:674-675).
+        // (Written as scan-then-process so that the lanes of a warp leave the cheap scan together and run the
+        // per-traceback loop below side by side.)
+        if (d < traced_to + p.min_diags_between_traceback) d = traced_to + p.min_diags_between_traceback;
+        if (d > D) d = D;
+        while (d < D && width(d) > e * 2 + 1) d++;
         const bool at_end = d == D;
-        const bool tb_point = d >= traced_to + p.min_diags_between_traceback && width(d) <= e * 2 + 1;
-        if (!(at_end || tb_point)) continue;
         const int64_t lo = traced_to, hi = d, from = d - (at_end ? 0 : p.traceback_diagonals + 1);
         const int64_t edge_cells = at_end ? 0 : width(from + 1);
         int64_t k = 0, n_tot = 0;
@@ -252,6 +276,7 @@ MAB_HD void schedule_walk(const mab_params &p, int64_t D, WidthFn &&width, Sink 
         }
         sink.traceback(lo, hi, from, at_end, n_tot, edge_cells);
         traced_to = from;
+        d++;
     }
 }
 

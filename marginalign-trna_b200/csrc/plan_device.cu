@@ -88,46 +88,79 @@ struct Status {  // device-side status block (256 B), read back by the host
 
 // ------------------------------------------------------------------------------------------------ kernels
 
+struct RegionRec {  // one region as found by the walk
+    int64_t x1, y1, x2, y2;
+    AnchorStream cur;
+    int flags;
+};
+
+__device__ __forceinline__ void store_region(const DevInput &in, int64_t a, int64_t r, const RegionRec &rec,
+                                             RegionDesc *regions, RegionTmp *tmp, int64_t *diag_count) {
+    const int64_t lX = rec.x2 - rec.x1, lY = rec.y2 - rec.y1;
+    RegionDesc rg;
+    rg.sym_x_off = in.off_x[a] + rec.x1;
+    rg.sym_y_off = in.off_y[a] + rec.y1;
+    rg.diag_base = 0;
+    rg.lX = (int32_t) lX;
+    rg.lY = (int32_t) lY;
+    rg.x1 = (int32_t) rec.x1;
+    rg.y1 = (int32_t) rec.y1;
+    rg.aln = (int32_t) a;
+    rg.flags = rec.flags;
+    rg.tb_base = rg.n_tb = rg.tot_base = rg.n_tot = 0;
+    regions[r] = rg;
+    tmp[r] = RegionTmp{rec.x1, rec.y1, rec.x2, rec.y2, rec.cur.o, rec.cur.l, rec.cur.j, rec.cur.k};
+    diag_count[r] = lX + lY + 1;
+}
+
+// WRITE = false: validate, count regions and diagonals.  WRITE = true: the same walk again, now that the scan has told
+// every alignment where its regions go.  The first two regions of an alignment (all of them, for short reads) are
+// held in registers and stored after the walk, where the lanes of the warp are together again; only further regions
+// are stored from inside the walk.
 template <bool WRITE>
 __global__ void k_regions(DevInput in, mab_params p, int64_t *region_count /* [n+1] or aln_region in WRITE */,
                           Status *status, RegionDesc *regions, RegionTmp *tmp, int64_t *diag_count) {
-    const int64_t a = (int64_t) blockIdx.x * blockDim.x + threadIdx.x;
-    if (a >= in.n) return;
+    const int64_t a_raw = (int64_t) blockIdx.x * blockDim.x + threadIdx.x;
+    const bool live = a_raw < in.n;
+    const int64_t a = live ? a_raw : 0;  // idle lanes shadow alignment 0 so the whole warp stays in the stepping loop
+    if (in.n == 0) return;
     const AlnInput ai = aln_input(in, a);
-    if (!WRITE) {
+    bool more = live;
+    if (!WRITE && live) {
         const int bad = plan_core::validate(ai);
         if (bad) {
             if (atomicCAS(&status->error_code, 0, bad) == 0) status->error_aln = a;
             region_count[a] = 0;
-            return;
+            more = false;
         }
     }
+    const bool counted = more;
     int64_t n_regions = 0, n_diags = 0;
     const int64_t base = WRITE ? region_count[a] : 0;
-    plan_core::for_each_region(ai, p, [&](const Split &sp, const AnchorStream &cur, bool rl, bool rr) {
-        const int64_t lX = sp.x2 - sp.x1, lY = sp.y2 - sp.y1, D = lX + lY;
+    RegionRec r0{}, r1{};
+    auto sink = [&](const Split &sp, const AnchorStream &cur, bool rl, bool rr) {
+        const int64_t D = (sp.x2 - sp.x1) + (sp.y2 - sp.y1);
         if (D == 0) return;  // getPosteriorProbsWithBanding :650-652
         if (WRITE) {
-            const int64_t r = base + n_regions;
-            RegionDesc rg;
-            rg.sym_x_off = in.off_x[a] + sp.x1;
-            rg.sym_y_off = in.off_y[a] + sp.y1;
-            rg.diag_base = 0;
-            rg.lX = (int32_t) lX;
-            rg.lY = (int32_t) lY;
-            rg.x1 = (int32_t) sp.x1;
-            rg.y1 = (int32_t) sp.y1;
-            rg.aln = (int32_t) a;
-            rg.flags = (rl ? 1 : 0) | (rr ? 2 : 0);
-            rg.tb_base = rg.n_tb = rg.tot_base = rg.n_tot = 0;
-            regions[r] = rg;
-            tmp[r] = RegionTmp{sp.x1, sp.y1, sp.x2, sp.y2, cur.o, cur.l, cur.j, cur.k};
-            diag_count[r] = D + 1;
+            const RegionRec rec{sp.x1, sp.y1, sp.x2, sp.y2, cur, (rl ? 1 : 0) | (rr ? 2 : 0)};
+            if (n_regions == 0) r0 = rec;
+            else if (n_regions == 1) r1 = rec;
+            else store_region(in, a, base + n_regions, rec, regions, tmp, diag_count);
         }
         n_regions++;
         n_diags += D + 1;
-    });
-    if (!WRITE) {
+    };
+    // one anchor per step, the warp re-joined at every step (lanes find their next anchor after different numbers
+    // of bases; left to itself the compiler let them drift apart for the whole walk: 1.2 active lanes per instruction)
+    plan_core::RegionWalker walker(ai, p);
+    while (__any_sync(0xffffffffu, more)) {
+        if (more) more = walker.step(sink);
+    }
+    if (!counted) return;
+    if (WRITE) {
+        if (n_regions > 0) store_region(in, a, base, r0, regions, tmp, diag_count);
+        if (n_regions > 1) store_region(in, a, base + 1, r1, regions, tmp, diag_count);
+    } else {
         region_count[a] = n_regions;
         if (n_diags) atomicAdd(&status->n_diagonals, (unsigned long long) n_diags);
     }

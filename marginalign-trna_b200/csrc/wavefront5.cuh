@@ -43,28 +43,47 @@ enum CoefMode { COEF_CONST = 0, COEF_SMEM = 1, COEF_MIXED = 2 };
 // constant bank saturates the indexed-constant cache (the index differs per lane, every distinct address is a
 // separate request: IDC 92 % busy); all four from shared memory loads the LSU instead.  COEF_MIXED splits them:
 // (c3, c2) with one conflict-free LDS.128, (c1, c0) with two LDC.64.
+// Shared-memory loads with an explicit 32-bit address and immediate offset: one address register serves both halves
+// of a coefficient row (the compiler otherwise rebuilds a second base per load).
+__device__ __forceinline__ double2 lds_v2(unsigned addr) {
+    double2 v;
+    asm("ld.shared.v2.f64 {%0, %1}, [%2];" : "=d"(v.x), "=d"(v.y) : "r"(addr));
+    return v;
+}
+__device__ __forceinline__ double2 lds_v2_128(unsigned addr) {
+    double2 v;
+    asm("ld.shared.v2.f64 {%0, %1}, [%2+128];" : "=d"(v.x), "=d"(v.y) : "r"(addr));
+    return v;
+}
+
+// coef_addr: shared-space address of sh.coef[0][0][replica of this lane]; piece p lives 256 bytes further per step.
 template <int CM>
-__device__ __forceinline__ double la_bf(double x, double y, const double2 *coef_lane) {
+__device__ __forceinline__ double la_bf(double x, double y, unsigned coef_addr) {
     const bool lt = x < y;
     const double hi = lt ? y : x;
     const double lo = lt ? x : y;
     const double d = __dsub_rn(hi, lo);  // +inf if lo = -inf, NaN if both are -inf: both fail (d < 7.5) below
-    const int piece = (d > 1.00 ? 1 : 0) + (d > 2.50 ? 1 : 0) + (d > 4.50 ? 1 : 0);
     double c3, c2, c1, c0;
     if (CM == COEF_CONST) {
+        const int piece = (d > 1.00 ? 1 : 0) + (d > 2.50 ? 1 : 0) + (d > 4.50 ? 1 : 0);
         c3 = c_la_coef[piece * 4];
         c2 = c_la_coef[piece * 4 + 1];
         c1 = c_la_coef[piece * 4 + 2];
         c0 = c_la_coef[piece * 4 + 3];
     } else {
-        const double2 c32 = coef_lane[piece * 2 * W5_COPIES];
+        unsigned a = coef_addr;  // three predicated adds pick the row
+        if (d > 1.00) a += 2 * W5_COPIES * 16;
+        if (d > 2.50) a += 2 * W5_COPIES * 16;
+        if (d > 4.50) a += 2 * W5_COPIES * 16;
+        const double2 c32 = lds_v2(a);
         c3 = c32.x;
         c2 = c32.y;
         if (CM == COEF_SMEM) {
-            const double2 c10 = coef_lane[(piece * 2 + 1) * W5_COPIES];
+            const double2 c10 = lds_v2_128(a);
             c1 = c10.x;
             c0 = c10.y;
         } else {
+            const int piece = (int) ((a - coef_addr) >> 8);
             c1 = c_la_coef[piece * 4 + 2];
             c0 = c_la_coef[piece * 4 + 3];
         }
@@ -72,8 +91,12 @@ __device__ __forceinline__ double la_bf(double x, double y, const double2 *coef_
     double r = __dadd_rn(__dmul_rn(c3, d), c2);
     r = __dadd_rn(__dmul_rn(r, d), c1);
     r = __dadd_rn(__dmul_rn(r, d), c0);
-    r = __dadd_rn(r, lo);
-    return (d < 7.5) ? r : hi;
+    // result = d < 7.5 ? r + lo : hi, as one predicated add into a register preloaded with hi
+    double res = hi;
+    asm("{\n\t.reg .pred p;\n\tsetp.lt.f64 p, %1, 0d401E000000000000;\n\t@p add.rn.f64 %0, %2, %3;\n\t}"
+        : "+d"(res)
+        : "d"(d), "d"(r), "d"(lo));
+    return res;
 }
 
 // Four logAdds, same instruction stream for both lane roles.  Slots t1..t8 hold the addends.
@@ -84,7 +107,7 @@ struct Quad {
 };
 template <int CM>
 __device__ __forceinline__ Quad four_logadds(bool chain, double t1, double t2, double t3, double t4, double t5, double t6,
-                                             double t7, double t8, const double2 *coef) {
+                                             double t7, double t8, unsigned coef) {
     Quad q;
     q.r1 = la_bf<CM>(t1, t2, coef);
     q.r2 = la_bf<CM>(chain ? q.r1 : t3, t4, coef);
@@ -199,7 +222,7 @@ k_forward5(const __grid_constant__ DevModel model, Blob bl, int n_regions, doubl
     if (lane < 15) ring[(lane / 5) * slot_doubles + lane % 5] = neg_inf();  // low guards of the three slots
     __syncthreads();
     const double2 *etp_lane = &sh.etp[role][0][0][lane & (W5_COPIES - 1)];
-    const double2 *coef_lane = &sh.coef[0][0][lane & (W5_COPIES - 1)];
+    const unsigned coef_lane = (unsigned) __cvta_generic_to_shared(&sh.coef[0][0][lane & (W5_COPIES - 1)]);
     // per-lane state picks (see table comment): v4 = c1[role ? LX : SY], v6 = c2[role ? SY : LX]
     const int s4 = role ? LX : SY, s6 = role ? SY : LX;
     const int s_out4 = role ? LY : M;  // where r4 goes
@@ -228,7 +251,9 @@ k_forward5(const __grid_constant__ DevModel model, Blob bl, int n_regions, doubl
         // per-lane sequence pointers: cell (x, y) of diagonal d consumes X[x-1] and Y[y-1].  For x = 0 (y = 0) the
         // byte before the region is read and ignored: every term that uses it comes from an out-of-band neighbour.
         int x0 = (0 + L1) >> 1, y0 = (0 - L1) >> 1;  // coordinates of cell 0 of the previous diagonal
-        const uint8_t *px = bl.sym_x + rg.sym_x_off + x0 - 1 + jl, *py = bl.sym_y + rg.sym_y_off + y0 - 1 - jl;
+        // warp-uniform base pointers (shifted by the -1) + 32-bit per-lane offsets: one address add per load
+        const uint8_t *sxb = bl.sym_x + rg.sym_x_off - 1, *syb = bl.sym_y + rg.sym_y_off - 1;
+        unsigned xo = (unsigned) (x0 + jl), yo = (unsigned) (y0 - jl);
         __syncwarp();
         for (int d = 1; d <= D; d++) {
             cur = nxt;
@@ -237,22 +262,19 @@ k_forward5(const __grid_constant__ DevModel model, Blob bl, int n_regions, doubl
             const int w = (int) (nxt.cell_off - cur.cell_off);
             const int oLo = (L - 1 - L1) >> 1, oMi = (L - L2) >> 1;
             const int nx0 = (d + L) >> 1, ny0 = (d - L) >> 1;
-            px += nx0 - x0;
-            py += ny0 - y0;
+            xo += (unsigned) (nx0 - x0);
+            yo += (unsigned) (ny0 - y0);
             x0 = nx0;
             y0 = ny0;
             // per-lane neighbour geometry, branch-free: the match lane reads cell (d-2, xmy) twice, the gap lane the
             // lower (d-1, xmy-1) and upper (d-1, xmy+1) cells
             const double *nb_slot = chain ? slot2 : slot1;
             const int nb_off = chain ? oMi : oLo, nb_w = chain ? w2 : w1, nb_step = chain ? 0 : 1;
-            // posterior mode: does this diagonal carry a total?  (then all states also go to FT)
-            double *ft = nullptr;
-            if (!FULL && (cur.tot_flags & MAB_DIAG_IS_TOTAL))
-                ft = FT + (int64_t) bl.totals[cur.tot_flags & MAB_DIAG_TOT_MASK].full_off * 5;
+            double *f_match = F + cur.cell_off;  // posterior mode: the match plane
             for (int j0 = 0; j0 < w; j0 += 16) {
                 const int j = j0 + jl;
                 if (j < w) {
-                    const int cX = __ldg(px + j0), cY = __ldg(py - j0);
+                    const int cX = __ldg(sxb + (xo + (unsigned) j0)), cY = __ldg(syb + (yo - (unsigned) j0));
                     const double2 *e = etp_lane + (cX * 5 + cY) * (4 * W5_COPIES);
                     const double *c1 = nb_slot + clamp_pos(j + nb_off, nb_w) * 5;
                     const double *c2 = nb_slot + clamp_pos(j + nb_off + nb_step, nb_w) * 5;
@@ -269,30 +291,20 @@ k_forward5(const __grid_constant__ DevModel model, Blob bl, int n_regions, doubl
                         out[LX] = q.r2;
                         out[SY] = q.r3;
                     }
-                    if (FULL) {
-                        double *g = F + (cur.cell_off + j) * 5;
-                        g[s_out4] = q.r4;
-                        if (!chain) {
-                            g[SX] = q.r1;
-                            g[LX] = q.r2;
-                            g[SY] = q.r3;
-                        }
-                    } else {
-                        if (chain) F[cur.cell_off + j] = q.r4;
-                        if (ft != nullptr) {
-                            double *g = ft + (int64_t) j * 5;
-                            g[s_out4] = q.r4;
-                            if (!chain) {
-                                g[SX] = q.r1;
-                                g[LX] = q.r2;
-                                g[SY] = q.r3;
-                            }
-                        }
-                    }
+                    if (!FULL && chain) f_match[j] = q.r4;  // 16 consecutive doubles per half-warp
                 }
             }
             write_high_guard(slot, w, lane);
             __syncwarp();
+            // all five states leave through a coalesced copy of the finished ring slot: every diagonal in
+            // expectation mode, only the diagonals that carry a total (1 in 10) in posterior mode
+            if (FULL) {
+                double *g = F + cur.cell_off * 5;
+                for (int i = lane; i < w * 5; i += 32) g[i] = slot[5 + i];
+            } else if (cur.tot_flags & MAB_DIAG_IS_TOTAL) {
+                double *g = FT + (int64_t) bl.totals[cur.tot_flags & MAB_DIAG_TOT_MASK].full_off * 5;
+                for (int i = lane; i < w * 5; i += 32) g[i] = slot[5 + i];
+            }
             L2 = L1;
             L1 = L;
             w2 = w1;
@@ -324,7 +336,7 @@ k_backward5(const __grid_constant__ DevModel model, Blob bl, int n_tbs, double *
     if (lane < 15) ring[(lane / 5) * slot_doubles + lane % 5] = neg_inf();
     __syncthreads();
     const double2 *etp_lane = &sh.etp[role][0][0][lane & (W5_COPIES - 1)];
-    const double2 *coef_lane = &sh.coef[0][0][lane & (W5_COPIES - 1)];
+    const unsigned coef_lane = (unsigned) __cvta_generic_to_shared(&sh.coef[0][0][lane & (W5_COPIES - 1)]);
     const int s_out4 = role ? LY : M;
     // per-lane picks inside the neighbour cells, as byte-free state indices (see the table comment):
     //   match lane: v2 = nUp.SY v4 = nUp.LY v6 = nLo.SX v8 = nLo.LX;  gap lane: v2 = nLo.SX v4 = nUp.SY v6 = nLo.LX v8 = nUp.LY
@@ -363,7 +375,8 @@ k_backward5(const __grid_constant__ DevModel model, Blob bl, int n_tbs, double *
         // the neighbours of target cell (x, y) consume X[x] and/or Y[y] (0-based); at x = lX (y = lY) the byte after
         // the region is read and ignored: the neighbours that would use it are out of band (-inf)
         int x0 = (tb.hi + L1) >> 1, y0 = (tb.hi - L1) >> 1;
-        const uint8_t *px = bl.sym_x + rg.sym_x_off + x0 + jl, *py = bl.sym_y + rg.sym_y_off + y0 - jl;
+        const uint8_t *sxb = bl.sym_x + rg.sym_x_off, *syb = bl.sym_y + rg.sym_y_off;  // warp-uniform bases
+        unsigned xo = (unsigned) (x0 + jl), yo = (unsigned) (y0 - jl);                 // 32-bit per-lane offsets
         __syncwarp();
         for (int d = tb.hi - 1; d > tb.lo; d--) {
             up1 = cur;
@@ -373,19 +386,18 @@ k_backward5(const __grid_constant__ DevModel model, Blob bl, int n_tbs, double *
             const int oUp = (L - 1 - L1) >> 1;  // (d+1, xmy-1): the cell whose "upper" is the target
             const int oMi = (L - L2) >> 1;      // (d+2, xmy)
             const int nx0 = (d + L) >> 1, ny0 = (d - L) >> 1;
-            px += nx0 - x0;
-            py += ny0 - y0;
+            xo += (unsigned) (nx0 - x0);
+            yo += (unsigned) (ny0 - y0);
             x0 = nx0;
             y0 = ny0;
             const bool keep = d <= tb.from;
-            const bool to_edge = d == tb.from + 1;
-            double *bt = nullptr;
-            if (!FULL && keep && (cur.tot_flags & MAB_DIAG_IS_TOTAL))
-                bt = BT + (int64_t) bl.totals[cur.tot_flags & MAB_DIAG_TOT_MASK].full_off * 5;
+            // where the match lanes put their result: the match plane of B (posterior mode, kept diagonals), the
+            // edge buffer (first discarded diagonal of an intermediate traceback, both modes), or nowhere
+            double *b_match = d == tb.from + 1 ? edge + tb.edge_off : ((!FULL && keep) ? B + cur.cell_off : nullptr);
             for (int j0 = 0; j0 < w; j0 += 16) {
                 const int j = j0 + jl;
                 if (j < w) {
-                    const int cX = __ldg(px + j0), cY = __ldg(py - j0);
+                    const int cX = __ldg(sxb + (xo + (unsigned) j0)), cY = __ldg(syb + (yo - (unsigned) j0));
                     const double2 *e = etp_lane + (cX * 5 + cY) * (4 * W5_COPIES);
                     const int iUp = j + oUp;
                     const double *nUp = slot1 + clamp_pos(iUp, w1) * 5;
@@ -408,34 +420,20 @@ k_backward5(const __grid_constant__ DevModel model, Blob bl, int n_tbs, double *
                         out[SY] = q.r2;
                         out[LX] = q.r3;
                     }
-                    if (keep) {
-                        if (FULL) {
-                            double *g = B + (cur.cell_off + j) * 5;
-                            g[s_out4] = q.r4;
-                            if (!chain) {
-                                g[SX] = q.r1;
-                                g[SY] = q.r2;
-                                g[LX] = q.r3;
-                            }
-                        } else {
-                            if (chain) B[cur.cell_off + j] = q.r4;
-                            if (bt != nullptr) {
-                                double *g = bt + (int64_t) j * 5;
-                                g[s_out4] = q.r4;
-                                if (!chain) {
-                                    g[SX] = q.r1;
-                                    g[SY] = q.r2;
-                                    g[LX] = q.r3;
-                                }
-                            }
-                        }
-                    } else if (to_edge && chain) {
-                        edge[tb.edge_off + j] = q.r4;
-                    }
+                    if (chain && b_match != nullptr) b_match[j] = q.r4;
                 }
             }
             write_high_guard(slot, w, lane);
             __syncwarp();
+            if (keep) {  // all five states: coalesced copy of the finished ring slot (see k_forward5)
+                if (FULL) {
+                    double *g = B + cur.cell_off * 5;
+                    for (int i = lane; i < w * 5; i += 32) g[i] = slot[5 + i];
+                } else if (cur.tot_flags & MAB_DIAG_IS_TOTAL) {
+                    double *g = BT + (int64_t) bl.totals[cur.tot_flags & MAB_DIAG_TOT_MASK].full_off * 5;
+                    for (int i = lane; i < w * 5; i += 32) g[i] = slot[5 + i];
+                }
+            }
             L2 = L1;
             L1 = L;
             w2 = w1;

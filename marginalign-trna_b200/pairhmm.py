@@ -8,6 +8,7 @@ all arithmetic happens in libmargin_b200.so (CUDA, sm_100a).  There is no CPU fa
 operations raise RuntimeError.
 """
 import ctypes as C
+import time
 from concurrent.futures import ThreadPoolExecutor
 from dataclasses import dataclass
 
@@ -276,11 +277,11 @@ class DevicePlan:
         # 256-byte aligned view of the workspace
         self.ws_ptr = (self.d_ws.data_ptr() + 255) & ~255
 
-    @classmethod
-    def build_on_device(cls, batch, params, device, expectations=False, staging=None):
-        """Uploads bases + cigars of `batch` (one pinned staging buffer, one H2D copy) and plans on the GPU."""
-        torch = require_cuda()
-        L = capi.load()
+    @staticmethod
+    def pack_inputs(batch, staging=None):
+        """Packs bases + cigars of `batch` into one pinned host buffer (host-only work; safe to run on a helper
+        thread while the GPU is busy).  Returns the tuple build_on_device consumes."""
+        torch = _torch()
         n = batch.n
         parts = [np.ascontiguousarray(batch.off_x, dtype=np.int64), np.ascontiguousarray(batch.off_y, dtype=np.int64),
                  np.ascontiguousarray(batch.off_ops, dtype=np.int64), np.ascontiguousarray(batch.lens, dtype=np.int32),
@@ -296,13 +297,21 @@ class DevicePlan:
         for a, o in zip(parts, offs):
             if a.nbytes:
                 hv[o:o + a.nbytes] = a.view(np.uint8).reshape(-1)
+        len_x, len_y = (int(batch.off_x[-1]), int(batch.off_y[-1])) if n else (0, 0)
+        return h_in, offs, total, n, len_x, len_y
+
+    @classmethod
+    def build_on_device(cls, batch, params, device, expectations=False, staging=None, packed=None):
+        """Uploads bases + cigars (one pinned staging buffer, one H2D copy) and plans on the GPU."""
+        torch = require_cuda()
+        L = capi.load()
+        h_in, offs, total, n, len_x, len_y = packed if packed is not None else cls.pack_inputs(batch, staging)
         d_in = torch.empty(total + 256, dtype=torch.uint8, device=device)
         base = (d_in.data_ptr() + 255) & ~255
         d_view = d_in[base - d_in.data_ptr():base - d_in.data_ptr() + total]
         d_view.copy_(h_in[:total], non_blocking=True)
         ptr = [base + o for o in offs]
         p = params.to_c()
-        len_x, len_y = int(batch.off_x[-1]) if n else 0, int(batch.off_y[-1]) if n else 0
         need = int(L.mab_plan_device_arena_hint(C.byref(p), n, len_x, len_y))
         stream = C.c_void_p(torch.cuda.current_stream(device).cuda_stream)
         for _ in range(3):
@@ -359,7 +368,9 @@ class PairHmmEngine:
             raise ValueError("plan_on must be 'device' or 'host'")
         self.plan_on = plan_on
         self.last_stats = {}
-        self._staging = _Staging()
+        self._t = {"wait_pack_s": 0.0, "plan_s": 0.0, "compute_s": 0.0, "host_alloc_s": 0.0, "drain_s": 0.0}
+        self._stagings = (_Staging(), _Staging())
+        self._copy_stream = torch.cuda.Stream(device=self.device)
 
     # ---------------------------------------------------------------- chunking
     def _chunks(self, batch, params):
@@ -386,8 +397,21 @@ class PairHmmEngine:
         """Yields one DevicePlan per chunk.  Host planning of chunk k+1 overlaps the GPU work on chunk k."""
         chunks = self._chunks(batch, params)
         if self.plan_on == "device":
-            for b in chunks:
-                yield DevicePlan.build_on_device(batch.slice(*b), params, self.device, expectations, self._staging)
+            # the inputs of chunk k+1 are packed into pinned memory by a helper thread while the GPU works on chunk k
+            # (two staging buffers alternate: the H2D copy of a buffer has completed before build_on_device returns)
+            with ThreadPoolExecutor(1) as pool:
+                pack = lambda i: DevicePlan.pack_inputs(batch.slice(*chunks[i]), self._stagings[i % 2])
+                fut = pool.submit(pack, 0)
+                for ci in range(len(chunks)):
+                    t0 = time.perf_counter()
+                    packed = fut.result()
+                    t1 = time.perf_counter()
+                    if ci + 1 < len(chunks):
+                        fut = pool.submit(pack, ci + 1)
+                    dplan = DevicePlan.build_on_device(None, params, self.device, expectations, packed=packed)
+                    self._t["wait_pack_s"] += t1 - t0
+                    self._t["plan_s"] += time.perf_counter() - t1
+                    yield dplan
             return
         with ThreadPoolExecutor(1) as pool:
             make = lambda b: Plan.from_batch(batch.slice(*b), params, self.plan_threads)
@@ -424,15 +448,27 @@ class PairHmmEngine:
         pending = []  # D2H copies in flight: (first alignment, n alignments, pinned tensors)
         first = 0
         with torch.cuda.device(self.device):
+            for k in self._t:
+                self._t[k] = 0.0
             for dplan in self._device_plans(batch, params, False):
                 info = dplan.plan.info
+                t0 = time.perf_counter()
                 d_off, d_x, d_y, d_p = self.posteriors_device(model, dplan)
-                # pinned host blocks (torch's pinned allocator recycles them between calls), asynchronous D2H
+                t1 = time.perf_counter()
+                self._t["compute_s"] += t1 - t0
+                # pinned host blocks (torch's pinned allocator recycles them between calls); the D2H copies run on a
+                # second stream so they overlap the kernels of the next chunk
                 host = [torch.empty(t.shape, dtype=t.dtype, pin_memory=True) for t in (d_off, d_x, d_y, d_p)]
-                for h, t in zip(host, (d_off, d_x, d_y, d_p)):
-                    h.copy_(t, non_blocking=True)
-                ev = torch.cuda.Event()
-                ev.record(torch.cuda.current_stream(self.device))
+                done = torch.cuda.Event()
+                done.record(torch.cuda.current_stream(self.device))
+                with torch.cuda.stream(self._copy_stream):
+                    self._copy_stream.wait_event(done)
+                    for h, t in zip(host, (d_off, d_x, d_y, d_p)):
+                        h.copy_(t, non_blocking=True)
+                        t.record_stream(self._copy_stream)
+                    ev = torch.cuda.Event()
+                    ev.record(self._copy_stream)
+                self._t["host_alloc_s"] += time.perf_counter() - t1
                 pending.append((first, info.n_alignments, host, ev, (d_off, d_x, d_y, d_p)))
                 first += info.n_alignments
                 stats["cells"] += info.n_cells
@@ -441,6 +477,7 @@ class PairHmmEngine:
                 stats["h2d_bytes"] += dplan.h2d_bytes
                 stats["chunks"] += 1
                 del dplan
+            t_drain = time.perf_counter()
             for a0, na, host, ev, _keep in pending:
                 ev.synchronize()
                 off = host[0].numpy()
@@ -448,6 +485,8 @@ class PairHmmEngine:
                 offs.append(off[1:] + base)
                 blocks.append((a0, a0 + na, base, host[1].numpy(), host[2].numpy(), host[3].numpy()))
                 stats["d2h_bytes"] += sum(h.numel() * h.element_size() for h in host)
+            self._t["drain_s"] = time.perf_counter() - t_drain
+        stats["host_wall"] = dict(self._t)
         if not blocks:
             blocks = [(0, 0, 0, np.zeros(0, np.int32), np.zeros(0, np.int32), np.zeros(0, np.int32))]
         self.last_stats = stats

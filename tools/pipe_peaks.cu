@@ -35,7 +35,9 @@ __global__ void k_pipe(double *out, double a, double b, int iters) {
             if (OP == 0) v[c] = __dadd_rn(v[c], b);
             if (OP == 1) v[c] = __dmul_rn(v[c], b);
             if (OP == 2) v[c] = __fma_rn(v[c], b, a);
-            if (OP == 3) n[c] += (v[c] > (double) n[c]) ? 3 : 1;  // DSETP + SEL + IADD per step
+            if (OP == 3) n[c] += (v[c] > b) ? 3 : 1;                     // DSETP + SEL + IADD per step
+            if (OP == 7) v[c] = __dadd_rn(v[c], (double) f[c]);          // F2F.F64.F32 + DADD per step
+            if (OP == 8) f[c] = __fadd_rn(f[c], 1.0f), v[c] = (double) f[c];  // FADD + F2F.F64.F32 per step
             if (OP == 4) f[c] = __fadd_rn(f[c], (float) b);
             if (OP == 5) f[c] = __fmaf_rn(f[c], (float) b, (float) a);
             if (OP == 6) n[c] = n[c] * 3 + i;
@@ -96,7 +98,7 @@ int main() {
     const int sms = p.multiProcessorCount;
     const double dadd = run<0>(sms, d_out, 1), dmul = run<1>(sms, d_out, 1), dfma = run<2>(sms, d_out, 1),
                  dsetp = run<3>(sms, d_out, 1), fadd = run<4>(sms, d_out, 1), ffma = run<5>(sms, d_out, 1),
-                 imad = run<6>(sms, d_out, 1);
+                 imad = run<6>(sms, d_out, 1), f2f_dadd = run<7>(sms, d_out, 1), f2f_fadd = run<8>(sms, d_out, 1);
     k_dadd_latency<<<1, 32>>>(d_out, 0.5, 4096, d_cyc);
     cudaDeviceSynchronize();
     k_dadd_latency<<<1, 32>>>(d_out, 0.5, 4096, d_cyc);
@@ -105,7 +107,7 @@ int main() {
     cudaDeviceGetAttribute(&clk, cudaDevAttrClockRate, 0);
     printf("{\"gpu\": \"%s\", \"sms\": %d, \"clock_khz_attr\": %d, \"dadd_tops\": %.3f, \"dmul_tops\": %.3f, "
            "\"dfma_tops\": %.3f, \"dsetp_sel_tops\": %.3f, \"fadd_tops\": %.3f, \"ffma_tops\": %.3f, \"imad_tops\": %.3f, "
-           "\"dadd_latency_cycles\": %.2f}\n",
-           p.name, sms, clk, dadd, dmul, dfma, dsetp, fadd, ffma, imad, (double) h_cyc / (4096.0 * 4));
+           "\"f2f_f64_f32_plus_dadd_tops\": %.3f, \"f2f_f64_f32_plus_fadd_tops\": %.3f, \"dadd_latency_cycles\": %.2f}\n",
+           p.name, sms, clk, dadd, dmul, dfma, dsetp, fadd, ffma, imad, f2f_dadd, f2f_fadd, (double) h_cyc / (4096.0 * 4));
     return cudaGetLastError() == cudaSuccess ? 0 : 2;
 }
