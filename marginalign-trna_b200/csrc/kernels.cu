@@ -596,24 +596,60 @@ k_emit_diag(Blob bl, int64_t n_diagonals, const int32_t *__restrict__ pint, cons
 }
 
 // ------------------------------------------------------------------------------------------------ expectations
+// diagonalCalculationExpectations + updateExpectations (pairwiseAligner.c:348-368, 617-628).
+//
+// One warp per region (dynamic queue), but the lanes do not follow diagonals: a region's cells are contiguous in
+// memory (diagonal after diagonal), so the warp sweeps them 32 at a time -- every lane busy whatever the band width --
+// and each lane finds the diagonal of its cell among the few diagonal starts the chunk touches.  Per cell: 13 (9)
+// exp(f_from + b_to + (eP + tP) - total), in the reference's operand order.  Transition sums live in registers;
+// emission sums in warp-private shared-memory bins with one column per lane pair [S*16 bins][16], added with plain
+// read-modify-writes (lanes 0-15, then 16-31), so there is no atomic and no conflict.  One global atomic per bin per
+// warp at the very end.
+#define EXP_WARPS 4
 
-// diagonalCalculationExpectations + updateExpectations (pairwiseAligner.c:348-368, 617-628), one warp per region.
-// Per block: transitions / emissions / likelihood are accumulated in shared memory, then added to the global
-// accumulator with one atomic per entry.
 template <int S>
-__global__ void __launch_bounds__(THREADS_PER_BLOCK)
+struct TransTable;
+template <>
+struct TransTable<5> {  // stateMachine5 cellCalculate order (stateMachine.c:399-429): group, from, to
+    static constexpr int N = 13, NL = 4, NM = 5;
+    __device__ static constexpr int from(int k) {
+        constexpr int f[13] = {M, SX, M, LX, M, SX, SY, LX, LY, M, SY, M, LY};
+        return f[k];
+    }
+    __device__ static constexpr int to(int k) {
+        constexpr int t[13] = {SX, SX, LX, LX, M, M, M, M, M, SY, SY, LY, LY};
+        return t[k];
+    }
+};
+template <>
+struct TransTable<3> {  // stateMachine3 cellCalculate order (stateMachine.c:636-661)
+    static constexpr int N = 9, NL = 3, NM = 3;
+    __device__ static constexpr int from(int k) {
+        constexpr int f[9] = {M, SX, SY, M, SX, SY, M, SY, SX};
+        return f[k];
+    }
+    __device__ static constexpr int to(int k) {
+        constexpr int t[9] = {SX, SX, SX, M, M, M, SY, SY, SY};
+        return t[k];
+    }
+};
+
+template <int S>
+__global__ void __launch_bounds__(EXP_WARPS * 32)
 k_expect(const __grid_constant__ DevModel model, Blob bl, int n_regions, const double *__restrict__ F,
          const double *__restrict__ B, const double *__restrict__ totals, double *__restrict__ out, int *counter) {
-    constexpr int NT = S == 5 ? 13 : 9;
-    constexpr int NL = S == 5 ? 4 : 3, NM = S == 5 ? 5 : 3;
-    constexpr int NOUT = S * S + S * 16 + 1;
+    using TT = TransTable<S>;
+    constexpr int NT = TT::N, NL = TT::NL, NM = TT::NM;
+    constexpr int NE = S * 16, NOUT = S * S + NE + 1;
     __shared__ DevModel sm;
-    __shared__ double acc[NOUT];
+    __shared__ double bins_all[EXP_WARPS][NE][16];
     for (int i = threadIdx.x; i < (int) (sizeof(DevModel) / 4); i += blockDim.x)
         ((int32_t *) &sm)[i] = ((const int32_t *) &model)[i];
-    for (int i = threadIdx.x; i < NOUT; i += blockDim.x) acc[i] = 0.0;
+    for (int i = threadIdx.x; i < EXP_WARPS * NE * 16; i += blockDim.x) (&bins_all[0][0][0])[i] = 0.0;
     __syncthreads();
-    const int lane = threadIdx.x & 31;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    double(*bins)[16] = bins_all[warp];
+    const int col = lane & 15;
     const double NINF = neg_inf();
     double tacc[NT];
 #pragma unroll
@@ -627,83 +663,97 @@ k_expect(const __grid_constant__ DevModel model, Blob bl, int n_regions, const d
         const DiagDesc *dd = bl.diags + rg.diag_base;
         const uint8_t *sx = bl.sym_x + rg.sym_x_off, *sy = bl.sym_y + rg.sym_y_off;
         const int D = rg.lX + rg.lY;
-        for (int d = 1; d <= D; d++) {
-            const DiagDesc cur = dd[d], p1 = dd[d - 1];
-            const int w = (int) (dd[d + 1].cell_off - cur.cell_off);
-            const int w1 = (int) (cur.cell_off - p1.cell_off);
-            const double total = totals[cur.tot_flags & MAB_DIAG_TOT_MASK];
-            if (lane == 0) lik += total;  // hmmExpectations->likelihood += totalProbability, once per diagonal (:625)
-            const bool mid_ok = d >= 2 && !(cur.tot_flags & MAB_DIAG_NO_MIDDLE);
-            int64_t c2 = 0;
-            int L2 = 0, w2 = 0;
-            if (d >= 2) {
-                const DiagDesc p2 = dd[d - 2];
-                c2 = p2.cell_off;
-                L2 = p2.xmyL;
-                w2 = (int) (p1.cell_off - p2.cell_off);
+        const int64_t c_begin = dd[1].cell_off, c_end = dd[D + 1].cell_off;  // diagonals 1 .. D
+        int g0 = 1;  // diagonal of the first cell of the current chunk
+        for (int64_t c0 = c_begin; c0 < c_end; c0 += 32) {
+            // starts of the diagonals after g0: lane i holds the start of diagonal g0 + 1 + i (or "infinity")
+            const int gi = g0 + 1 + lane;
+            const int64_t start_i = gi <= D ? dd[gi].cell_off : c_end + 64;
+            const int64_t c = c0 + lane;
+            int k_adv = 0, n_starts = 0;  // starts <= my cell; starts inside the chunk (uniform)
+            bool next_starts_new = false;
+            for (int i = 0; i < 32; i++) {
+                const int64_t si = __shfl_sync(FULL_MASK, start_i, i);
+                if (si > c0 + 31) {  // uniform: no later diagonal starts inside this chunk (starts strictly increase,
+                    next_starts_new = si == c0 + 32;  // so this always triggers by i = 31)
+                    break;
+                }
+                k_adv += si <= c ? 1 : 0;
+                n_starts++;
             }
-            const int oLo = (cur.xmyL - 1 - p1.xmyL) >> 1, oMi = (cur.xmyL - L2) >> 1;
-            for (int j = lane; j < w; j += 32) {
+            const bool active = c < c_end;
+            const int d = g0 + k_adv;
+            g0 += n_starts + (next_starts_new ? 1 : 0);  // diagonal of the first cell of the next chunk
+            double e_to[S];
+#pragma unroll
+            for (int s = 0; s < S; s++) e_to[s] = 0.0;
+            int row = -1;  // emission row cX*4+cY, or -1: no emission (inactive lane, or a symbol is N, :359)
+            if (active) {
+                const DiagDesc cur = dd[d], p1 = dd[d - 1];
+                const int j = (int) (c - cur.cell_off);
+                const int w1 = (int) (cur.cell_off - p1.cell_off);
+                const double total = totals[cur.tot_flags & MAB_DIAG_TOT_MASK];
+                if (j == 0) lik += total;  // hmmExpectations->likelihood += totalProbability, once per diagonal (:625)
+                const bool mid_ok = d >= 2 && !(cur.tot_flags & MAB_DIAG_NO_MIDDLE);
+                int64_t c2 = 0;
+                int L2 = 0, w2 = 0;
+                if (d >= 2) {
+                    const DiagDesc p2 = dd[d - 2];
+                    c2 = p2.cell_off;
+                    L2 = p2.xmyL;
+                    w2 = (int) (p1.cell_off - p2.cell_off);
+                }
                 const int xmy = cur.xmyL + 2 * j;
                 const int x = (d + xmy) >> 1, y = (d - xmy) >> 1;
                 const int cX = x > 0 ? sx[x - 1] : 4, cY = y > 0 ? sy[y - 1] : 4;
-                const int iLo = j + oLo, iUp = iLo + 1, iMi = j + oMi;
-                const Cell<S> b = cell_load<S>(B + (cur.cell_off + j) * S);
+                if (cX < 4 && cY < 4) row = cX * 4 + cY;
+                const int iLo = j + ((cur.xmyL - 1 - p1.xmyL) >> 1), iUp = iLo + 1, iMi = j + ((cur.xmyL - L2) >> 1);
+                const Cell<S> b = cell_load<S>(B + c * S);
                 const Cell<S> lo = (iLo >= 0 && iLo < w1) ? cell_load<S>(F + (p1.cell_off + iLo) * S) : cell_fill<S>(NINF);
                 const Cell<S> up = (iUp >= 0 && iUp < w1) ? cell_load<S>(F + (p1.cell_off + iUp) * S) : cell_fill<S>(NINF);
                 const Cell<S> mi = (mid_ok && iMi >= 0 && iMi < w2) ? cell_load<S>(F + (c2 + iMi) * S) : cell_fill<S>(NINF);
                 const double *eL = sm.etp_lower[cX], *eM = sm.etp_middle[cX * 5 + cY], *eU = sm.etp_upper[cY];
-                double e_to[S];
-#pragma unroll
-                for (int s = 0; s < S; s++) e_to[s] = 0.0;
 #pragma unroll
                 for (int k = 0; k < NT; k++) {
-                    const int from = sm.t_from[k], to = sm.t_to[k];
-                    double f, e;
-                    if (k < NL) {
-                        f = lo.v[0];
-#pragma unroll
-                        for (int s = 1; s < S; s++) f = from == s ? lo.v[s] : f;
-                        e = eL[k];
-                    } else if (k < NL + NM) {
-                        f = mi.v[0];
-#pragma unroll
-                        for (int s = 1; s < S; s++) f = from == s ? mi.v[s] : f;
-                        e = eM[k - NL];
-                    } else {
-                        f = up.v[0];
-#pragma unroll
-                        for (int s = 1; s < S; s++) f = from == s ? up.v[s] : f;
-                        e = eU[k - NL - NM];
-                    }
-                    double bt = b.v[0];
-#pragma unroll
-                    for (int s = 1; s < S; s++) bt = to == s ? b.v[s] : bt;
+                    const double f = k < NL ? lo.v[TT::from(k)] : (k < NL + NM ? mi.v[TT::from(k)] : up.v[TT::from(k)]);
+                    const double e = k < NL ? eL[k] : (k < NL + NM ? eM[k - NL] : eU[k - NL - NM]);
                     // exp(fromCells[from] + toCells[to] + (eP + tP) - totalProbability), left to right (:356)
-                    const double p = exp(__dsub_rn(__dadd_rn(__dadd_rn(f, bt), e), total));
+                    const double p = exp(__dsub_rn(__dadd_rn(__dadd_rn(f, b.v[TT::to(k)]), e), total));
                     tacc[k] += p;
-#pragma unroll
-                    for (int s = 0; s < S; s++) e_to[s] += to == s ? p : 0.0;
-                }
-                if (cX < 4 && cY < 4) {
-#pragma unroll
-                    for (int s = 0; s < S; s++) atomicAdd(&acc[S * S + s * 16 + cX * 4 + cY], e_to[s]);
+                    e_to[TT::to(k)] += p;
                 }
             }
+            // emission bins: lanes 0-15 first, then 16-31 on the same columns
+            if (row >= 0 && lane < 16) {
+#pragma unroll
+                for (int s = 0; s < S; s++) bins[s * 16 + row][col] += e_to[s];
+            }
+            __syncwarp();
+            if (row >= 0 && lane >= 16) {
+#pragma unroll
+                for (int s = 0; s < S; s++) bins[s * 16 + row][col] += e_to[s];
+            }
+            __syncwarp();
         }
     }
-    // reduce the per-lane transition sums
+    // per-warp reduction: transitions and likelihood by shuffles, emission bins over their 16 columns
 #pragma unroll
     for (int k = 0; k < NT; k++) {
         double v = tacc[k];
 #pragma unroll
         for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(FULL_MASK, v, o);
-        if (lane == 0) atomicAdd(&acc[sm.t_from[k] * S + sm.t_to[k]], v);
+        if (lane == 0 && v != 0.0) atomicAdd(&out[TT::from(k) * S + TT::to(k)], v);
     }
-    if (lane == 0) atomicAdd(&acc[NOUT - 1], lik);
-    __syncthreads();
-    for (int i = threadIdx.x; i < NOUT; i += blockDim.x)
-        if (acc[i] != 0.0) atomicAdd(&out[i], acc[i]);
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) lik += __shfl_xor_sync(FULL_MASK, lik, o);
+    if (lane == 0 && lik != 0.0) atomicAdd(&out[NOUT - 1], lik);
+    __syncwarp();
+    for (int i = lane; i < NE; i += 32) {
+        double v = 0.0;
+#pragma unroll
+        for (int q = 0; q < 16; q++) v += bins[i][q];
+        if (v != 0.0) atomicAdd(&out[S * S + i], v);
+    }
 }
 
 // ------------------------------------------------------------------------------------------------ launch helpers
@@ -897,7 +947,7 @@ int run_expectations(const DevModel &dm, const mab_plan *plan, const void *d_blo
     if (rc) return rc;
     {
         LaunchTimer lt(K_EXPECT, st);
-        k_expect<S><<<grid_for(h.n_regions, 8), THREADS_PER_BLOCK, 0, st>>>(dm, bl, (int) h.n_regions, w.fwd, w.bwd,
+        k_expect<S><<<grid_for(h.n_regions, 4, EXP_WARPS), EXP_WARPS * 32, 0, st>>>(dm, bl, (int) h.n_regions, w.fwd, w.bwd,
                                                                         w.totals, d_out, w.counters + 4);
     }
     return check(cudaGetLastError(), "expectation launch");
