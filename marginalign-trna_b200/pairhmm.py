@@ -256,7 +256,7 @@ class DevicePlan:
     Two ways to get one: from a host-built Plan (the blob is copied over PCIe), or DevicePlan.build_on_device, which
     uploads only the raw inputs and runs the planner on the GPU (mab_plan_build_device)."""
 
-    def __init__(self, plan: Plan, device, expectations=False, stream=None, _resident=None):
+    def __init__(self, plan: Plan, device, expectations=False, stream=None, _resident=None, _alloc_ws=True):
         torch = require_cuda()
         self.plan = plan
         self.device = device
@@ -269,13 +269,28 @@ class DevicePlan:
                 self.d_blob.copy_(self.h_blob, non_blocking=True)
             self.blob_ptr = self.d_blob.data_ptr()
             self.h2d_bytes = nb
+            self._inputs = None
         else:
             self.d_blob, self.blob_ptr, self.h2d_bytes, self._inputs = _resident
         ws = plan.info.workspace_bytes_expectations if expectations else plan.info.workspace_bytes_posteriors
         self.ws_bytes = int(ws)
-        self.d_ws = torch.empty(self.ws_bytes + 256, dtype=torch.uint8, device=device)
-        # 256-byte aligned view of the workspace
-        self.ws_ptr = (self.d_ws.data_ptr() + 255) & ~255
+        self.d_ws = None
+        if _alloc_ws:
+            self.alloc_workspace()
+
+    def alloc_workspace(self):
+        """Scratch for the DP kernels, allocated on the caller's current stream (256-byte aligned view)."""
+        if self.d_ws is None:
+            self.d_ws = _torch().empty(self.ws_bytes + 256, dtype=_torch().uint8, device=self.device)
+            self.ws_ptr = (self.d_ws.data_ptr() + 255) & ~255
+
+    def adopt(self, stream):
+        """Hands a plan built on another stream (already synchronised) over to `stream`: the caching allocator must
+        not recycle the blob or the inputs while kernels of `stream` still read them."""
+        for t in (self.d_blob,) + tuple(x for x in (self._inputs or ()) if hasattr(x, "record_stream")):
+            if t is not None and t.is_cuda:
+                t.record_stream(stream)
+        self.alloc_workspace()
 
     @staticmethod
     def pack_inputs(batch, staging=None):
@@ -301,7 +316,8 @@ class DevicePlan:
         return h_in, offs, total, n, len_x, len_y
 
     @classmethod
-    def build_on_device(cls, batch, params, device, expectations=False, staging=None, packed=None):
+    def build_on_device(cls, batch, params, device, expectations=False, staging=None, packed=None,
+                        alloc_ws=True):
         """Uploads bases + cigars (one pinned staging buffer, one H2D copy) and plans on the GPU."""
         torch = require_cuda()
         L = capi.load()
@@ -329,7 +345,8 @@ class DevicePlan:
         else:
             raise RuntimeError("mab_plan_build_device: arena sizing did not converge")
         plan = Plan(h)
-        return cls(plan, device, expectations=expectations, _resident=(arena, aptr, total, (d_in, h_in)))
+        return cls(plan, device, expectations=expectations, _resident=(arena, aptr, total, (d_in, h_in)),
+                   _alloc_ws=alloc_ws)
 
 
 class _Staging:
@@ -368,9 +385,10 @@ class PairHmmEngine:
             raise ValueError("plan_on must be 'device' or 'host'")
         self.plan_on = plan_on
         self.last_stats = {}
-        self._t = {"wait_pack_s": 0.0, "plan_s": 0.0, "compute_s": 0.0, "host_alloc_s": 0.0, "drain_s": 0.0}
+        self._t = {"wait_plan_s": 0.0, "plan_s": 0.0, "compute_s": 0.0, "host_alloc_s": 0.0, "drain_s": 0.0}
         self._stagings = (_Staging(), _Staging())
         self._copy_stream = torch.cuda.Stream(device=self.device)
+        self._plan_stream = torch.cuda.Stream(device=self.device)
 
     # ---------------------------------------------------------------- chunking
     def _chunks(self, batch, params):
@@ -396,21 +414,30 @@ class PairHmmEngine:
     def _device_plans(self, batch, params, expectations):
         """Yields one DevicePlan per chunk.  Host planning of chunk k+1 overlaps the GPU work on chunk k."""
         chunks = self._chunks(batch, params)
+        torch = self.torch
         if self.plan_on == "device":
-            # the inputs of chunk k+1 are packed into pinned memory by a helper thread while the GPU works on chunk k
-            # (two staging buffers alternate: the H2D copy of a buffer has completed before build_on_device returns)
+            # chunk k+1 is packed into pinned memory, uploaded and planned by a helper thread on its own stream while
+            # the DP kernels of chunk k run on the caller's stream (two staging buffers alternate: the H2D copy of a
+            # buffer has completed before the helper hands the plan over)
+            def make(i):
+                t0 = time.perf_counter()
+                with torch.cuda.device(self.device), torch.cuda.stream(self._plan_stream):
+                    packed = DevicePlan.pack_inputs(batch.slice(*chunks[i]), self._stagings[i % 2])
+                    dplan = DevicePlan.build_on_device(None, params, self.device, expectations, packed=packed,
+                                                       alloc_ws=False)
+                    self._plan_stream.synchronize()
+                self._t["plan_s"] += time.perf_counter() - t0
+                return dplan
+
             with ThreadPoolExecutor(1) as pool:
-                pack = lambda i: DevicePlan.pack_inputs(batch.slice(*chunks[i]), self._stagings[i % 2])
-                fut = pool.submit(pack, 0)
+                fut = pool.submit(make, 0)
                 for ci in range(len(chunks)):
                     t0 = time.perf_counter()
-                    packed = fut.result()
-                    t1 = time.perf_counter()
+                    dplan = fut.result()
+                    self._t["wait_plan_s"] += time.perf_counter() - t0
                     if ci + 1 < len(chunks):
-                        fut = pool.submit(pack, ci + 1)
-                    dplan = DevicePlan.build_on_device(None, params, self.device, expectations, packed=packed)
-                    self._t["wait_pack_s"] += t1 - t0
-                    self._t["plan_s"] += time.perf_counter() - t1
+                        fut = pool.submit(make, ci + 1)
+                    dplan.adopt(torch.cuda.current_stream(self.device))
                     yield dplan
             return
         with ThreadPoolExecutor(1) as pool:
