@@ -400,12 +400,16 @@ class PairHmmEngine:
             params.diagonal_expansion + 4)
         cum = np.cumsum(est.astype(np.int64))
         bounds, start, base = [], 0, 0
+        # the first chunk is a quarter of the others: nothing overlaps its packing, upload and planning, so the
+        # pipeline (helper thread plans chunk k+1 while chunk k computes) should fill quickly
+        limit = max(self.max_cells // 4, 1)
         while start < batch.n:
-            end = int(np.searchsorted(cum, base + self.max_cells, side="right"))
+            end = int(np.searchsorted(cum, base + limit, side="right"))
             end = max(end, start + 1)
             bounds.append((start, min(end, batch.n)))
             start = bounds[-1][1]
             base = int(cum[start - 1])
+            limit = self.max_cells
         return bounds
 
     def _stream_ptr(self):
