@@ -48,7 +48,8 @@ def parse_args():
     ap.add_argument("--ref-sample", type=int, default=0, help="alignments in the CPU reference sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true", help="skip the end-to-end leg (profiling runs)")
-    ap.add_argument("--max-cells", type=int, default=400_000_000, help="DP cells resident per chunk")
+    ap.add_argument("--max-cells", type=int, default=0,
+                    help="DP cells resident per chunk (0: the engine sizes chunks from the band width and free HBM)")
     return ap.parse_args()
 
 
@@ -242,12 +243,12 @@ def run_ours(args, rank, world, local_rank):
     hmm = mab.Hmm.loadHmm(os.path.join(ROOT, "tests", "golden", "input_model.hmm"))
     model = mab.PairHmmModel.from_hmm(hmm)
     S = model.state_number
-    eng = mab.PairHmmEngine(device=dev, max_cells=args.max_cells)
+    eng = mab.PairHmmEngine(device=dev, max_cells=args.max_cells or None)
     em = args.mode == "em"
 
     # ---- resident setup: plan every chunk and copy its blob into HBM; one workspace sized for the largest chunk
     t_plan0 = time.perf_counter()
-    chunks = eng._chunks(batch, params)
+    chunks = eng._chunks(batch, params, em)
     plans = [mab.Plan.from_batch(batch if b == (0, batch.n) else batch.subset(np.arange(b[0], b[1])), params)
              for b in chunks]
     t_plan = time.perf_counter() - t_plan0

@@ -155,10 +155,43 @@ int mab_posteriors_emit(const mab_plan *plan, const void *d_blob, void *d_ws, in
         int32_t *d_y, int32_t *d_p, int64_t capacity, void *stream);
 int mab_expectations(const mab_model *m, const mab_plan *plan, const void *d_blob, void *d_ws, int64_t ws_bytes,
         double *d_out, void *stream);
+/* ---- realign tail --------------------------------------------------------------------------------
+ * Replaces what cPecanRealign does with the posterior pairs of an alignment before it prints the new cigar
+ * (cPecanRealign.c:590-631): reweightAlignedPairs2 (pairwiseAligner.c:1251-1261; AMAP gap reweighting),
+ * filterPairwiseAlignmentToMakePairsOrdered (multipleAligner.c:941-967; maximum-expected-accuracy chain with the
+ * reference's rand() jitter) and convertAlignedPairsToPairwiseAlignment (cPecanRealign.c:50-92; the cigar).  Works on
+ * the device-resident output of mab_posteriors_emit, for all n alignments of the batch at once; only cigars leave
+ * the GPU.
+ *   d_off_x / d_off_y [n+1] : sequence offsets of the batch (alignment i has lX = off_x[i+1] - off_x[i]); len_x/len_y
+ *                             their last entries.  d_pair_off [n+1], d_x, d_y, d_p: as written by mab_posteriors_*.
+ *   gap_gamma / match_gamma : cPecanRealign --gapGamma / --matchGamma (rounded to float like the reference).
+ *   d_rand [n_rand]         : the jitter stream, mab_rand_sequence(1, n_rand, ...) copied to the device; n_rand must
+ *                             be at least twice the largest pair count of one alignment (every reference process
+ *                             restarts rand() at seed 1 and draws twice per pair).
+ *   d_ws                    : scratch of mab_realign_workspace_bytes(...) bytes, 256-byte aligned; it carries the
+ *                             chains from mab_realign_chain to mab_realign_emit.
+ * mab_realign_chain writes d_op_off[n+1] / d_chain_off[n+1] (cigar operations / chain pairs per alignment, exclusive
+ * scans, totals in entry n); the caller sizes the outputs from them and calls mab_realign_emit, which writes the
+ * operations (op codes 0 M, 1 D, 2 I as in the input cigars) and, unless d_chain_x is NULL, the chain pairs. */
+int64_t mab_realign_workspace_bytes(int64_t n, int64_t n_pairs, int64_t len_x, int64_t len_y);
+int mab_realign_chain(int64_t n, const int64_t *d_off_x, const int64_t *d_off_y, int64_t len_x, int64_t len_y,
+        const int64_t *d_pair_off, const int32_t *d_x, const int32_t *d_y, const int32_t *d_p, int64_t n_pairs,
+        double gap_gamma, double match_gamma, const int32_t *d_rand, int64_t n_rand, void *d_ws, int64_t ws_bytes,
+        int64_t *d_op_off, int64_t *d_chain_off, void *stream);
+int mab_realign_emit(int64_t n, const int64_t *d_off_x, const int64_t *d_off_y, int64_t len_x, int64_t len_y,
+        int64_t n_pairs, void *d_ws, int64_t ws_bytes, const int64_t *d_op_off, const int64_t *d_chain_off,
+        uint8_t *d_ops, int32_t *d_lens, int32_t *d_chain_x, int32_t *d_chain_y, void *stream);
+/* The first n values glibc's rand() returns after srand(seed) (host memory): the jitter stream of st_random()
+ * (sonLib/C/impl/sonLibRandom.c:39-43) without touching the process-wide libc generator. */
+int mab_rand_sequence(uint32_t seed, int64_t n, int32_t *out);
+
 /* Debug/test hook: copies the forward / backward matrices ([cell][S] doubles, cells in plan order) and the totals
  * out of the workspace after a compute call.  Any pointer may be NULL. */
 int mab_debug_copy_matrices(const mab_plan *plan, const void *d_ws, double *h_fwd, double *h_bwd, double *h_totals,
         void *stream);
+/* Debug/test hook: warps that share one 5-state work item (region / traceback) in the wavefront kernels.
+ * 0 = chosen from the mean band width (default), 1, 2, 4 or 8 = forced.  Results do not depend on it. */
+int mab_debug_set_warp_group(int warps);
 /* Kernel launches issued by this library on the calling thread since the last reset (bench.py's gpu_launches). */
 int64_t mab_launch_count(int reset);
 /* Per-kernel timing for the roofline report: when enabled every launch is bracketed by CUDA events on its stream.

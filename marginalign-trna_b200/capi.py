@@ -66,6 +66,13 @@ SIGNATURES = {
     "mab_posteriors_emit": (C.c_int, [vp, vp, vp, C.c_int64, vp, vp, vp, C.c_int64, vp]),
     "mab_expectations": (C.c_int, [vp, vp, vp, vp, C.c_int64, vp, vp]),
     "mab_debug_copy_matrices": (C.c_int, [vp, vp, dp, dp, dp, vp]),
+    "mab_realign_workspace_bytes": (C.c_int64, [C.c_int64, C.c_int64, C.c_int64, C.c_int64]),
+    "mab_realign_chain": (C.c_int, [C.c_int64, vp, vp, C.c_int64, C.c_int64, vp, vp, vp, vp, C.c_int64, C.c_double,
+                                    C.c_double, vp, C.c_int64, vp, C.c_int64, vp, vp, vp]),
+    "mab_realign_emit": (C.c_int, [C.c_int64, vp, vp, C.c_int64, C.c_int64, C.c_int64, vp, C.c_int64, vp, vp, vp, vp,
+                                   vp, vp, vp]),
+    "mab_rand_sequence": (C.c_int, [C.c_uint32, C.c_int64, vp]),
+    "mab_debug_set_warp_group": (C.c_int, [C.c_int]),
     "mab_launch_count": (C.c_int64, [C.c_int]),
     "mab_kernel_timing": (C.c_int, [C.c_int]),
     "mab_kernel_count": (C.c_int, []),

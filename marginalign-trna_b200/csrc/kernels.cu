@@ -606,6 +606,7 @@ k_emit_diag(Blob bl, int64_t n_diagonals, const int32_t *__restrict__ pint, cons
 // read-modify-writes (lanes 0-15, then 16-31), so there is no atomic and no conflict.  One global atomic per bin per
 // warp at the very end.
 #define EXP_WARPS 4
+#define EXP_SEGMENT 4096  // cells per work item of k_expect
 
 template <int S>
 struct TransTable;
@@ -636,8 +637,9 @@ struct TransTable<3> {  // stateMachine3 cellCalculate order (stateMachine.c:636
 
 template <int S>
 __global__ void __launch_bounds__(EXP_WARPS * 32)
-k_expect(const __grid_constant__ DevModel model, Blob bl, int n_regions, const double *__restrict__ F,
-         const double *__restrict__ B, const double *__restrict__ totals, double *__restrict__ out, int *counter) {
+k_expect(const __grid_constant__ DevModel model, Blob bl, int64_t n_cells, int64_t n_diagonals,
+         const double *__restrict__ F, const double *__restrict__ B, const double *__restrict__ totals,
+         double *__restrict__ out, int *counter) {
     using TT = TransTable<S>;
     constexpr int NT = TT::N, NL = TT::NL, NM = TT::NM;
     constexpr int NE = S * 16, NOUT = S * S + NE + 1;
@@ -656,16 +658,40 @@ k_expect(const __grid_constant__ DevModel model, Blob bl, int n_regions, const d
     for (int k = 0; k < NT; k++) tacc[k] = 0.0;
     double lik = 0.0;
 
+    // Work item = a segment of EXP_SEGMENT consecutive cells of the global cell numbering (cells are numbered region by
+    // region, diagonal by diagonal), so that a batch of a few long reads spreads over the whole GPU as well as a
+    // batch of many short ones.  Inside a segment the cells are walked region by region in flat 32-cell chunks.
+    const int64_t n_segments = (n_cells + EXP_SEGMENT - 1) / EXP_SEGMENT;
     for (;;) {
         const int item = next_item(counter, lane);
-        if (item >= n_regions) break;
-        const RegionDesc rg = bl.regions[bl.order_fwd[item]];
+        if (item >= n_segments) break;
+        int64_t c0 = (int64_t) item * EXP_SEGMENT;
+        const int64_t seg_end = min(n_cells, c0 + EXP_SEGMENT);
+        // global diagonal that holds cell c0: the last one whose first cell is <= c0 (warp-uniform binary search)
+        int64_t g;
+        {
+            int64_t lo = 0, hi = n_diagonals;  // diags[n_diagonals] is the sentinel (cell_off = n_cells > c0)
+            while (hi - lo > 1) {
+                const int64_t mid = (lo + hi) >> 1;
+                if (bl.diags[mid].cell_off <= c0) lo = mid;
+                else hi = mid;
+            }
+            g = lo;
+        }
+        while (c0 < seg_end) {
+        const RegionDesc rg = bl.regions[bl.diag_region[g]];
         const DiagDesc *dd = bl.diags + rg.diag_base;
         const uint8_t *sx = bl.sym_x + rg.sym_x_off, *sy = bl.sym_y + rg.sym_y_off;
         const int D = rg.lX + rg.lY;
-        const int64_t c_begin = dd[1].cell_off, c_end = dd[D + 1].cell_off;  // diagonals 1 .. D
-        int g0 = 1;  // diagonal of the first cell of the current chunk
-        for (int64_t c0 = c_begin; c0 < c_end; c0 += 32) {
+        const int64_t region_end = dd[D + 1].cell_off;
+        const int64_t c_end = min(region_end, seg_end);  // diagonals 1 .. D of this region, cut at the segment end
+        int g0 = (int) (g - rg.diag_base);  // diagonal of the first cell of the current chunk
+        if (g0 == 0) {  // diagonal 0 has no incoming transitions (the reference starts at diagonal 1, :617-628)
+            g0 = 1;
+            c0 = dd[1].cell_off;
+        }
+        g = rg.diag_base + D + 1;  // where the walk continues: diagonal 0 of the next region
+        for (; c0 < c_end; c0 += 32) {
             // starts of the diagonals after g0: lane i holds the start of diagonal g0 + 1 + i (or "infinity")
             const int gi = g0 + 1 + lane;
             const int64_t start_i = gi <= D ? dd[gi].cell_off : c_end + 64;
@@ -734,6 +760,8 @@ k_expect(const __grid_constant__ DevModel model, Blob bl, int n_regions, const d
                 for (int s = 0; s < S; s++) bins[s * 16 + row][col] += e_to[s];
             }
             __syncwarp();
+        }
+        if (c0 >= region_end) c0 = region_end;  // region finished: go on with the next one (else the segment ended)
         }
     }
     // per-warp reduction: transitions and likelihood by shuffles, emission bins over their 16 columns
@@ -831,9 +859,57 @@ int grid_for(int64_t items, int blocks_per_sm, int warps_per_block = WARPS_PER_B
     return (int) (want < 1 ? 1 : (want < cap ? want : cap));
 }
 
+// warps per 5-state work item: 0 = chosen from the mean band width (run_dp), 1/2/4/8 = forced (tests, profiling)
+int g_w5_group = getenv("MAB_W5_GROUP") ? atoi(getenv("MAB_W5_GROUP")) : 0;
+
 template <typename K>
 int allow_smem(K kernel, int64_t bytes) {
     return check(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) bytes), "smem attribute");
+}
+
+// Launch shape of a wavefront kernel.  G warps share one work item and its shared-memory ring (wavefront5.cuh); the
+// choice maximises the number of busy warps: few items with wide diagonals want a large G (expansion 50, forward:
+// 333 regions x 4 chunks of 16 cells), many items want G = 1 unless the ring is so big that only a few one-warp
+// items fit an SM (expansion 200).  Measured on 10 kb reads (profiles/r1_ncu_summary.md, r1c).
+struct WaveLaunch {
+    int G, groups, warps, blocks_per_sm;
+    int64_t ring_bytes;
+};
+WaveLaunch wave_launch_for(int S, int G, const BlobHeader &h) {
+    static const int w5_warps = getenv("MAB_W5_WARPS") ? std::max(1, std::min(32, atoi(getenv("MAB_W5_WARPS")))) : 8;
+    const DeviceInfo &di = device_info();
+    WaveLaunch l;
+    l.G = G;
+    const int want_warps = S == 5 ? std::max(w5_warps / G, 1) * G : WARPS_PER_BLOCK;
+    const int64_t static_bytes = S == 5 ? (int64_t) sizeof(Wave5Shared) + 1024 : 8 * 1024;
+    const int64_t ring_per_group = (int64_t) 3 * (h.max_width + 2) * S * 8;
+    const int64_t budget = (int64_t) di.max_smem_optin - static_bytes;
+    l.groups = (int) std::min<int64_t>(want_warps / G, budget / std::max<int64_t>(1, ring_per_group));
+    if (G > 1) l.groups = std::min(l.groups, 15);  // one named barrier (1..15) per group
+    l.warps = l.groups * G;
+    l.ring_bytes = ring_per_group * l.groups;
+    l.blocks_per_sm = l.warps < 1 ? 0 : (int) std::max<int64_t>(
+        1, std::min<int64_t>(64 / l.warps, (220 * 1024) / (l.ring_bytes + static_bytes + 1024)));
+    return l;
+}
+WaveLaunch wave_launch(int S, int64_t items, const BlobHeader &h) {
+    if (S != 5) return wave_launch_for(S, 1, h);
+    if (g_w5_group == 1 || g_w5_group == 2 || g_w5_group == 4 || g_w5_group == 8) return wave_launch_for(S, g_w5_group, h);
+    const double mean_w = h.n_diagonals > 0 ? (double) h.n_cells / (double) h.n_diagonals : 1.0;
+    const int chunks = std::max(1, (int) std::ceil(mean_w / 16.0));
+    const double saturated = 24.0 * device_info().sm_count;  // warps beyond this add no throughput
+    WaveLaunch best = wave_launch_for(S, 1, h);
+    double best_score = -1.0;
+    for (int G = 1; G <= 8; G *= 2) {
+        const WaveLaunch l = wave_launch_for(S, G, h);
+        if (l.warps < 1) continue;
+        const double resident = (double) device_info().sm_count * l.blocks_per_sm * l.groups;
+        const double busy = std::min<double>((double) items, resident) * std::min(G, chunks);
+        const double rounds = std::ceil((double) chunks / G) * G / chunks;  // idle warps in the last round of chunks
+        const double score = std::min(busy, saturated) / (rounds * (G > 1 ? 1.1 : 1.0));
+        if (score > best_score * 1.0001) best = l, best_score = score;
+    }
+    return best;
 }
 
 // forward + backward + totals: shared by posterior mode (FULL = false) and expectation mode (FULL = true)
@@ -841,60 +917,60 @@ template <int S, bool FULL>
 int run_dp(const DevModel &dm, const mab_plan *plan, const Blob &bl, const Workspace &w, cudaStream_t st) {
     const BlobHeader &h = plan->hdr;
     const DeviceInfo &di = device_info();
-    // shared-memory ring per warp: 3 diagonals x (max_width + 2 guard) cells x S doubles; fewer warps per block for
-    // wide bands.  The 5-state kernels also hold ~27 KB of replicated tables per block, so they use bigger blocks.
-    static const int w5_warps = getenv("MAB_W5_WARPS") ? std::max(1, std::min(32, atoi(getenv("MAB_W5_WARPS")))) : 8;
-    const int want_warps = S == 5 ? w5_warps : WARPS_PER_BLOCK;
-    const int64_t static_bytes = S == 5 ? (int64_t) sizeof(Wave5Shared) + 1024 : 8 * 1024;
-    const int64_t ring_per_warp = (int64_t) 3 * (h.max_width + 2) * S * 8;
-    const int64_t budget = (int64_t) di.max_smem_optin - static_bytes;
-    const int nw = (int) std::min<int64_t>(want_warps, budget / std::max<int64_t>(1, ring_per_warp));
-    if (nw < 1) {
+    // shared-memory ring per work item: 3 diagonals x (max_width + 2 guard) cells x S doubles.  The 5-state kernels
+    // also hold ~27 KB of replicated tables per block and may give one item to G warps (wave_launch).
+    const WaveLaunch lf = wave_launch(S, h.n_regions, h), lb = wave_launch(S, h.n_tracebacks, h);
+    if (lf.warps < 1 || lb.warps < 1) {
         mab_set_error("band too wide for the shared-memory ring (max width %lld cells); lower diagonalExpansion or "
                       "splitMatrixBiggerThanThis", (long long) h.max_width);
         return MAB_E_ARG;
     }
-    const int64_t ring_bytes = ring_per_warp * nw;
     const int ring_w = (int) h.max_width;
-    const int blocks_per_sm = (int) std::max<int64_t>(
-        1, std::min<int64_t>(64 / nw, (220 * 1024) / (ring_bytes + static_bytes + 1024)));
     int rc;
     if ((rc = check(cudaMemsetAsync(w.counters, 0, 256, st), "memset counters"))) return rc;
     if (S == 5) {
         // where the logAdd coefficients are fetched from (wavefront5.cuh): smem (default, fastest measured) |
-        // mixed | const -- kept switchable for profiling
+        // mixed | const -- kept switchable for profiling (single-warp items only)
         static const int cm = [] {
             const char *e = getenv("MAB_COEF");
             if (e && !strcmp(e, "const")) return (int) COEF_CONST;
             if (e && !strcmp(e, "mixed")) return (int) COEF_MIXED;
             return (int) COEF_SMEM;
         }();
-        auto kf = cm == COEF_CONST ? k_forward5<FULL, COEF_CONST> : cm == COEF_SMEM ? k_forward5<FULL, COEF_SMEM>
-                                                                                     : k_forward5<FULL, COEF_MIXED>;
-        auto kb = cm == COEF_CONST ? k_backward5<FULL, COEF_CONST> : cm == COEF_SMEM ? k_backward5<FULL, COEF_SMEM>
-                                                                                     : k_backward5<FULL, COEF_MIXED>;
-        if ((rc = allow_smem(kf, ring_bytes)) || (rc = allow_smem(kb, ring_bytes))) return rc;
+        auto kf = k_forward5<FULL, COEF_SMEM, 1>;
+        auto kb = k_backward5<FULL, COEF_SMEM, 1>;
+        if (lf.G == 1 && cm == COEF_CONST) kf = k_forward5<FULL, COEF_CONST, 1>;
+        if (lf.G == 1 && cm == COEF_MIXED) kf = k_forward5<FULL, COEF_MIXED, 1>;
+        if (lb.G == 1 && cm == COEF_CONST) kb = k_backward5<FULL, COEF_CONST, 1>;
+        if (lb.G == 1 && cm == COEF_MIXED) kb = k_backward5<FULL, COEF_MIXED, 1>;
+        if (lf.G == 2) kf = k_forward5<FULL, COEF_SMEM, 2>;
+        if (lf.G == 4) kf = k_forward5<FULL, COEF_SMEM, 4>;
+        if (lf.G == 8) kf = k_forward5<FULL, COEF_SMEM, 8>;
+        if (lb.G == 2) kb = k_backward5<FULL, COEF_SMEM, 2>;
+        if (lb.G == 4) kb = k_backward5<FULL, COEF_SMEM, 4>;
+        if (lb.G == 8) kb = k_backward5<FULL, COEF_SMEM, 8>;
+        if ((rc = allow_smem(kf, lf.ring_bytes)) || (rc = allow_smem(kb, lb.ring_bytes))) return rc;
         {
             LaunchTimer lt(K_FORWARD, st);
-            kf<<<grid_for(h.n_regions, blocks_per_sm, nw), nw * 32, ring_bytes, st>>>(
+            kf<<<grid_for(h.n_regions, lf.blocks_per_sm, lf.groups), lf.warps * 32, lf.ring_bytes, st>>>(
                 dm, bl, (int) h.n_regions, w.fwd, w.fwd_tot, w.counters + 0, ring_w);
         }
         {
             LaunchTimer lt(K_BACKWARD, st);
-            kb<<<grid_for(h.n_tracebacks, blocks_per_sm, nw), nw * 32, ring_bytes, st>>>(
+            kb<<<grid_for(h.n_tracebacks, lb.blocks_per_sm, lb.groups), lb.warps * 32, lb.ring_bytes, st>>>(
                 dm, bl, (int) h.n_tracebacks, w.bwd, w.bwd_tot, w.edge, w.counters + 1, ring_w);
         }
     } else {
-        if ((rc = allow_smem(k_forward<S, FULL>, ring_bytes)) || (rc = allow_smem(k_backward<S, FULL>, ring_bytes)))
+        if ((rc = allow_smem(k_forward<S, FULL>, lf.ring_bytes)) || (rc = allow_smem(k_backward<S, FULL>, lb.ring_bytes)))
             return rc;
         {
             LaunchTimer lt(K_FORWARD, st);
-            k_forward<S, FULL><<<grid_for(h.n_regions, blocks_per_sm, nw), nw * 32, ring_bytes, st>>>(
+            k_forward<S, FULL><<<grid_for(h.n_regions, lf.blocks_per_sm, lf.warps), lf.warps * 32, lf.ring_bytes, st>>>(
                 dm, bl, (int) h.n_regions, w.fwd, w.fwd_tot, w.counters + 0, ring_w);
         }
         {
             LaunchTimer lt(K_BACKWARD, st);
-            k_backward<S, FULL><<<grid_for(h.n_tracebacks, blocks_per_sm, nw), nw * 32, ring_bytes, st>>>(
+            k_backward<S, FULL><<<grid_for(h.n_tracebacks, lb.blocks_per_sm, lb.warps), lb.warps * 32, lb.ring_bytes, st>>>(
                 dm, bl, (int) h.n_tracebacks, w.bwd, w.bwd_tot, w.edge, w.counters + 1, ring_w);
         }
     }
@@ -947,8 +1023,9 @@ int run_expectations(const DevModel &dm, const mab_plan *plan, const void *d_blo
     if (rc) return rc;
     {
         LaunchTimer lt(K_EXPECT, st);
-        k_expect<S><<<grid_for(h.n_regions, 4, EXP_WARPS), EXP_WARPS * 32, 0, st>>>(dm, bl, (int) h.n_regions, w.fwd, w.bwd,
-                                                                        w.totals, d_out, w.counters + 4);
+        const int64_t n_segments = (h.n_cells + EXP_SEGMENT - 1) / EXP_SEGMENT;
+        k_expect<S><<<grid_for(n_segments, 4, EXP_WARPS), EXP_WARPS * 32, 0, st>>>(dm, bl, h.n_cells, h.n_diagonals, w.fwd,
+                                                                                 w.bwd, w.totals, d_out, w.counters + 4);
     }
     return check(cudaGetLastError(), "expectation launch");
 }
@@ -979,6 +1056,15 @@ extern "C" int mab_kernel_timing(int enable) {
     return MAB_OK;
 }
 
+extern "C" int mab_debug_set_warp_group(int warps) {
+    if (warps != 0 && warps != 1 && warps != 2 && warps != 4 && warps != 8) {
+        mab_set_error("warp group must be 0 (auto), 1, 2, 4 or 8");
+        return MAB_E_ARG;
+    }
+    g_w5_group = warps;
+    return MAB_OK;
+}
+
 extern "C" int mab_kernel_count(void) { return K_COUNT; }
 
 extern "C" const char *mab_kernel_name(int kernel) {
@@ -1006,6 +1092,8 @@ extern "C" int mab_kernel_times(double *ms, int64_t *launches, int reset) {
     }
     return MAB_OK;
 }
+
+void mab_count_launches(int n) { g_launches += n; }  // launches issued by realign.cu
 
 extern "C" int64_t mab_launch_count(int reset) {
     const int64_t v = g_launches;

@@ -200,11 +200,31 @@ __device__ __forceinline__ void write_high_guard(double *slot, int w, int lane) 
     if (lane < 5) slot[(w + 1) * 5 + lane] = neg_inf();
 }
 
+// ---- warp groups -------------------------------------------------------------------------------------------------
+// G warps share one work item (region / traceback): warp gw of the group takes the 16-cell chunks gw, gw + G, ... of
+// every diagonal, the ring lives once per group, and one named barrier per diagonal replaces the __syncwarp().  G = 1
+// is the tRNA shape (12-13 cells per diagonal); wide bands (diagonalExpansion 50-500: 51-501 cells) use G = 2/4/8 so
+// that a region with few, long, wide diagonals still fills the SM and a 60 KB ring is paid once per 8 warps.
+template <int G>
+__device__ __forceinline__ void group_sync(int group) {
+    if (G == 1) __syncwarp();
+    else asm volatile("bar.sync %0, %1;" ::"r"(group + 1), "n"(G * 32) : "memory");
+}
+template <int G>
+__device__ __forceinline__ int next_item_group(int *counter, int lane, int gw, int group, volatile int *sh_item) {
+    if (G == 1) return next_item(counter, lane);
+    if (gw == 0 && lane == 0) sh_item[group] = atomicAdd(counter, 1);
+    group_sync<G>(group);  // also separates the previous item's last reads of the ring from the next item's init
+    const int item = sh_item[group];
+    group_sync<G>(group);  // nobody re-writes sh_item before every warp of the group has read it
+    return item;
+}
+
 // ------------------------------------------------------------------------------------------------ forward
 // FULL = true : F holds all 5 states of every cell ([cell][5]); required by expectation mode.
 // FULL = false: posterior mode -- F holds the match state of every cell, FT all states of the cells on the
 //               diagonals where a total probability is evaluated (indexed through TotalDesc::full_off).
-template <bool FULL, int CM>
+template <bool FULL, int CM, int G>
 __global__ void __launch_bounds__(1024)
 k_forward5(const __grid_constant__ DevModel model, Blob bl, int n_regions, double *__restrict__ F,
            double *__restrict__ FT, int *counter, int ring_w) {
@@ -218,7 +238,9 @@ k_forward5(const __grid_constant__ DevModel model, Blob bl, int n_regions, doubl
     const bool chain = role == 0;
     const int jl = lane & 15;    // cell within a chunk of 16
     const int slot_doubles = (ring_w + 2) * 5;
-    double *ring = reinterpret_cast<double *>(dyn_smem_raw) + (size_t) warp * 3 * slot_doubles;
+    const int group = warp / G, gw = warp % G;  // G warps share a work item and its ring
+    __shared__ int sh_item[16];
+    double *ring = reinterpret_cast<double *>(dyn_smem_raw) + (size_t) group * 3 * slot_doubles;
     if (lane < 15) ring[(lane / 5) * slot_doubles + lane % 5] = neg_inf();  // low guards of the three slots
     __syncthreads();
     const double2 *etp_lane = &sh.etp[role][0][0][lane & (W5_COPIES - 1)];
@@ -228,7 +250,7 @@ k_forward5(const __grid_constant__ DevModel model, Blob bl, int n_regions, doubl
     const int s_out4 = role ? LY : M;  // where r4 goes
 
     for (;;) {
-        const int item = next_item(counter, lane);
+        const int item = next_item_group<G>(counter, lane, gw, group, sh_item);
         if (item >= n_regions) break;
         const RegionDesc rg = bl.regions[bl.order_fwd[item]];
         const DiagDesc *dd = bl.diags + rg.diag_base;
@@ -239,14 +261,14 @@ k_forward5(const __grid_constant__ DevModel model, Blob bl, int n_regions, doubl
         // diagonal 0 (pairwiseAligner.c:658-659) goes to slot1; slot2 is the empty "d-2" of diagonal 1
         {
             const double *init = sh.boundary[(rg.flags & 1) ? 1 : 0];
-            for (int i = lane; i < w1 * 5; i += 32) {
+            for (int i = gw * 32 + lane; i < w1 * 5; i += 32 * G) {
                 const double v = init[i % 5];
                 slot1[5 + i] = v;
                 if (FULL) F[cur.cell_off * 5 + i] = v;
                 else if (i % 5 == 0) F[cur.cell_off + i / 5] = v;
             }
-            write_high_guard(slot1, w1, lane);
-            write_high_guard(slot2, 0, lane);
+            if (gw == 0) write_high_guard(slot1, w1, lane);
+            if (gw == 0) write_high_guard(slot2, 0, lane);
         }
         // per-lane sequence pointers: cell (x, y) of diagonal d consumes X[x-1] and Y[y-1].  For x = 0 (y = 0) the
         // byte before the region is read and ignored: every term that uses it comes from an out-of-band neighbour.
@@ -254,7 +276,7 @@ k_forward5(const __grid_constant__ DevModel model, Blob bl, int n_regions, doubl
         // warp-uniform base pointers (shifted by the -1) + 32-bit per-lane offsets: one address add per load
         const uint8_t *sxb = bl.sym_x + rg.sym_x_off - 1, *syb = bl.sym_y + rg.sym_y_off - 1;
         unsigned xo = (unsigned) (x0 + jl), yo = (unsigned) (y0 - jl);
-        __syncwarp();
+        group_sync<G>(group);
         for (int d = 1; d <= D; d++) {
             cur = nxt;
             nxt = dd[d + 1];
@@ -271,7 +293,7 @@ k_forward5(const __grid_constant__ DevModel model, Blob bl, int n_regions, doubl
             const double *nb_slot = chain ? slot2 : slot1;
             const int nb_off = chain ? oMi : oLo, nb_w = chain ? w2 : w1, nb_step = chain ? 0 : 1;
             double *f_match = F + cur.cell_off;  // posterior mode: the match plane
-            for (int j0 = 0; j0 < w; j0 += 16) {
+            for (int j0 = gw * 16; j0 < w; j0 += 16 * G) {
                 const int j = j0 + jl;
                 if (j < w) {
                     const int cX = __ldg(sxb + (xo + (unsigned) j0)), cY = __ldg(syb + (yo - (unsigned) j0));
@@ -294,16 +316,16 @@ k_forward5(const __grid_constant__ DevModel model, Blob bl, int n_regions, doubl
                     if (!FULL && chain) f_match[j] = q.r4;  // 16 consecutive doubles per half-warp
                 }
             }
-            write_high_guard(slot, w, lane);
-            __syncwarp();
+            if (gw == 0) write_high_guard(slot, w, lane);
+            group_sync<G>(group);
             // all five states leave through a coalesced copy of the finished ring slot: every diagonal in
             // expectation mode, only the diagonals that carry a total (1 in 10) in posterior mode
             if (FULL) {
                 double *g = F + cur.cell_off * 5;
-                for (int i = lane; i < w * 5; i += 32) g[i] = slot[5 + i];
+                for (int i = gw * 32 + lane; i < w * 5; i += 32 * G) g[i] = slot[5 + i];
             } else if (cur.tot_flags & MAB_DIAG_IS_TOTAL) {
                 double *g = FT + (int64_t) bl.totals[cur.tot_flags & MAB_DIAG_TOT_MASK].full_off * 5;
-                for (int i = lane; i < w * 5; i += 32) g[i] = slot[5 + i];
+                for (int i = gw * 32 + lane; i < w * 5; i += 32 * G) g[i] = slot[5 + i];
             }
             L2 = L1;
             L1 = L;
@@ -320,7 +342,7 @@ k_forward5(const __grid_constant__ DevModel model, Blob bl, int n_regions, doubl
 // ------------------------------------------------------------------------------------------------ backward
 // One warp per traceback.  FULL as above (B / BT); `edge` receives the match state of diagonal from+1 of
 // intermediate tracebacks (see TracebackDesc::edge_off).
-template <bool FULL, int CM>
+template <bool FULL, int CM, int G>
 __global__ void __launch_bounds__(1024)
 k_backward5(const __grid_constant__ DevModel model, Blob bl, int n_tbs, double *__restrict__ B,
             double *__restrict__ BT, double *__restrict__ edge, int *counter, int ring_w) {
@@ -332,7 +354,9 @@ k_backward5(const __grid_constant__ DevModel model, Blob bl, int n_tbs, double *
     const bool chain = role == 0;
     const int jl = lane & 15;
     const int slot_doubles = (ring_w + 2) * 5;
-    double *ring = reinterpret_cast<double *>(dyn_smem_raw) + (size_t) warp * 3 * slot_doubles;
+    const int group = warp / G, gw = warp % G;  // G warps share a work item and its ring
+    __shared__ int sh_item[16];
+    double *ring = reinterpret_cast<double *>(dyn_smem_raw) + (size_t) group * 3 * slot_doubles;
     if (lane < 15) ring[(lane / 5) * slot_doubles + lane % 5] = neg_inf();
     __syncthreads();
     const double2 *etp_lane = &sh.etp[role][0][0][lane & (W5_COPIES - 1)];
@@ -343,7 +367,7 @@ k_backward5(const __grid_constant__ DevModel model, Blob bl, int n_tbs, double *
     const int s2 = chain ? SY : SX, s4 = chain ? LY : SY, s6 = chain ? SX : LX, s8 = chain ? LX : LY;
 
     for (;;) {
-        const int item = next_item(counter, lane);
+        const int item = next_item_group<G>(counter, lane, gw, group, sh_item);
         if (item >= n_tbs) break;
         const TracebackDesc tb = bl.tbs[bl.order_bwd[item]];
         const RegionDesc rg = bl.regions[tb.region];
@@ -358,7 +382,7 @@ k_backward5(const __grid_constant__ DevModel model, Blob bl, int n_tbs, double *
             double *bt = nullptr;
             if (!FULL && keep && (cur.tot_flags & MAB_DIAG_IS_TOTAL))
                 bt = BT + (int64_t) bl.totals[cur.tot_flags & MAB_DIAG_TOT_MASK].full_off * 5;
-            for (int i = lane; i < w1 * 5; i += 32) {
+            for (int i = gw * 32 + lane; i < w1 * 5; i += 32 * G) {
                 const double v = init[i % 5];
                 slot1[5 + i] = v;
                 if (keep) {
@@ -369,15 +393,15 @@ k_backward5(const __grid_constant__ DevModel model, Blob bl, int n_tbs, double *
                     }
                 }
             }
-            write_high_guard(slot1, w1, lane);
-            write_high_guard(slot2, 0, lane);  // the empty "d+2" of diagonal hi-1
+            if (gw == 0) write_high_guard(slot1, w1, lane);
+            if (gw == 0) write_high_guard(slot2, 0, lane);  // the empty "d+2" of diagonal hi-1
         }
         // the neighbours of target cell (x, y) consume X[x] and/or Y[y] (0-based); at x = lX (y = lY) the byte after
         // the region is read and ignored: the neighbours that would use it are out of band (-inf)
         int x0 = (tb.hi + L1) >> 1, y0 = (tb.hi - L1) >> 1;
         const uint8_t *sxb = bl.sym_x + rg.sym_x_off, *syb = bl.sym_y + rg.sym_y_off;  // warp-uniform bases
         unsigned xo = (unsigned) (x0 + jl), yo = (unsigned) (y0 - jl);                 // 32-bit per-lane offsets
-        __syncwarp();
+        group_sync<G>(group);
         for (int d = tb.hi - 1; d > tb.lo; d--) {
             up1 = cur;
             cur = dd[d];
@@ -394,7 +418,7 @@ k_backward5(const __grid_constant__ DevModel model, Blob bl, int n_tbs, double *
             // where the match lanes put their result: the match plane of B (posterior mode, kept diagonals), the
             // edge buffer (first discarded diagonal of an intermediate traceback, both modes), or nowhere
             double *b_match = d == tb.from + 1 ? edge + tb.edge_off : ((!FULL && keep) ? B + cur.cell_off : nullptr);
-            for (int j0 = 0; j0 < w; j0 += 16) {
+            for (int j0 = gw * 16; j0 < w; j0 += 16 * G) {
                 const int j = j0 + jl;
                 if (j < w) {
                     const int cX = __ldg(sxb + (xo + (unsigned) j0)), cY = __ldg(syb + (yo - (unsigned) j0));
@@ -423,15 +447,15 @@ k_backward5(const __grid_constant__ DevModel model, Blob bl, int n_tbs, double *
                     if (chain && b_match != nullptr) b_match[j] = q.r4;
                 }
             }
-            write_high_guard(slot, w, lane);
-            __syncwarp();
+            if (gw == 0) write_high_guard(slot, w, lane);
+            group_sync<G>(group);
             if (keep) {  // all five states: coalesced copy of the finished ring slot (see k_forward5)
                 if (FULL) {
                     double *g = B + cur.cell_off * 5;
-                    for (int i = lane; i < w * 5; i += 32) g[i] = slot[5 + i];
+                    for (int i = gw * 32 + lane; i < w * 5; i += 32 * G) g[i] = slot[5 + i];
                 } else if (cur.tot_flags & MAB_DIAG_IS_TOTAL) {
                     double *g = BT + (int64_t) bl.totals[cur.tot_flags & MAB_DIAG_TOT_MASK].full_off * 5;
-                    for (int i = lane; i < w * 5; i += 32) g[i] = slot[5 + i];
+                    for (int i = gw * 32 + lane; i < w * 5; i += 32 * G) g[i] = slot[5 + i];
                 }
             }
             L2 = L1;

@@ -375,11 +375,11 @@ class PairHmmEngine:
     posterior mode, 80 B in expectation mode).  plan_on = "device" (default): raw inputs are uploaded and the plan is
     built on the GPU; "host": the C++ host planner builds the blob and it is copied over PCIe."""
 
-    def __init__(self, device=None, max_cells=400_000_000, plan_threads=0, plan_on="device"):
+    def __init__(self, device=None, max_cells=None, plan_threads=0, plan_on="device"):
         torch = require_cuda()
         self.torch = torch
         self.device = torch.device(device if device is not None else "cuda:%d" % torch.cuda.current_device())
-        self.max_cells = int(max_cells)
+        self.max_cells = int(max_cells) if max_cells else None  # None: chosen per batch (_auto_max_cells)
         self.plan_threads = plan_threads
         if plan_on not in ("device", "host"):
             raise ValueError("plan_on must be 'device' or 'host'")
@@ -391,25 +391,47 @@ class PairHmmEngine:
         self._plan_stream = torch.cuda.Stream(device=self.device)
 
     # ---------------------------------------------------------------- chunking
-    def _chunks(self, batch, params):
+    BASE_CELLS = 400_000_000  # chunk size that pipelines well for short reads (tRNA: ~140 k alignments per chunk)
+
+    def _auto_max_cells(self, est, params, expectations):
+        """Chunk size when the caller gave none.  The forward sweep of one region is sequential over its diagonals, so
+        a chunk must hold enough regions to fill the GPU (~6000 resident warps / the warps one region gets, see
+        wave_launch in csrc/kernels.cu): a few hundred 10 kb reads per chunk would leave the forward kernel
+        latency-bound.  Bounded by free HBM (posterior mode ~28 B of workspace per cell + outputs, expectation mode
+        160 B)."""
+        free, _total = self.torch.cuda.mem_get_info(self.device)
+        mem_cap = min(int(0.55 * free / (170 if expectations else 40)), 2_000_000_000)  # 32-bit side offsets
+        group = min(8, max(1, -(-(params.diagonal_expansion + 2) // 16)))
+        want_alignments = 6144 // group
+        target = int(float(est.mean()) * want_alignments) if len(est) else 0
+        return max(min(max(self.BASE_CELLS, target), mem_cap), 1), want_alignments
+
+    def _chunks(self, batch, params, expectations=False):
         """Contiguous alignment ranges of at most ~max_cells estimated DP cells (cells ~ diagonals x band width; the
         exact count comes from the plan)."""
         if batch.n == 0:
             return [(0, 0)]
         est = ((batch.off_x[1:] - batch.off_x[:-1]) + (batch.off_y[1:] - batch.off_y[:-1]) + 1) * (
             params.diagonal_expansion + 4)
+        if self.max_cells:
+            max_cells, want_alignments = self.max_cells, 0
+        else:
+            max_cells, want_alignments = self._auto_max_cells(est, params, expectations)
         cum = np.cumsum(est.astype(np.int64))
         bounds, start, base = [], 0, 0
         # the first chunk is a quarter of the others: nothing overlaps its packing, upload and planning, so the
-        # pipeline (helper thread plans chunk k+1 while chunk k computes) should fill quickly
-        limit = max(self.max_cells // 4, 1)
+        # pipeline (helper thread plans chunk k+1 while chunk k computes) should fill quickly -- unless a quarter
+        # chunk would hold too few alignments to fill the GPU
+        limit = max(max_cells // 4, 1)
+        if want_alignments and limit < float(est.mean()) * want_alignments:
+            limit = max_cells
         while start < batch.n:
             end = int(np.searchsorted(cum, base + limit, side="right"))
             end = max(end, start + 1)
             bounds.append((start, min(end, batch.n)))
             start = bounds[-1][1]
             base = int(cum[start - 1])
-            limit = self.max_cells
+            limit = max_cells
         return bounds
 
     def _stream_ptr(self):
@@ -417,7 +439,7 @@ class PairHmmEngine:
 
     def _device_plans(self, batch, params, expectations):
         """Yields one DevicePlan per chunk.  Host planning of chunk k+1 overlaps the GPU work on chunk k."""
-        chunks = self._chunks(batch, params)
+        chunks = self._chunks(batch, params, expectations)
         torch = self.torch
         if self.plan_on == "device":
             # chunk k+1 is packed into pinned memory, uploaded and planned by a helper thread on its own stream while

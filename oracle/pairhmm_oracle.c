@@ -785,3 +785,161 @@ int64_t ph_count_cells(int64_t lX, int64_t lY, const int64_t *anchors, int64_t n
     free(sY);
     return cells;
 }
+
+/* ------------------------------------------------------------------------------------------------------------------
+ * Realign tail: what cPecanRealign does with the posterior pairs of one alignment
+ * (cPecanRealign.c:590-631).  Restated over flat arrays; libc srand()/rand() supply the jitter exactly as the
+ * reference's st_random() does (sonLib/C/impl/sonLibRandom.c:39-43).
+ *
+ *   1. AMAP reweight: getIndelProbabilities (pairwiseAligner.c:1216-1231), reweightAlignedPairs (:1233-1249),
+ *      reweightAlignedPairs2 (:1251-1261).
+ *   2. Maximum-expected-accuracy chain: filterPairwiseAlignmentToMakePairsOrdered (multipleAligner.c:941-967) ->
+ *      convertAlignedPairsToMultipleAlignedPairs (:622-629, pops from the tail: the list is reversed) ->
+ *      makeAlignmentWeightAdjacencyLists (:154-169, two st_random() draws per pair: the first for the weight filed
+ *      under the Y column, the second for the weight filed under the X column, which is the one the DP reads) ->
+ *      pairwiseAlignColumns (:355-489).
+ *   3. Sort by (x, y) (cPecanRealign.c:611) and build the cigar: convertAlignedPairsToPairwiseAlignment (:50-92).
+ * ------------------------------------------------------------------------------------------------------------------ */
+
+typedef struct {
+    int64_t y, pred;   /* pred: index into the candidate array, -1 = the (-1,-1) sentinel */
+    int64_t x, src;    /* src: index of the input pair */
+    double score;
+} ph_cand;
+
+static int cand_cmp_y(const void *a, const void *b) {
+    int64_t i = ((const ph_cand *) a)->y, j = ((const ph_cand *) b)->y;
+    return i > j ? 1 : (i < j ? -1 : 0);
+}
+
+/* pairs: n rows (p_int, x, y) in the order getAlignedPairsUsingAnchors returns them.  seed < 0: leave the libc
+ * stream alone; else srand(seed) (a fresh cPecanRealign process has seed 1).  out_xy: chain pairs sorted, cap n rows.
+ * out_w (may be NULL): reweighted integer weight of every INPUT pair.  Returns the chain length. */
+int64_t ph_realign_chain(const int64_t *pairs, int64_t n, int64_t lX, int64_t lY, double gapGamma, double matchGamma,
+        int seed, int64_t *out_xy, int64_t *out_w) {
+    if (seed >= 0) srand((unsigned) seed);
+    int64_t *w = malloc(sizeof(int64_t) * (n > 0 ? n : 1));
+    for (int64_t i = 0; i < n; i++) w[i] = pairs[3 * i];
+    if (gapGamma > 0.0) { /* reweightAlignedPairs2 :1252 */
+        int64_t *ix = malloc(sizeof(int64_t) * (lX > 0 ? lX : 1)), *iy = malloc(sizeof(int64_t) * (lY > 0 ? lY : 1));
+        for (int64_t i = 0; i < lX; i++) ix[i] = PH_PROB_1;
+        for (int64_t i = 0; i < lY; i++) iy[i] = PH_PROB_1;
+        for (int64_t i = 0; i < n; i++) {
+            ix[pairs[3 * i + 1]] -= pairs[3 * i];
+            iy[pairs[3 * i + 2]] -= pairs[3 * i];
+        }
+        for (int64_t i = 0; i < lX; i++) if (ix[i] < 0) ix[i] = 0;
+        for (int64_t i = 0; i < lY; i++) if (iy[i] < 0) iy[i] = 0;
+        for (int64_t i = 0; i < n; i++) { /* :1244: int64 - double * int64, truncated back to int64 */
+            int64_t updated = pairs[3 * i] - gapGamma * (ix[pairs[3 * i + 1]] + iy[pairs[3 * i + 2]]);
+            w[i] = updated;
+        }
+        free(ix);
+        free(iy);
+    }
+    if (out_w != NULL) memcpy(out_w, w, sizeof(int64_t) * n);
+    /* jitter: element k of the reversed list is input pair n-1-k; draws 2k (unused by the DP) and 2k+1 */
+    double *aw = malloc(sizeof(double) * (n > 0 ? n : 1));
+    for (int64_t k = 0; k < n; k++) {
+        const double r0 = rand() / (RAND_MAX + 1.0);
+        (void) r0;
+        double r1 = rand() / (RAND_MAX + 1.0);
+        r1 = r1 >= 1.0 ? 0.9999 : (r1 < 0.0 ? 0.0 : r1);
+        aw[n - 1 - k] = ((double) w[n - 1 - k]) / PH_PROB_1 + r1 * 0.00001;
+    }
+    /* pairs by X column */
+    int64_t *colStart = calloc(lX + 2, sizeof(int64_t)), *byCol = malloc(sizeof(int64_t) * (n > 0 ? n : 1));
+    for (int64_t i = 0; i < n; i++) colStart[pairs[3 * i + 1] + 1]++;
+    for (int64_t i = 0; i < lX; i++) colStart[i + 1] += colStart[i];
+    int64_t *fill = malloc(sizeof(int64_t) * (lX + 1));
+    memcpy(fill, colStart, sizeof(int64_t) * (lX + 1));
+    for (int64_t i = 0; i < n; i++) byCol[fill[pairs[3 * i + 1]]++] = i;
+    free(fill);
+    /* the DP: `cands` holds every ColumnPair ever constructed, `front` the sorted set bestScoringAlignments */
+    ph_cand *cands = malloc(sizeof(ph_cand) * (n + 2));
+    int64_t nCands = 0;
+    int64_t *front = malloc(sizeof(int64_t) * (n + 2)); /* candidate indices; -1 = min sentinel, -2 = max sentinel */
+    int64_t nFront = 2;
+    front[0] = -1;
+    front[1] = -2;
+#define F_Y(i) ((i) == -1 ? -1 : ((i) == -2 ? lY : cands[i].y))
+#define F_SCORE(i) ((i) == -1 ? 0.0 : ((i) == -2 ? (double) INT64_MAX : cands[i].score))
+    ph_cand *l = malloc(sizeof(ph_cand) * (lY + 1));
+    for (int64_t x = 0; x < lX; x++) {
+        int64_t nl = 0;
+        for (int64_t k = colStart[x]; k < colStart[x + 1]; k++) {
+            const int64_t i = byCol[k];
+            if (aw[i] >= matchGamma && aw[i] > 0.0) {
+                const int64_t y = pairs[3 * i + 2];
+                int64_t f = 0; /* searchLessThan: last frontier element with yIndex < y */
+                while (f + 1 < nFront && F_Y(front[f + 1]) < y) f++;
+                l[nl].x = x;
+                l[nl].y = y;
+                l[nl].src = i;
+                l[nl].pred = front[f];
+                l[nl].score = F_SCORE(front[f]) + aw[i] * 1.0;
+                nl++;
+            }
+        }
+        qsort(l, nl, sizeof(ph_cand), cand_cmp_y);
+        while (nl > 0) {
+            const ph_cand cP = l[--nl];
+            int64_t g = 0; /* searchGreaterThanOrEqual */
+            while (F_Y(front[g]) < cP.y) g++;
+            if (cP.score >= F_SCORE(front[g]) || F_Y(front[g]) > cP.y) {
+                int64_t e = g;
+                while (cP.score >= F_SCORE(front[e])) e++;
+                cands[nCands] = cP;
+                /* replace front[g..e) by the new candidate */
+                memmove(front + g + 1, front + e, sizeof(int64_t) * (nFront - e));
+                front[g] = nCands++;
+                nFront += 1 - (e - g);
+            }
+        }
+    }
+    /* traceback from the right-most real point */
+    int64_t m = 0;
+    for (int64_t c = front[nFront - 2]; c >= 0; c = cands[c].pred) m++;
+    int64_t k = m;
+    for (int64_t c = front[nFront - 2]; c >= 0; c = cands[c].pred) {
+        k--;
+        out_xy[2 * k] = cands[c].x;
+        out_xy[2 * k + 1] = cands[c].y;
+    }
+#undef F_Y
+#undef F_SCORE
+    free(l);
+    free(front);
+    free(cands);
+    free(byCol);
+    free(colStart);
+    free(aw);
+    free(w);
+    return m;
+}
+
+/* convertAlignedPairsToPairwiseAlignment (cPecanRealign.c:50-92).  xy: m sorted chain pairs.  out_ops rows
+ * (op, length) with sonLib op codes 0 match, 1 indel-X ('D'), 2 indel-Y ('I'); cap rows.  Returns the op count. */
+int64_t ph_cigar_from_pairs(const int64_t *xy, int64_t m, int64_t lX, int64_t lY, int64_t *out_ops, int64_t cap) {
+    int64_t pX = -1, pY = -1, mL = 0, nOps = 0;
+#define PUSH(op, len) do { if (nOps < cap) { out_ops[2 * nOps] = (op); out_ops[2 * nOps + 1] = (len); } nOps++; } while (0)
+    for (int64_t i = 0; i <= m; i++) {
+        const int64_t x = i < m ? xy[2 * i] : lX, y = i < m ? xy[2 * i + 1] : lY;
+        if (x - pX > 0 && y - pY > 0) {
+            if (x - pX > 1) {
+                if (mL > 0) { PUSH(0, mL); mL = 0; }
+                PUSH(1, x - pX - 1);
+            }
+            if (y - pY > 1) {
+                if (mL > 0) { PUSH(0, mL); mL = 0; }
+                PUSH(2, y - pY - 1);
+            }
+            mL++;
+            pX = x;
+            pY = y;
+        }
+    }
+    if (mL > 1) PUSH(0, mL - 1);
+#undef PUSH
+    return nOps;
+}

@@ -65,6 +65,14 @@ int64_t ph_count_cells(int64_t lX, int64_t lY, const int64_t *anchors, int64_t n
 int64_t ph_anchors_from_cigar(const int32_t *ops, const int64_t *lens, int64_t nOps, const char *sX, const char *sY,
         int64_t *out, int64_t cap);
 
+/* Realign tail of one alignment (cPecanRealign.c:590-611): AMAP reweight + maximum-expected-accuracy chain.  pairs:
+ * n rows (p_int, x, y) in list order; seed >= 0 -> srand(seed) first (the reference process starts at 1); out_xy:
+ * sorted chain pairs (cap n rows); out_w (or NULL): reweighted weight of every input pair.  Returns chain length. */
+int64_t ph_realign_chain(const int64_t *pairs, int64_t n, int64_t lX, int64_t lY, double gapGamma, double matchGamma,
+        int seed, int64_t *out_xy, int64_t *out_w);
+/* convertAlignedPairsToPairwiseAlignment (cPecanRealign.c:50-92): rows (op, length); returns the op count */
+int64_t ph_cigar_from_pairs(const int64_t *xy, int64_t m, int64_t lX, int64_t lY, int64_t *out_ops, int64_t cap);
+
 #ifdef __cplusplus
 }
 #endif

@@ -64,6 +64,11 @@ def lib():
         L.ph_anchors_from_cigar.argtypes = [C.POINTER(C.c_int32), i64p, C.c_int64, C.c_char_p, C.c_char_p, i64p,
                                             C.c_int64]
         L.ph_anchors_from_cigar.restype = C.c_int64
+        L.ph_realign_chain.argtypes = [i64p, C.c_int64, C.c_int64, C.c_int64, C.c_double, C.c_double, C.c_int, i64p,
+                                       i64p]
+        L.ph_realign_chain.restype = C.c_int64
+        L.ph_cigar_from_pairs.argtypes = [i64p, C.c_int64, C.c_int64, C.c_int64, i64p, C.c_int64]
+        L.ph_cigar_from_pairs.restype = C.c_int64
         _lib = L
     return _lib
 
@@ -180,3 +185,30 @@ def anchors_from_cigar(ops, lens, sX, sY):
                                     lens.ctypes.data_as(C.POINTER(C.c_int64)), len(ops), _b(sX), _b(sY),
                                     out.ctypes.data_as(C.POINTER(C.c_int64)), cap)
     return out[:n]
+
+
+def realign_chain(pairs, lX, lY, gap_gamma=0.5, match_gamma=0.0, seed=1):
+    """AMAP reweight + MEA chain of one alignment.  pairs: rows (p_int, x, y) in list order.  gap_gamma/match_gamma
+    are floats in the reference (pairwiseAligner.h:38, cPecanRealign.c:390).  Returns (chain xy rows, weights)."""
+    p, pp = _i64(np.asarray(pairs, dtype=np.int64).reshape(-1, 3))
+    out = np.zeros((len(p) + 1, 2), dtype=np.int64)
+    w = np.zeros(len(p) + 1, dtype=np.int64)
+    m = lib().ph_realign_chain(pp, len(p), lX, lY, float(np.float32(gap_gamma)), float(np.float32(match_gamma)), seed,
+                               out.ctypes.data_as(C.POINTER(C.c_int64)), w.ctypes.data_as(C.POINTER(C.c_int64)))
+    return out[:m], w[:len(p)]
+
+
+def cigar_from_pairs(xy, lX, lY):
+    """Rows (op, length), op 0 M / 1 D (reference only) / 2 I (read only)."""
+    a, ap = _i64(np.asarray(xy, dtype=np.int64).reshape(-1, 2))
+    cap = 3 * len(a) + 4
+    out = np.zeros((cap, 2), dtype=np.int64)
+    n = lib().ph_cigar_from_pairs(ap, len(a), lX, lY, out.ctypes.data_as(C.POINTER(C.c_int64)), cap)
+    return out[:n]
+
+
+def realign(m, sX, sY, anchors, params, gap_gamma=0.5, match_gamma=0.0, seed=1):
+    """Posterior pairs -> chain -> cigar ops of one alignment (cPecanRealign.c:584-631)."""
+    pairs = aligned_pairs(m, sX, sY, anchors, params)
+    xy, _ = realign_chain(pairs, len(sX), len(sY), gap_gamma, match_gamma, seed)
+    return cigar_from_pairs(xy, len(sX), len(sY)), xy

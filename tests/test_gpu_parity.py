@@ -197,6 +197,41 @@ def test_wide_band_and_long_read(engine, golden):
     assert_exp_match(np.concatenate([T, E, [lik]]), np.concatenate([oT, oE, [olik]]), "wide")
 
 
+def test_warp_group_size_does_not_change_results(engine, golden):
+    """The 5-state wavefront kernels may give one work item to 1, 2, 4 or 8 warps (wide bands); every group size
+    must produce bit-identical pairs and expectations, and the wide-band ones must match the oracle."""
+    L = mab.capi.load()
+    spec = golden.model_arrays("fixture5asym")
+    model, om = gpu_model(spec), oracle_model(po, spec)
+    cases = [
+        (mab.synth.make_trna_batch(300, seed=11), mab.AlignmentParameters(), None),
+        (mab.synth.make_long_batch(3, read_len=2500, genome_len=40_000, seed=12),
+         mab.AlignmentParameters(diagonal_expansion=50, split_matrix_bigger_than=300),
+         po.make_params(expansion=50, split=300 ** 2)),
+    ]
+    try:
+        for b, P, oP in cases:
+            base = None
+            for g in (1, 2, 4, 8, 0):
+                mab.capi.check(L.mab_debug_set_warp_group(g))
+                res = engine.get_aligned_pairs_using_anchors(model, b, P)
+                T, E, lik = engine.get_expectations_using_anchors(model, b, P)
+                got = (res.offsets.copy(), res.x.copy(), res.y.copy(), res.p.copy(), np.concatenate([T, E, [lik]]))
+                if base is None:
+                    base = got
+                    if oP is not None:
+                        for i in range(b.n):
+                            anc = po.anchors_from_cigar(*b.cigar(i), b.x(i), b.y(i))
+                            assert_pairs_match(res.pairs(i), po.aligned_pairs(om, b.x(i), b.y(i), anc, oP), 0.01, i)
+                else:
+                    for k in range(4):
+                        assert np.array_equal(base[k], got[k]), (g, k)
+                    assert_exp_match(got[4], base[4], ("group", g), rtol=1e-11)
+    finally:
+        L.mab_debug_set_warp_group(0)
+    assert L.mab_debug_set_warp_group(3) != 0
+
+
 def test_full_size_properties(engine, golden):
     """Size-independent properties on a batch too large for the oracle (50k tRNA reads, ~140 M cells):
     (1) every pair is in range and unique per alignment, 0 < p_int <= 1e7  (the reference's
