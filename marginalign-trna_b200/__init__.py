@@ -7,7 +7,7 @@ The directory name is the project name and is not a valid Python identifier; imp
 from . import build, capi, em, hmm, seqio, shard, synth  # noqa: F401
 from .hmm import Hmm  # noqa: F401
 from .pairhmm import (AlignmentParameters, DevicePlan, PairHmmEngine, PairHmmModel, Plan,  # noqa: F401
-                      PosteriorPairs)
+                      PosteriorPairs, RealignedCigars, jitter_table)
 from .synth import AlignmentBatch  # noqa: F401
 
 __version__ = "0.1.0"

@@ -582,3 +582,131 @@ class PairHmmEngine:
             h.transitions, h.emissions, h.likelihood = T, E, lik
             return h
         return T, E, lik
+
+
+# ------------------------------------------------------------------------------------------------ realign tail
+class RealignedCigars:
+    """Result of PairHmmEngine.realign: the new cigar of every alignment (op codes 0 M, 1 D = reference only,
+    2 I = read only, relative to the alignment's sub-sequences, like the guide cigars of an AlignmentBatch), and the
+    chain of aligned pairs when it was asked for."""
+
+    def __init__(self, off_ops, ops, lens, chain_off=None, chain_x=None, chain_y=None):
+        self.off_ops, self.ops, self.lens = off_ops, ops, lens
+        self.chain_off, self.chain_x, self.chain_y = chain_off, chain_x, chain_y
+
+    @property
+    def n(self):
+        return len(self.off_ops) - 1
+
+    def cigar(self, i):
+        s = slice(int(self.off_ops[i]), int(self.off_ops[i + 1]))
+        return self.ops[s], self.lens[s]
+
+    def chain(self, i):
+        s = slice(int(self.chain_off[i]), int(self.chain_off[i + 1]))
+        return np.stack([self.chain_x[s], self.chain_y[s]], axis=1)
+
+
+_JITTER = {}
+
+
+def jitter_table(n_draws):
+    """The first n_draws values of glibc rand() after srand(1) (every cPecanRealign process starts there): the stream
+    behind st_random() in makeAlignmentWeight (multipleAligner.c:140-147)."""
+    have = _JITTER.get("t")
+    if have is None or len(have) < n_draws:
+        n = max(1 << 16, 1 << int(np.ceil(np.log2(max(n_draws, 2)))))
+        have = np.empty(n, dtype=np.int32)
+        capi.check(capi.load().mab_rand_sequence(1, n, have.ctypes.data))
+        _JITTER["t"] = have
+    return have
+
+
+def _realign_chunk(engine, d_off_x, d_off_y, len_x, len_y, d_pair_off, d_x, d_y, d_p, gap_gamma, match_gamma,
+                   want_chain):
+    """Device half of the realign tail for one chunk; returns host arrays (off_ops, ops, lens, chain_off, cx, cy)."""
+    torch, L = engine.torch, capi.load()
+    dev = engine.device
+    n = int(d_off_x.numel()) - 1
+    n_pairs = int(d_x.numel())
+    max_pairs = int((d_pair_off[1:] - d_pair_off[:-1]).max().item()) if n else 0
+    table = jitter_table(2 * max_pairs + 2)
+    key = (str(dev), len(table))
+    if engine._jitter_dev is None or engine._jitter_dev[0] != key:
+        engine._jitter_dev = (key, torch.from_numpy(table).to(dev))
+    d_rand = engine._jitter_dev[1]
+    ws_bytes = int(L.mab_realign_workspace_bytes(n, n_pairs, len_x, len_y))
+    d_ws = torch.empty(ws_bytes + 256, dtype=torch.uint8, device=dev)
+    ws_ptr = (d_ws.data_ptr() + 255) & ~255
+    d_op_off = torch.empty(n + 1, dtype=torch.int64, device=dev)
+    d_ch_off = torch.empty(n + 1, dtype=torch.int64, device=dev)
+    sp = engine._stream_ptr()
+    capi.check(L.mab_realign_chain(n, d_off_x.data_ptr(), d_off_y.data_ptr(), len_x, len_y, d_pair_off.data_ptr(),
+                                   d_x.data_ptr(), d_y.data_ptr(), d_p.data_ptr(), n_pairs, gap_gamma, match_gamma,
+                                   d_rand.data_ptr(), d_rand.numel(), ws_ptr, ws_bytes, d_op_off.data_ptr(),
+                                   d_ch_off.data_ptr(), sp))
+    totals = torch.stack([d_op_off[n], d_ch_off[n]]).cpu()  # one sync: output sizes are data dependent
+    n_ops, n_chain = int(totals[0]), int(totals[1])
+    d_ops = torch.empty(max(n_ops, 1), dtype=torch.uint8, device=dev)
+    d_lens = torch.empty(max(n_ops, 1), dtype=torch.int32, device=dev)
+    d_cx = torch.empty(max(n_chain, 1), dtype=torch.int32, device=dev) if want_chain else None
+    d_cy = torch.empty(max(n_chain, 1), dtype=torch.int32, device=dev) if want_chain else None
+    capi.check(L.mab_realign_emit(n, d_off_x.data_ptr(), d_off_y.data_ptr(), len_x, len_y, n_pairs, ws_ptr, ws_bytes,
+                                  d_op_off.data_ptr(), d_ch_off.data_ptr(), d_ops.data_ptr(), d_lens.data_ptr(),
+                                  d_cx.data_ptr() if want_chain else None, d_cy.data_ptr() if want_chain else None, sp))
+    out = [d_op_off.cpu().numpy(), d_ops[:n_ops].cpu().numpy(), d_lens[:n_ops].cpu().numpy()]
+    if want_chain:
+        out += [d_ch_off.cpu().numpy(), d_cx[:n_chain].cpu().numpy(), d_cy[:n_chain].cpu().numpy()]
+    else:
+        out += [None, None, None]
+    return out
+
+
+def _engine_realign(self, model, batch, params=None, gap_gamma=0.5, match_gamma=0.0, want_chain=False):
+    """Realigns every guide alignment of `batch`: posterior pairs -> AMAP reweight -> maximum-expected-accuracy chain
+    -> cigar, all on the GPU (cPecanRealign's default mode as marginAlignLib.py:315-318 drives it: --gapGamma,
+    --matchGamma, --diagonalExpansion 10 --splitMatrixBiggerThanThis 3000 --loadHmm).  Only the cigars come back."""
+    params = params or AlignmentParameters()
+    torch = self.torch
+    parts = []
+    stats = dict(cells=0, chunks=0, h2d_bytes=0, d2h_bytes=0, pairs=0)
+    first = 0
+    with torch.cuda.device(self.device):
+        for dplan in self._device_plans(batch, params, False):
+            info = dplan.plan.info
+            n = info.n_alignments
+            sub = batch.slice(first, first + n)
+            d_off, d_x, d_y, d_p = self.posteriors_device(model, dplan)
+            offs = torch.from_numpy(np.stack([np.ascontiguousarray(sub.off_x, dtype=np.int64),
+                                              np.ascontiguousarray(sub.off_y, dtype=np.int64)])).to(self.device)
+            len_x, len_y = (int(sub.off_x[-1]), int(sub.off_y[-1])) if n else (0, 0)
+            res = _realign_chunk(self, offs[0], offs[1], len_x, len_y, d_off, d_x, d_y, d_p, gap_gamma, match_gamma,
+                                 want_chain)
+            parts.append(res)
+            first += n
+            stats["cells"] += info.n_cells
+            stats["chunks"] += 1
+            stats["pairs"] += int(d_x.numel())
+            stats["h2d_bytes"] += dplan.h2d_bytes + offs.numel() * 8
+            stats["d2h_bytes"] += sum(a.nbytes for a in res if a is not None)
+            del dplan, d_off, d_x, d_y, d_p
+    self.last_stats = stats
+
+    def cat_off(idx):
+        out, base = [np.zeros(1, dtype=np.int64)], 0
+        for p in parts:
+            out.append(p[idx][1:] + base)
+            base += int(p[idx][-1])
+        return np.concatenate(out)
+
+    def cat(idx, dtype):
+        return np.concatenate([p[idx] for p in parts]) if parts else np.zeros(0, dtype=dtype)
+
+    if want_chain:
+        return RealignedCigars(cat_off(0), cat(1, np.uint8), cat(2, np.int32), cat_off(3), cat(4, np.int32),
+                               cat(5, np.int32))
+    return RealignedCigars(cat_off(0), cat(1, np.uint8), cat(2, np.int32))
+
+
+PairHmmEngine.realign = _engine_realign
+PairHmmEngine._jitter_dev = None
