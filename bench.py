@@ -41,7 +41,9 @@ def parse_args():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default="trna", choices=["trna", "long"])
-    ap.add_argument("--mode", default="posterior", choices=["posterior", "em"])
+    ap.add_argument("--mode", default="posterior", choices=["posterior", "em", "realign"],
+                    help="posterior: getAlignedPairsUsingAnchors; em: getExpectationsUsingAnchors; realign: posterior "
+                         "+ AMAP reweight + MEA chain + cigar (cPecanRealign's default mode)")
     ap.add_argument("--reads", type=int, default=0, help="alignments per GPU per step (default: 1M tRNA / 2000 long)")
     ap.add_argument("--expansion", type=int, default=0, help="diagonalExpansion (default 10 tRNA / 50 long)")
     ap.add_argument("--e2e-steps", type=int, default=2)
@@ -149,12 +151,18 @@ def _ref_work(item):
         pr = _W["pyref"]
         if mode == "posterior":
             return len(pr.aligned_pairs(_W["model"], x, y, anchors, expansion=exp, split=split))
+        if mode == "realign":  # cPecanRealign.c:584-611 through the reference library
+            pairs = pr.aligned_pairs(_W["model"], x, y, anchors, expansion=exp, split=split)
+            return len(pr.realign_tail(pairs, x, y, 0.5, 0.0, seed=1))
         pr.expectations(_W["model"], x, y, anchors, expansion=exp, split=split)
         return 0
     po = _W["po"]
     P = po.make_params(expansion=exp, split=split)
     if mode == "posterior":
         return len(po.aligned_pairs(_W["model"], x, y, anchors, P))
+    if mode == "realign":
+        pairs = po.aligned_pairs(_W["model"], x, y, anchors, P)
+        return len(po.realign_chain(pairs, len(x), len(y), 0.5, 0.0, seed=1)[0])
     po.expectations(_W["model"], x, y, anchors, P)
     return 0
 
@@ -189,8 +197,10 @@ def cpu_reference_throughput(batch, params, mode, n_sample, steps=1, warmup=0):
     return dict(value=cells / dt / 1e9, unit="GCUPS", cores=cores, kind=kind, ms_per_step=dt * 1e3,
                 reads_per_s=n_sample / dt, cells=int(cells),
                 sample="first %d alignments of the workload (%d cells), %s mode, one %s call per alignment in a "
-                       "%d-process pool" % (n_sample, cells, mode, "getAlignedPairsUsingAnchors" if mode == "posterior"
-                                            else "getExpectationsUsingAnchors", cores))
+                       "%d-process pool" % (n_sample, cells, mode, {"posterior": "getAlignedPairsUsingAnchors",
+                                             "realign": "getAlignedPairsUsingAnchors + reweightAlignedPairs2 + "
+                                                        "filterPairwiseAlignmentToMakePairsOrdered",
+                                             "em": "getExpectationsUsingAnchors"}[mode], cores))
 
 
 def run_reference(args, rank, world):
@@ -277,6 +287,23 @@ def run_ours(args, rank, world, local_rank):
     init = np.full(model.n_expectations, 1e-12)
     init[-1] = 0.0
     d_exp = torch.from_numpy(init).to(dev)
+    realign = args.mode == "realign"
+    rl = []
+    if realign:  # per chunk: sequence offsets on the device; shared: jitter stream, scratch, cigar outputs
+        d_rand = torch.from_numpy(mab.jitter_table(1 << 22)).to(dev)
+        for b in chunks:
+            sub = batch.slice(*b)
+            rl.append((sub.n, torch.from_numpy(np.ascontiguousarray(sub.off_x, dtype=np.int64)).to(dev),
+                       torch.from_numpy(np.ascontiguousarray(sub.off_y, dtype=np.int64)).to(dev),
+                       int(sub.off_x[-1]), int(sub.off_y[-1])))
+        rl_ws = max(int(L.mab_realign_workspace_bytes(n, cap, lx, ly)) for n, _, _, lx, ly in rl)
+        d_rl_ws = torch.empty(rl_ws + 256, dtype=torch.uint8, device=dev)
+        rl_ptr = (d_rl_ws.data_ptr() + 255) & ~255
+        cap_ops = max(2 * (lx + ly) + n for n, _, _, lx, ly in rl)
+        d_ops = torch.empty(cap_ops, dtype=torch.uint8, device=dev)
+        d_lens = torch.empty(cap_ops, dtype=torch.int32, device=dev)
+        d_op_off = torch.empty(max_n + 1, dtype=torch.int64, device=dev)
+        d_ch_off = torch.empty(max_n + 1, dtype=torch.int64, device=dev)
 
     def resident_step():
         for p, db in zip(plans, d_blobs):
@@ -287,6 +314,15 @@ def run_ours(args, rank, world, local_rank):
                                                     d_np.data_ptr(), sptr))
                 capi.check(L.mab_posteriors_emit(p._h, db.data_ptr(), ws_ptr, ws_need, d_x.data_ptr(), d_y.data_ptr(),
                                                  d_p.data_ptr(), cap, sptr))
+                if realign:
+                    n, ox, oy, lx, ly = rl[plans.index(p)]
+                    capi.check(L.mab_realign_chain(n, ox.data_ptr(), oy.data_ptr(), lx, ly, d_off.data_ptr(),
+                                                   d_x.data_ptr(), d_y.data_ptr(), d_p.data_ptr(), cap, 0.5, 0.0,
+                                                   d_rand.data_ptr(), d_rand.numel(), rl_ptr, rl_ws,
+                                                   d_op_off.data_ptr(), d_ch_off.data_ptr(), sptr))
+                    capi.check(L.mab_realign_emit(n, ox.data_ptr(), oy.data_ptr(), lx, ly, cap, rl_ptr, rl_ws,
+                                                  d_op_off.data_ptr(), d_ch_off.data_ptr(), d_ops.data_ptr(),
+                                                  d_lens.data_ptr(), None, None, sptr))
         if em and dist is not None:
             dist.all_reduce(d_exp)  # the path's only collective: 106 (58) doubles per EM iteration
 
@@ -340,7 +376,10 @@ def run_ours(args, rank, world, local_rank):
     e2e = None
     e2e_steps = max(1, min(args.e2e_steps, args.steps))
     run_e2e = (lambda: eng.get_expectations_using_anchors(model, batch, params)) if em else \
+              (lambda: eng.realign(model, batch, params)) if realign else \
               (lambda: eng.get_aligned_pairs_using_anchors(model, batch, params))
+    if realign:
+        del d_rl_ws, d_ops, d_lens
     del d_x, d_y, d_p, d_ws, d_blobs
     torch.cuda.empty_cache()
     if not args.no_e2e:
@@ -359,8 +398,10 @@ def run_ours(args, rank, world, local_rank):
         e2e = {"value": total_cells / dt / 1e9, "unit": "GCUPS", "h2d_bytes_per_step": int(st["h2d_bytes"]),
                "d2h_bytes_per_step": int(st["d2h_bytes"]), "ms_per_step": dt * 1e3, "steps": e2e_steps,
                "reads_per_s": n_reads * world / dt, "host_wall_s": st.get("host_wall"),
-               "note": "packing of bases+cigars into pinned memory, H2D, planning on the GPU, DP kernels, D2H of the "
-                       "pairs into pinned host blocks, per step (rank 0 breakdown in host_wall_s)"}
+               "note": "packing of bases+cigars into pinned memory, H2D, planning on the GPU, DP kernels, %s, per step "
+                       "(rank 0 breakdown in host_wall_s)" % (
+                           "realign tail on the GPU, D2H of the cigars" if realign else
+                           "D2H of the expectation vector" if em else "D2H of the pairs into pinned host blocks")}
 
     if rank != 0:
         return

@@ -40,9 +40,12 @@ namespace {
 thread_local int64_t g_launches = 0;
 
 // Optional per-kernel timing with CUDA events on the launching stream (bench.py's roofline numbers).
-enum KernelId { K_FORWARD = 0, K_BACKWARD, K_TOTALS, K_POSTERIOR, K_SCAN, K_EMIT, K_EXPECT, K_COUNT };
+enum KernelId { K_FORWARD = 0, K_BACKWARD, K_TOTALS, K_POSTERIOR, K_SCAN, K_EMIT, K_EXPECT,
+                K_RL_WEIGHTS = MAB_K_RL_WEIGHTS, K_RL_CHAIN = MAB_K_RL_CHAIN, K_RL_SCAN = MAB_K_RL_SCAN,
+                K_RL_EMIT = MAB_K_RL_EMIT, K_COUNT };
 const char *const kKernelNames[K_COUNT] = {"k_forward", "k_backward", "k_totals", "k_posterior_diag", "scan+offsets",
-                                           "k_emit_diag", "k_expect"};
+                                           "k_emit_diag", "k_expect", "k_rl_weights", "k_rl_chain", "k_rl_scan",
+                                           "k_rl_emit"};
 struct TimedLaunch {
     cudaEvent_t start, stop;
     int kernel;
@@ -526,40 +529,76 @@ __device__ __forceinline__ DiagWork diag_work(const Blob &bl, int64_t g) {
     return k;
 }
 
+// One warp per group of 32 consecutive diagonals: lane i owns diagonal g0 + i (its DiagWork, its total, its pair count)
+// while the cells of the whole group -- contiguous in memory -- are swept 32 at a time, every lane finding the diagonal
+// of its cell among the 32 starts by a shuffle binary search.  Loads of F / B and the store of pint are coalesced
+// whatever the band width (a thread per diagonal walked 13 ... 500 cells serially with a stride between lanes).
 __global__ void __launch_bounds__(256)
 k_posterior_diag(Blob bl, int64_t n_diagonals, const double *__restrict__ F, const double *__restrict__ B,
                  const double *__restrict__ totals, double threshold, double log_reject, int32_t *__restrict__ pint,
                  int64_t *__restrict__ counts) {
-    const int64_t g = (int64_t) blockIdx.x * blockDim.x + threadIdx.x;
-    if (g > n_diagonals) return;
-    if (g == n_diagonals) {  // sentinel: the scan leaves the total number of pairs here
-        counts[g] = 0;
-        return;
-    }
-    const DiagWork k = diag_work(bl, g);
-    int64_t count = 0;
-    if (k.d >= 1) {
-        const double total = totals[k.tot];
-        for (int j = 0; j < k.w; j++) {
-            const int xmy = k.xmyL + 2 * j;
-            const int x = (k.d + xmy) >> 1, y = (k.d - xmy) >> 1;
+    const int lane = threadIdx.x & 31;
+    const int64_t warp = ((int64_t) blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int64_t g0 = warp * 32;
+    if (g0 > n_diagonals) return;
+    const int64_t g = g0 + lane;
+    if (g == n_diagonals) counts[g] = 0;  // sentinel: the scan leaves the total number of pairs here
+    const bool mine = g < n_diagonals;
+    DiagWork k;
+    k.c0 = 0, k.w = 0, k.d = 0, k.xmyL = 0, k.slot = 0, k.tot = 0, k.x1 = 0, k.y1 = 0;
+    if (mine) k = diag_work(bl, g);
+    const double my_total = (mine && k.d >= 1) ? totals[k.tot] : 0.0;
+    const int64_t base = __shfl_sync(FULL_MASK, k.c0, 0);
+    const int64_t g_last = min(g0 + 32, n_diagonals);  // one past the last diagonal of the group
+    const int64_t end = bl.diags[g_last].cell_off;
+    // start of my diagonal relative to the group; lanes past the last diagonal hold "infinity"
+    const int my_start = mine ? (int) (k.c0 - base) : 0x7fffffff;
+    int count = 0;
+    const int n_iter = (int) ((end - base + 31) >> 5);  // uniform: the shuffles need every lane in every round
+    for (int it = 0; it < n_iter; it++) {
+        const int64_t c = base + (int64_t) it * 32 + lane;
+        const bool active = c < end;
+        const int rel = active ? (int) (c - base) : 0;
+        int q = 0;  // largest lane whose diagonal starts at or before my cell
+#pragma unroll
+        for (int step = 16; step > 0; step >>= 1) {
+            const int t = __shfl_sync(FULL_MASK, my_start, (q + step) & 31);
+            if (q + step < 32 && t <= rel) q += step;
+        }
+        const int d = __shfl_sync(FULL_MASK, k.d, q);
+        const int xmyL = __shfl_sync(FULL_MASK, k.xmyL, q);
+        const int start = __shfl_sync(FULL_MASK, my_start, q);
+        const double total = __shfl_sync(FULL_MASK, my_total, q);
+        bool hit = false;
+        if (active && d >= 1) {
+            const int xmy = xmyL + 2 * (rel - start);
+            const int x = (d + xmy) >> 1, y = (d - xmy) >> 1;
             int32_t v = -1;
             if (x > 0 && y > 0) {
-                const double s = __dsub_rn(__dadd_rn(F[k.c0 + j], B[k.c0 + j]), total);
+                const double s = __dsub_rn(__dadd_rn(F[c], B[c]), total);
                 // exp() only where the pair can pass: s < log(threshold) - 0.1 implies exp(s) < threshold
                 if (s >= log_reject) {
                     double p = exp(s);
                     if (p >= threshold) {
                         if (p > 1.0) p = 1.0;
                         v = (int32_t) floor(__dmul_rn(p, MAB_PROB_1));
-                        count++;
+                        hit = true;
                     }
                 }
             }
-            pint[k.c0 + j] = v;
+            pint[c] = v;
+        }
+        // pairs per diagonal: every lane counts the hits that landed on ITS diagonal
+        const unsigned hits = __ballot_sync(FULL_MASK, hit);
+        if (hits) {
+#pragma unroll 1
+            for (unsigned m = hits; m; m &= m - 1) {
+                const int src = __ffs(m) - 1;
+                if (__shfl_sync(FULL_MASK, q, src) == lane) count++;
+            }
         }
     }
-    counts[k.slot] = count;
+    if (mine) counts[k.slot] = count;
 }
 
 __global__ void k_pair_offsets(Blob bl, int64_t n_aln, int64_t n_regions, int64_t n_diagonals,
@@ -996,7 +1035,7 @@ int run_posteriors(const DevModel &dm, const mab_plan *plan, const void *d_blob,
         // exp() is skipped where it cannot reach the threshold (log(0) = -inf: never skipped)
         const double log_reject = thr > 0.0 ? std::log(thr) - 0.1 : -INFINITY;
         k_posterior_diag<<<(unsigned) ((nD + 1 + 255) / 256), 256, 0, st>>>(bl, nD, w.fwd, w.bwd, w.totals, thr, log_reject,
-                                                                          w.pint, w.counts);
+                                                                          w.pint, w.counts);  // a warp per 32 diagonals
     }
     {
         LaunchTimer lt(K_SCAN, st);
@@ -1093,7 +1132,9 @@ extern "C" int mab_kernel_times(double *ms, int64_t *launches, int reset) {
     return MAB_OK;
 }
 
-void mab_count_launches(int n) { g_launches += n; }  // launches issued by realign.cu
+// launch accounting / event timing for the kernels of realign.cu
+void *mab_launch_timer_begin(int kernel, void *stream) { return new LaunchTimer(kernel, (cudaStream_t) stream); }
+void mab_launch_timer_end(void *timer) { delete static_cast<LaunchTimer *>(timer); }
 
 extern "C" int64_t mab_launch_count(int reset) {
     const int64_t v = g_launches;

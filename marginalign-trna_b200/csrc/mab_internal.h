@@ -13,6 +13,14 @@
 
 void mab_set_error(const char *fmt, ...);
 
+// kernel ids of realign.cu inside the per-kernel timing table of kernels.cu (mab_kernel_times)
+#define MAB_K_RL_WEIGHTS 7
+#define MAB_K_RL_CHAIN 8
+#define MAB_K_RL_SCAN 9
+#define MAB_K_RL_EMIT 10
+void *mab_launch_timer_begin(int kernel, void *stream);
+void mab_launch_timer_end(void *timer);
+
 // ---------------------------------------------------------------------------------------------- model
 
 // Host model: the generic ordered-transition-list form (mirrors what stateMachine{5,3}_cellCalculate hard-code).

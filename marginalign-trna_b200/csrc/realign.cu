@@ -341,7 +341,6 @@ static int rl_check(cudaError_t e, const char *what) {
     return MAB_E_CUDA;
 }
 
-void mab_count_launches(int n);  // kernels.cu: feeds mab_launch_count()
 
 /* glibc's rand() (stdlib/random_r.c, TYPE_3: x[i] = x[i-3] + x[i-31], seeded by the 16807 Lehmer generator, first
  * 310 outputs discarded), restated so that the jitter stream does not depend on, or disturb, the process-wide libc
@@ -436,12 +435,16 @@ extern "C" int mab_realign_chain(int64_t n, const int64_t *d_off_x, const int64_
         cudaGetDevice(&dev);
         cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
         const int64_t blocks_w = std::min<int64_t>((n + 7) / 8, (int64_t) sms * 8);
+        void *t = mab_launch_timer_begin(MAB_K_RL_WEIGHTS, st);
         k_rl_weights<<<(unsigned) blocks_w, 256, 0, st>>>(a);
+        mab_launch_timer_end(t);
+        t = mab_launch_timer_begin(MAB_K_RL_CHAIN, st);
         k_rl_chain<<<(unsigned) ((n + 127) / 128), 128, 0, st>>>(a);
-        mab_count_launches(2);
+        mab_launch_timer_end(t);
     }
+    void *t = mab_launch_timer_begin(MAB_K_RL_SCAN, st);
     k_rl_scan<<<1, 1024, 0, st>>>(a.cnt, n, d_op_off, d_chain_off);
-    mab_count_launches(1);
+    mab_launch_timer_end(t);
     return rl_check(cudaGetLastError(), "realign launch");
 }
 
@@ -457,8 +460,9 @@ extern "C" int mab_realign_emit(int64_t n, const int64_t *d_off_x, const int64_t
         mab_set_error("realign emit: missing outputs");
         return MAB_E_ARG;
     }
+    void *t = mab_launch_timer_begin(MAB_K_RL_EMIT, stream);
     k_rl_emit<<<(unsigned) ((n + 127) / 128), 128, 0, (cudaStream_t) stream>>>(a, d_op_off, d_chain_off, d_ops, d_lens,
                                                                             d_chain_x, d_chain_y);
-    mab_count_launches(1);
+    mab_launch_timer_end(t);
     return rl_check(cudaGetLastError(), "realign emit launch");
 }
