@@ -1,0 +1,65 @@
+"""BASELINE config 2 on the GPU: EM training of the 5-state asymmetric model, 10 iterations, on the reference's own
+fixture alignments (tests/inputBigMutations.sam reads vs tests/referencesMutated.fa, stored in
+tests/golden/bigmutations_alignments.json), marginAlign's EM parameters (expansion 10, split 300, trainEmissions;
+src/margin/marginAlign.py:41-52, cPecanEm.py:107-202).  The same loop is run with the CPU oracle computing the
+expectations; the per-iteration likelihoods and the final normalised model must agree within 1e-5 relative (spec),
+what we assert is 1e-7."""
+import json
+import os
+
+import numpy as np
+import pytest
+
+import marginalign_trna_b200 as mab
+from conftest import GOLDEN
+from oracle import pyoracle as po
+
+pytestmark = pytest.mark.gpu
+
+ITERATIONS = 10
+RTOL = 1e-7  # spec: 1e-5
+
+
+def oracle_em(batch, options):
+    """cPecanEm.py:107-202 with the oracle as the E-step."""
+    hmm = mab.em.initial_hmm(options)
+    oP = po.make_params(expansion=options.diagonalExpansion, split=options.splitMatrixBiggerThanThis ** 2)
+    running = []
+    for _ in range(options.iterations):
+        om = po.model_from_hmm(hmm._modelTypeInt(), hmm.transitions, hmm.emissions)
+        S = om.S
+        T, E, lik = np.full(S * S, 1e-12), np.full(S * 16, 1e-12), 0.0
+        for i in range(batch.n):
+            anc = po.anchors_from_cigar(*batch.cigar(i), batch.x(i), batch.y(i))
+            T, E, lik = po.expectations(om, batch.x(i), batch.y(i), anc, oP, T=T, E=E, lik=lik)
+        new = mab.Hmm(hmm.modelType)
+        new.addExpectations(T, E, lik)
+        hmm = mab.em.maximisation(new, hmm, options)
+        running.append(hmm.likelihood)
+    return hmm, running
+
+
+@pytest.mark.parametrize("model_type,start", [("fiveStateAsymmetric", "fixture"), ("threeState", "equal")])
+def test_em_ten_iterations_match_the_oracle(tmp_path, model_type, start):
+    with open(os.path.join(GOLDEN, "bigmutations_alignments.json")) as fh:
+        alns = json.load(fh)[:5]
+    b = mab.AlignmentBatch.from_lists([a["x"] for a in alns], [a["y"] for a in alns],
+                                      [(a["ops"], a["lens"]) for a in alns])
+    kw = dict(iterations=ITERATIONS, trials=1, modelType=model_type)
+    if start == "fixture":
+        kw["inputModel"] = os.path.join(GOLDEN, "input_model.hmm")
+    else:
+        kw["randomStart"] = False
+    out = str(tmp_path / "trained.hmm")
+    eng = mab.PairHmmEngine()
+    got = mab.em.expectation_maximisation_trials(eng, b, out, mab.em.EmOptions(**kw))
+    want, running = oracle_em(b, mab.em.EmOptions(**kw))
+    assert len(got.runningLikelihoods) == ITERATIONS
+    np.testing.assert_allclose(got.runningLikelihoods, running, rtol=RTOL)
+    np.testing.assert_allclose(got.transitions, want.transitions, rtol=RTOL, atol=1e-300)
+    np.testing.assert_allclose(got.emissions, want.emissions, rtol=RTOL, atol=1e-300)
+    # EM must not lose likelihood (the reference's own test_em_* check, pairwiseAlignerTest.c:769-832)
+    assert all(b2 >= a2 - abs(a2) * 1e-9 for a2, b2 in zip(running, running[1:]))
+    # the written model loads back to the same parameters (the .hmm file stays drop-in)
+    back = mab.Hmm.loadHmm(out)
+    np.testing.assert_allclose(back.transitions, got.transitions, rtol=1e-6)
