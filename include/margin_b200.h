@@ -185,6 +185,24 @@ int mab_realign_emit(int64_t n, const int64_t *d_off_x, const int64_t *d_off_y, 
  * (sonLib/C/impl/sonLibRandom.c:39-43) without touching the process-wide libc generator. */
 int mab_rand_sequence(uint32_t seed, int64_t n, int32_t *out);
 
+/* ---- marginCaller columns -----------------------------------------------------------------------
+ * Replaces the consumer of --outputAllPosteriorProbs in posteriorProbabilityCalculationTargetFn
+ * (src/margin/marginCallerLib.py:58-68) and the per-column calculation of variantCallSamFileTargetFn (:189-209,
+ * calcBasePosteriorProbs :81-92), on the device-resident output of mab_posteriors_emit.
+ *   mab_columns_accumulate: table[col_base[i] + x][base of read[y]] += round6(p_int / 1e7) for every pair (x, y,
+ *       p_int) of alignment i, in units of 1e-6 (the "%f" the reference writes and re-reads, cPecanRealign.c:346-351).
+ *       d_table: int64 [n_columns][4] (A, C, G, T), zeroed by the caller before the first batch; d_col_base[i] =
+ *       column of the first base of alignment i's reference window (offset of its reference sequence in the
+ *       concatenated column space + the alignment's reference start).  d_seq_y / d_off_y: the read sub-sequences.
+ *   mab_columns_call: d_post[n_columns][4] = posterior of each true base given the normalised observations;
+ *       d_log_err[true][observed], d_log_evo[reference][true] are log substitution matrices; d_ref the reference
+ *       bases (ASCII) of the column space.  Columns with no observation or a non-ACGT reference base give zeros. */
+int mab_columns_accumulate(int64_t n, const int64_t *d_pair_off, const int32_t *d_x, const int32_t *d_y,
+        const int32_t *d_p, const uint8_t *d_seq_y, const int64_t *d_off_y, const int64_t *d_col_base,
+        int64_t *d_table, int64_t n_columns, void *stream);
+int mab_columns_call(const int64_t *d_table, int64_t n_columns, const uint8_t *d_ref, const double *d_log_err,
+        const double *d_log_evo, double *d_post, void *stream);
+
 /* Debug/test hook: copies the forward / backward matrices ([cell][S] doubles, cells in plan order) and the totals
  * out of the workspace after a compute call.  Any pointer may be NULL. */
 int mab_debug_copy_matrices(const mab_plan *plan, const void *d_ws, double *h_fwd, double *h_bwd, double *h_totals,

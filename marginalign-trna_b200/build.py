@@ -5,7 +5,7 @@ import subprocess
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB_PATH = os.path.join(HERE, "libmargin_b200.so")
-SOURCES = ["kernels.cu", "plan_device.cu", "realign.cu", "plan.cpp", "model.cpp"]
+SOURCES = ["kernels.cu", "plan_device.cu", "realign.cu", "columns.cu", "plan.cpp", "model.cpp"]
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
     # the DP must not contract a*b+c into FMA (the reference is built without FMA); kernels also use explicit

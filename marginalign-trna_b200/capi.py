@@ -72,6 +72,8 @@ SIGNATURES = {
     "mab_realign_emit": (C.c_int, [C.c_int64, vp, vp, C.c_int64, C.c_int64, C.c_int64, vp, C.c_int64, vp, vp, vp, vp,
                                    vp, vp, vp]),
     "mab_rand_sequence": (C.c_int, [C.c_uint32, C.c_int64, vp]),
+    "mab_columns_accumulate": (C.c_int, [C.c_int64, vp, vp, vp, vp, vp, vp, vp, vp, C.c_int64, vp]),
+    "mab_columns_call": (C.c_int, [vp, C.c_int64, vp, vp, vp, vp, vp]),
     "mab_debug_set_warp_group": (C.c_int, [C.c_int]),
     "mab_launch_count": (C.c_int64, [C.c_int]),
     "mab_kernel_timing": (C.c_int, [C.c_int]),

@@ -42,10 +42,10 @@ thread_local int64_t g_launches = 0;
 // Optional per-kernel timing with CUDA events on the launching stream (bench.py's roofline numbers).
 enum KernelId { K_FORWARD = 0, K_BACKWARD, K_TOTALS, K_POSTERIOR, K_SCAN, K_EMIT, K_EXPECT,
                 K_RL_WEIGHTS = MAB_K_RL_WEIGHTS, K_RL_CHAIN = MAB_K_RL_CHAIN, K_RL_SCAN = MAB_K_RL_SCAN,
-                K_RL_EMIT = MAB_K_RL_EMIT, K_COUNT };
+                K_RL_EMIT = MAB_K_RL_EMIT, K_COL_ACC = MAB_K_COL_ACC, K_COL_CALL = MAB_K_COL_CALL, K_COUNT };
 const char *const kKernelNames[K_COUNT] = {"k_forward", "k_backward", "k_totals", "k_posterior_diag", "scan+offsets",
                                            "k_emit_diag", "k_expect", "k_rl_weights", "k_rl_chain", "k_rl_scan",
-                                           "k_rl_emit"};
+                                           "k_rl_emit", "k_col_accumulate", "k_col_call"};
 struct TimedLaunch {
     cudaEvent_t start, stop;
     int kernel;

@@ -18,6 +18,8 @@ void mab_set_error(const char *fmt, ...);
 #define MAB_K_RL_CHAIN 8
 #define MAB_K_RL_SCAN 9
 #define MAB_K_RL_EMIT 10
+#define MAB_K_COL_ACC 11   // columns.cu
+#define MAB_K_COL_CALL 12
 void *mab_launch_timer_begin(int kernel, void *stream);
 void mab_launch_timer_end(void *timer);
 
