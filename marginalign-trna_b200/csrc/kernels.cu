@@ -543,6 +543,7 @@ k_posterior_diag(Blob bl, int64_t n_diagonals, const double *__restrict__ F, con
     if (g0 > n_diagonals) return;
     const int64_t g = g0 + lane;
     if (g == n_diagonals) counts[g] = 0;  // sentinel: the scan leaves the total number of pairs here
+    if (g0 == n_diagonals) return;        // a warp that holds only the sentinel has no cells to sweep
     const bool mine = g < n_diagonals;
     DiagWork k;
     k.c0 = 0, k.w = 0, k.d = 0, k.xmyL = 0, k.slot = 0, k.tot = 0, k.x1 = 0, k.y1 = 0;

@@ -39,12 +39,17 @@ struct Front {  // one point of the frontier: 16 bytes
     int32_t y;
 };
 
+struct Rec {  // one pair as the chain DP reads it: 16 bytes, one load
+    double aw;
+    int32_t y, x;
+};
+
 struct RlLayout {  // device scratch, all offsets 256-byte aligned
     int64_t off_ix;     // int64[len_x]          indel weights of X positions, later int32 column starts / cursors
     int64_t off_iy;     // int64[len_y]          indel weights of Y positions
     int64_t off_front;  // Front[len_y + 2 n]    frontier of every alignment (lY + 2 slots each), later its chain
     int64_t off_aw;     // double[n_pairs]       avgWeight of every input pair
-    int64_t off_srt;    // int32[n_pairs]        pairs bucketed by X column (alignment-local pair indices)
+    int64_t off_rec;    // Rec[n_pairs]          pairs bucketed by X column: (avgWeight, y, x), 16 bytes each
     int64_t off_score;  // double[n_pairs]       candidate score, by sorted position
     int64_t off_pred;   // int32[n_pairs]        candidate predecessor (sorted position, -1 = start)
     int64_t off_cnt;    // int32[2 n]            per alignment: op count, chain length
@@ -60,7 +65,7 @@ RlLayout rl_layout(int64_t n, int64_t n_pairs, int64_t len_x, int64_t len_y) {
     l.off_iy = o, o = align256(o + 8 * std::max<int64_t>(len_y, 1));
     l.off_front = o, o = align256(o + 16 * std::max<int64_t>(len_y + 2 * n, 1));
     l.off_aw = o, o = align256(o + 8 * std::max<int64_t>(n_pairs, 1));
-    l.off_srt = o, o = align256(o + 4 * std::max<int64_t>(n_pairs, 1));
+    l.off_rec = o, o = align256(o + 16 * std::max<int64_t>(n_pairs, 1));
     l.off_score = o, o = align256(o + 8 * std::max<int64_t>(n_pairs, 1));
     l.off_pred = o, o = align256(o + 4 * std::max<int64_t>(n_pairs, 1));
     l.off_cnt = o, o = align256(o + 8 * std::max<int64_t>(n, 1));
@@ -78,7 +83,8 @@ struct RlArgs {
     long long *ix, *iy;
     Front *front;
     double *aw, *score;
-    int32_t *srt, *pred, *cnt;
+    Rec *rec;
+    int32_t *pred, *cnt;
 };
 
 #define RL_FULL 0xffffffffu
@@ -137,8 +143,8 @@ __global__ void __launch_bounds__(256) k_rl_weights(RlArgs a) {
             carry += __shfl_sync(RL_FULL, s, 31);
         }
         __syncwarp();
-        int32_t *srt = a.srt + p0;
-        for (int i = lane; i < np; i += 32) srt[atomicAdd(&col[px[i]], 1)] = i;
+        Rec *rec = a.rec + p0;
+        for (int i = lane; i < np; i += 32) rec[atomicAdd(&col[px[i]], 1)] = Rec{a.aw[p0 + i], py[i], px[i]};
         __syncwarp();
     }
 }
@@ -180,80 +186,104 @@ __device__ __forceinline__ int cigar_walk(const int2 *xy, int m, int lX, int lY,
     return n;
 }
 
+// The frontier holds the (-1, -1) start sentinel in slot 0 and the real points after it; the (lX, lY) end sentinel of
+// the reference (score INT64_MAX) is virtual: "slot nf".  `top` is a register copy of the right-most point: in a band
+// most candidates lie to its right, so their predecessor is `top` itself and they are appended with a single store.
+struct Frontier {
+    Front *fr;
+    int nf;
+    Front top;
+    __device__ __forceinline__ Front before(int y) const {  // stSortedSet_searchLessThan: last point with y' < y
+        if (top.y < y) return top;
+        int f = nf - 2;
+        while (fr[f].y >= y) f--;  // fr[0].y = -1 stops it
+        return fr[f];
+    }
+    __device__ __forceinline__ void insert(double s, int cand, int y) {  // :412-431
+        if (top.y < y) {  // lands just before the end sentinel, evicts nothing
+            top = Front{s, cand, y};
+            fr[nf++] = top;
+            return;
+        }
+        int g = nf - 1;
+        while (fr[g - 1].y >= y) g--;  // stSortedSet_searchGreaterThanOrEqual (exists: top.y >= y)
+        if (s >= fr[g].score || fr[g].y > y) {
+            int e = g;
+            while (e < nf && s >= fr[e].score) e++;  // points that score no better are evicted
+            if (e == g) {
+                for (int k = nf; k > g; k--) fr[k] = fr[k - 1];
+                nf++;
+            } else if (e > g + 1) {
+                const int drop = e - g - 1;
+                for (int k = e; k < nf; k++) fr[k - drop] = fr[k];
+                nf -= drop;
+            }
+            fr[g] = Front{s, cand, y};
+            top = fr[nf - 1];
+        }
+    }
+};
+
 __global__ void __launch_bounds__(128) k_rl_chain(RlArgs a) {
     const int64_t al = (int64_t) blockIdx.x * blockDim.x + threadIdx.x;
     if (al >= a.n) return;
     const int64_t ox = a.off_x[al], oy = a.off_y[al], p0 = a.pair_off[al];
     const int lX = (int) (a.off_x[al + 1] - ox), lY = (int) (a.off_y[al + 1] - oy);
     const int32_t *col = reinterpret_cast<const int32_t *>(a.ix + ox);
-    Front *fr = a.front + oy + 2 * al;  // lY + 2 slots
-    int32_t *srt = a.srt + p0, *pred = a.pred + p0;
+    Rec *rec = a.rec + p0;
+    int32_t *pred = a.pred + p0;
     double *score = a.score + p0;
-    const int32_t *px = a.x + p0, *py = a.y + p0;
-    const double *aw = a.aw + p0;
-    int nf = 2;
-    fr[0] = Front{0.0, -1, -1};
-    fr[1] = Front{9223372036854775808.0, -2, lY};  // (double) INT64_MAX, multipleAligner.c:377
+    Frontier F;
+    F.fr = a.front + oy + 2 * al;  // lY + 2 slots
+    F.nf = 1;
+    F.top = Front{0.0, -1, -1};
+    F.fr[0] = F.top;
     int start = 0;
     for (int x = 0; x < lX; x++) {
         const int end = col[x];
-        if (end > start) {
+        if (end == start + 1) {  // one weight in the column (the common case): score it and insert it
+            const Rec r = rec[start];
+            if (r.aw >= a.match_gamma && r.aw > 0.0) {
+                const Front pr = F.before(r.y);
+                pred[start] = pr.cand;
+                F.insert(__dadd_rn(pr.score, r.aw), start, r.y);
+            }
+        } else if (end > start) {
             for (int i = start + 1; i < end; i++) {  // the column's weights by Y (they arrive in atomic order)
-                const int v = srt[i], vy = py[v];
+                const Rec v = rec[i];
                 int j = i;
-                while (j > start && py[srt[j - 1]] > vy) {
-                    srt[j] = srt[j - 1];
+                while (j > start && rec[j - 1].y > v.y) {
+                    rec[j] = rec[j - 1];
                     j--;
                 }
-                srt[j] = v;
+                rec[j] = v;
             }
             // every admissible weight against the frontier as it stood before this column (:386-407)
             for (int i = start; i < end; i++) {
-                const int v = srt[i];
-                const double w = aw[v];
-                if (w >= a.match_gamma && w > 0.0) {
-                    const int y = py[v];
-                    int f = nf - 1;
-                    while (fr[f].y >= y) f--;  // stSortedSet_searchLessThan; fr[0].y = -1 stops it
-                    score[i] = __dadd_rn(fr[f].score, w);
-                    pred[i] = fr[f].cand;
+                const Rec r = rec[i];
+                if (r.aw >= a.match_gamma && r.aw > 0.0) {
+                    const Front pr = F.before(r.y);
+                    score[i] = __dadd_rn(pr.score, r.aw);
+                    pred[i] = pr.cand;
                 } else {
                     pred[i] = -3;
                 }
             }
             // the new points, right to left along Y (:410-432)
-            for (int i = end - 1; i >= start; i--) {
-                if (pred[i] == -3) continue;
-                const int y = py[srt[i]];
-                const double s = score[i];
-                int g = nf - 1;
-                while (fr[g - 1].y >= y) g--;  // stSortedSet_searchGreaterThanOrEqual; fr[nf-1].y = lY > y
-                if (s >= fr[g].score || fr[g].y > y) {
-                    int e = g;
-                    while (s >= fr[e].score) e++;  // evicted points; the end sentinel's score stops it
-                    if (e == g) {
-                        for (int k = nf; k > g; k--) fr[k] = fr[k - 1];
-                        nf++;
-                    } else if (e > g + 1) {
-                        const int drop = e - g - 1;
-                        for (int k = e; k < nf; k++) fr[k - drop] = fr[k];
-                        nf -= drop;
-                    }
-                    fr[g] = Front{s, i, y};
-                }
-            }
+            for (int i = end - 1; i >= start; i--)
+                if (pred[i] != -3) F.insert(score[i], i, rec[i].y);
         }
         start = end;
     }
     // traceback from the right-most real point (:436-463); the chain, ascending, replaces the frontier
-    const int last = fr[nf - 2].cand;
+    const int last = F.top.cand;
     int m = 0;
     for (int t = last; t >= 0; t = pred[t]) m++;
-    int2 *chain = reinterpret_cast<int2 *>(fr);
+    int2 *chain = reinterpret_cast<int2 *>(F.fr);
     int k = m;
     for (int t = last; t >= 0; t = pred[t]) {
-        const int v = srt[t];
-        chain[--k] = make_int2(px[v], py[v]);
+        const Rec r = rec[t];
+        chain[--k] = make_int2(r.x, r.y);
     }
     a.cnt[2 * al] = cigar_walk<false>(chain, m, lX, lY, nullptr, nullptr);
     a.cnt[2 * al + 1] = m;
@@ -403,7 +433,7 @@ static int rl_args(RlArgs &a, int64_t n, const int64_t *d_off_x, const int64_t *
     a.ix = (long long *) (b + l.off_ix), a.iy = (long long *) (b + l.off_iy);
     a.front = (Front *) (b + l.off_front);
     a.aw = (double *) (b + l.off_aw), a.score = (double *) (b + l.off_score);
-    a.srt = (int32_t *) (b + l.off_srt), a.pred = (int32_t *) (b + l.off_pred), a.cnt = (int32_t *) (b + l.off_cnt);
+    a.rec = (Rec *) (b + l.off_rec), a.pred = (int32_t *) (b + l.off_pred), a.cnt = (int32_t *) (b + l.off_cnt);
     a.rnd = nullptr, a.n_rand = 0, a.gap_gamma = 0.0, a.match_gamma = 0.0;
     return MAB_OK;
 }
