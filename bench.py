@@ -422,7 +422,11 @@ def run_ours(args, rank, world, local_rank):
         peak = 148 * 64 * smax * 1e6 / 1e12
         bytes_cell = S * 8  # forward/backward each write S doubles per cell to HBM
         roof = {"bound": "fp64", "kernel": dom, "achieved": achieved, "peak": peak, "unit": "TFLOP/s",
-                "frac": achieved / peak, "traffic": None,
+                "frac": achieved / peak,
+                # dram__bytes_read.sum + dram__bytes_write.sum of this kernel from the ncu --set full capture
+                # (profiles/r1_ncu_summary.md r1b: 0.48 + 2.87 GB per launch of 2.8e8 cells = 11.9 B per cell; posterior
+                # mode stores the match plane + all states on 1 diagonal in 10), scaled to this run's cells per launch
+                "traffic": (cells_per_launch * 11.9 if (S == 5 and not em) else None),
                 "peak_source": "nominal non-FMA FP64 issue rate 148 SM x 64 lanes x %.0f MHz (no measured FP64 peak "
                                "in MEASURED_PEAKS.json)" % smax,
                 "flops_per_cell": flops_cell_kernel, "ms_per_launch": per_launch_ms,

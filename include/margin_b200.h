@@ -163,7 +163,10 @@ int mab_expectations(const mab_model *m, const mab_plan *plan, const void *d_blo
  * the device-resident output of mab_posteriors_emit, for all n alignments of the batch at once; only cigars leave
  * the GPU.
  *   d_off_x / d_off_y [n+1] : sequence offsets of the batch (alignment i has lX = off_x[i+1] - off_x[i]); len_x/len_y
- *                             their last entries.  d_pair_off [n+1], d_x, d_y, d_p: as written by mab_posteriors_*.
+ *                             their last entries.  d_pair_off [n+1], d_x, d_y, d_p: as written by mab_posteriors_*;
+ *                             n_pairs = capacity of d_x/d_y/d_p (the same value in both calls).  An alignment whose
+ *                             pairs were clipped by that capacity is skipped (no operations, chain length 0): the
+ *                             caller compares the pair count of mab_posteriors_compute with its capacity.
  *   gap_gamma / match_gamma : cPecanRealign --gapGamma / --matchGamma (rounded to float like the reference).
  *   d_rand [n_rand]         : the jitter stream, mab_rand_sequence(1, n_rand, ...) copied to the device; n_rand must
  *                             be at least twice the largest pair count of one alignment (every reference process

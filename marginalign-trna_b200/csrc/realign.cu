@@ -75,6 +75,7 @@ RlLayout rl_layout(int64_t n, int64_t n_pairs, int64_t len_x, int64_t len_y) {
 
 struct RlArgs {
     int64_t n;
+    int64_t n_pairs;  // capacity of x / y / p: alignments whose pairs do not fit are skipped (chain length -1)
     const int64_t *off_x, *off_y, *pair_off;
     const int32_t *x, *y, *p;
     const int32_t *rnd;
@@ -88,6 +89,7 @@ struct RlArgs {
 };
 
 #define RL_FULL 0xffffffffu
+#define RL_LOOK 4  // columns whose loads are issued together in k_rl_chain
 
 // ------------------------------------------------------------------------------------------------ weights + buckets
 __global__ void __launch_bounds__(256) k_rl_weights(RlArgs a) {
@@ -98,6 +100,7 @@ __global__ void __launch_bounds__(256) k_rl_weights(RlArgs a) {
         const int64_t ox = a.off_x[al], oy = a.off_y[al], p0 = a.pair_off[al];
         const int lX = (int) (a.off_x[al + 1] - ox), lY = (int) (a.off_y[al + 1] - oy);
         const int np = (int) (a.pair_off[al + 1] - p0);
+        if (a.pair_off[al + 1] > a.n_pairs) continue;  // clipped by the caller's capacity: see k_rl_chain
         long long *ix = a.ix + ox, *iy = a.iy + oy;
         const int32_t *px = a.x + p0, *py = a.y + p0, *pp = a.p + p0;
         if (a.gap_gamma > 0.0) {  // reweightAlignedPairs2 returns the list untouched otherwise (:1252)
@@ -229,6 +232,11 @@ __global__ void __launch_bounds__(128) k_rl_chain(RlArgs a) {
     if (al >= a.n) return;
     const int64_t ox = a.off_x[al], oy = a.off_y[al], p0 = a.pair_off[al];
     const int lX = (int) (a.off_x[al + 1] - ox), lY = (int) (a.off_y[al + 1] - oy);
+    if (a.pair_off[al + 1] > a.n_pairs) {  // the pairs of this alignment were clipped: the caller re-runs the batch
+        a.cnt[2 * al] = 0;
+        a.cnt[2 * al + 1] = -1;
+        return;
+    }
     const int32_t *col = reinterpret_cast<const int32_t *>(a.ix + ox);
     Rec *rec = a.rec + p0;
     int32_t *pred = a.pred + p0;
@@ -238,42 +246,59 @@ __global__ void __launch_bounds__(128) k_rl_chain(RlArgs a) {
     F.nf = 1;
     F.top = Front{0.0, -1, -1};
     F.fr[0] = F.top;
+    // Columns are taken RL_LOOK at a time: their ends and the first record of each are loaded together (independent
+    // loads, one round trip for the block) before any of them is processed, so the sequential walk does not pay a
+    // dependent column-end -> record -> frontier chain per column.  A first record may turn out to be stale only in
+    // a column with several records, which re-reads them anyway.
     int start = 0;
-    for (int x = 0; x < lX; x++) {
-        const int end = col[x];
-        if (end == start + 1) {  // one weight in the column (the common case): score it and insert it
-            const Rec r = rec[start];
-            if (r.aw >= a.match_gamma && r.aw > 0.0) {
-                const Front pr = F.before(r.y);
-                pred[start] = pr.cand;
-                F.insert(__dadd_rn(pr.score, r.aw), start, r.y);
-            }
-        } else if (end > start) {
-            for (int i = start + 1; i < end; i++) {  // the column's weights by Y (they arrive in atomic order)
-                const Rec v = rec[i];
-                int j = i;
-                while (j > start && rec[j - 1].y > v.y) {
-                    rec[j] = rec[j - 1];
-                    j--;
-                }
-                rec[j] = v;
-            }
-            // every admissible weight against the frontier as it stood before this column (:386-407)
-            for (int i = start; i < end; i++) {
-                const Rec r = rec[i];
+    for (int x0 = 0; x0 < lX; x0 += RL_LOOK) {
+        int ends[RL_LOOK];
+        Rec firsts[RL_LOOK];
+#pragma unroll
+        for (int k = 0; k < RL_LOOK; k++) ends[k] = x0 + k < lX ? col[x0 + k] : -1;
+#pragma unroll
+        for (int k = 0; k < RL_LOOK; k++) {
+            const int st_k = k == 0 ? start : ends[k - 1];
+            firsts[k] = (ends[k] > st_k) ? rec[st_k] : Rec{0.0, 0, 0};
+        }
+#pragma unroll
+        for (int k = 0; k < RL_LOOK; k++) {
+            const int end = ends[k];
+            if (end < 0) break;
+            if (end == start + 1) {  // one weight in the column (the common case): score it and insert it
+                const Rec r = firsts[k];
                 if (r.aw >= a.match_gamma && r.aw > 0.0) {
                     const Front pr = F.before(r.y);
-                    score[i] = __dadd_rn(pr.score, r.aw);
-                    pred[i] = pr.cand;
-                } else {
-                    pred[i] = -3;
+                    pred[start] = pr.cand;
+                    F.insert(__dadd_rn(pr.score, r.aw), start, r.y);
                 }
+            } else if (end > start) {
+                for (int i = start + 1; i < end; i++) {  // the column's weights by Y (they arrive in atomic order)
+                    const Rec v = rec[i];
+                    int j = i;
+                    while (j > start && rec[j - 1].y > v.y) {
+                        rec[j] = rec[j - 1];
+                        j--;
+                    }
+                    rec[j] = v;
+                }
+                // every admissible weight against the frontier as it stood before this column (:386-407)
+                for (int i = start; i < end; i++) {
+                    const Rec r = rec[i];
+                    if (r.aw >= a.match_gamma && r.aw > 0.0) {
+                        const Front pr = F.before(r.y);
+                        score[i] = __dadd_rn(pr.score, r.aw);
+                        pred[i] = pr.cand;
+                    } else {
+                        pred[i] = -3;
+                    }
+                }
+                // the new points, right to left along Y (:410-432)
+                for (int i = end - 1; i >= start; i--)
+                    if (pred[i] != -3) F.insert(score[i], i, rec[i].y);
             }
-            // the new points, right to left along Y (:410-432)
-            for (int i = end - 1; i >= start; i--)
-                if (pred[i] != -3) F.insert(score[i], i, rec[i].y);
+            start = end;
         }
-        start = end;
     }
     // traceback from the right-most real point (:436-463); the chain, ascending, replaces the frontier
     const int last = F.top.cand;
@@ -298,7 +323,7 @@ __global__ void __launch_bounds__(1024) k_rl_scan(const int32_t *cnt, int64_t n,
     __syncthreads();
     for (int64_t base = 0; base < n; base += 1024) {
         const int64_t i = base + threadIdx.x;
-        long long v[2] = {i < n ? cnt[2 * i] : 0, i < n ? cnt[2 * i + 1] : 0};
+        long long v[2] = {i < n ? cnt[2 * i] : 0, i < n ? max(cnt[2 * i + 1], 0) : 0};
         long long s[2] = {v[0], v[1]};
 #pragma unroll
         for (int q = 0; q < 2; q++) {
@@ -351,6 +376,7 @@ k_rl_emit(RlArgs a, const int64_t *op_off, const int64_t *chain_off, uint8_t *op
     const int lX = (int) (a.off_x[al + 1] - a.off_x[al]), lY = (int) (a.off_y[al + 1] - oy);
     const int2 *chain = reinterpret_cast<const int2 *>(a.front + oy + 2 * al);
     const int m = a.cnt[2 * al + 1];
+    if (m < 0) return;  // skipped in k_rl_chain
     cigar_walk<true>(chain, m, lX, lY, ops + op_off[al], lens + op_off[al]);
     if (chain_x != nullptr) {
         const int64_t c0 = chain_off[al];
@@ -428,6 +454,7 @@ static int rl_args(RlArgs &a, int64_t n, const int64_t *d_off_x, const int64_t *
     }
     char *b = (char *) d_ws;
     a.n = n;
+    a.n_pairs = n_pairs;
     a.off_x = d_off_x, a.off_y = d_off_y, a.pair_off = d_pair_off;
     a.x = d_x, a.y = d_y, a.p = d_p;
     a.ix = (long long *) (b + l.off_ix), a.iy = (long long *) (b + l.off_iy);

@@ -8,6 +8,7 @@ all arithmetic happens in libmargin_b200.so (CUDA, sm_100a).  There is no CPU fa
 operations raise RuntimeError.
 """
 import ctypes as C
+import os
 import time
 from concurrent.futures import ThreadPoolExecutor
 from dataclasses import dataclass
@@ -315,17 +316,28 @@ class DevicePlan:
         len_x, len_y = (int(batch.off_x[-1]), int(batch.off_y[-1])) if n else (0, 0)
         return h_in, offs, total, n, len_x, len_y
 
-    @classmethod
-    def build_on_device(cls, batch, params, device, expectations=False, staging=None, packed=None,
-                        alloc_ws=True):
-        """Uploads bases + cigars (one pinned staging buffer, one H2D copy) and plans on the GPU."""
-        torch = require_cuda()
-        L = capi.load()
-        h_in, offs, total, n, len_x, len_y = packed if packed is not None else cls.pack_inputs(batch, staging)
+    @staticmethod
+    def upload_inputs(packed, device):
+        """H2D copy of a packed input buffer on the current stream; returns the device tensor."""
+        torch = _torch()
+        h_in, _offs, total = packed[0], packed[1], packed[2]
         d_in = torch.empty(total + 256, dtype=torch.uint8, device=device)
         base = (d_in.data_ptr() + 255) & ~255
-        d_view = d_in[base - d_in.data_ptr():base - d_in.data_ptr() + total]
-        d_view.copy_(h_in[:total], non_blocking=True)
+        d_in[base - d_in.data_ptr():base - d_in.data_ptr() + total].copy_(h_in[:total], non_blocking=True)
+        return d_in
+
+    @classmethod
+    def build_on_device(cls, batch, params, device, expectations=False, staging=None, packed=None,
+                        alloc_ws=True, d_in=None):
+        """Uploads bases + cigars (one pinned staging buffer, one H2D copy; skipped when the caller already did it and
+        passes d_in) and plans on the GPU, on the current stream."""
+        torch = require_cuda()
+        L = capi.load()
+        packed = packed if packed is not None else cls.pack_inputs(batch, staging)
+        h_in, offs, total, n, len_x, len_y = packed
+        if d_in is None:
+            d_in = cls.upload_inputs(packed, device)
+        base = (d_in.data_ptr() + 255) & ~255
         ptr = [base + o for o in offs]
         p = params.to_c()
         need = int(L.mab_plan_device_arena_hint(C.byref(p), n, len_x, len_y))
@@ -492,7 +504,7 @@ class PairHmmEngine:
                                          d_x.data_ptr(), d_y.data_ptr(), d_p.data_ptr(), total, self._stream_ptr()))
         return d_off, d_x, d_y, d_p
 
-    def get_aligned_pairs_using_anchors(self, model, batch, params=None):
+    def _get_aligned_pairs_sync(self, model, batch, params=None):
         """Posterior match probabilities of every alignment of `batch` (host in, host out)."""
         params = params or AlignmentParameters()
         torch = self.torch
@@ -530,6 +542,123 @@ class PairHmmEngine:
                 stats["h2d_bytes"] += dplan.h2d_bytes
                 stats["chunks"] += 1
                 del dplan
+            t_drain = time.perf_counter()
+            for a0, na, host, ev, _keep in pending:
+                ev.synchronize()
+                off = host[0].numpy()
+                base = int(offs[-1][-1])
+                offs.append(off[1:] + base)
+                blocks.append((a0, a0 + na, base, host[1].numpy(), host[2].numpy(), host[3].numpy()))
+                stats["d2h_bytes"] += sum(h.numel() * h.element_size() for h in host)
+            self._t["drain_s"] = time.perf_counter() - t_drain
+        stats["host_wall"] = dict(self._t)
+        if not blocks:
+            blocks = [(0, 0, 0, np.zeros(0, np.int32), np.zeros(0, np.int32), np.zeros(0, np.int32))]
+        self.last_stats = stats
+        return PosteriorPairs(np.concatenate(offs), blocks=blocks)
+
+    PAIRS_PER_CELL_CAP = float(os.environ.get("MAB_PAIR_CAP", "0.25"))  # output capacity of the sync-free path (measured: 0.07 pairs per cell at threshold 0.01)
+
+    def posteriors_async(self, model, dplan):
+        """posteriors_device without the host sync: outputs are sized by a bound (PAIRS_PER_CELL_CAP x cells; the emit
+        kernel clips at the capacity), the pair count follows asynchronously into pinned memory.  Returns a state
+        dict; `posteriors_settle` must be called before the pairs are trusted."""
+        torch, L = self.torch, capi.load()
+        info = dplan.plan.info
+        n = info.n_alignments
+        cap = int(info.n_cells * self.PAIRS_PER_CELL_CAP) + 1024
+        st = dict(dplan=dplan, n=n, cap=cap,
+                  d_off=torch.empty(n + 1, dtype=torch.int64, device=self.device),
+                  d_np=torch.empty(1, dtype=torch.int64, device=self.device),
+                  d_x=torch.empty(cap, dtype=torch.int32, device=self.device),
+                  d_y=torch.empty(cap, dtype=torch.int32, device=self.device),
+                  d_p=torch.empty(cap, dtype=torch.int32, device=self.device),
+                  h_np=torch.empty(1, dtype=torch.int64, pin_memory=True))
+        sp = self._stream_ptr()
+        capi.check(L.mab_posteriors_compute(model._h, dplan.plan._h, dplan.blob_ptr, dplan.ws_ptr, dplan.ws_bytes,
+                                            st["d_off"].data_ptr(), st["d_np"].data_ptr(), sp))
+        capi.check(L.mab_posteriors_emit(dplan.plan._h, dplan.blob_ptr, dplan.ws_ptr, dplan.ws_bytes,
+                                         st["d_x"].data_ptr(), st["d_y"].data_ptr(), st["d_p"].data_ptr(), cap, sp))
+        st["h_np"].copy_(st["d_np"], non_blocking=True)
+        st["counted"] = torch.cuda.Event()
+        st["counted"].record(torch.cuda.current_stream(self.device))
+        return st
+
+    def posteriors_settle(self, st):
+        """Waits for the pair count of an async chunk; if the bound was too small the pairs are emitted again into
+        exactly sized buffers (the workspace is still alive).  Returns the number of pairs."""
+        torch, L = self.torch, capi.load()
+        st["counted"].synchronize()
+        total = int(st["h_np"][0])
+        if total > st["cap"]:
+            dplan = st["dplan"]
+            for k in ("d_x", "d_y", "d_p"):
+                st[k] = torch.empty(total, dtype=torch.int32, device=self.device)
+            capi.check(L.mab_posteriors_emit(dplan.plan._h, dplan.blob_ptr, dplan.ws_ptr, dplan.ws_bytes,
+                                             st["d_x"].data_ptr(), st["d_y"].data_ptr(), st["d_p"].data_ptr(), total,
+                                             self._stream_ptr()))
+            st["cap"] = total
+            st["overflowed"] = True
+        st["total"] = total
+        return total
+
+    def get_aligned_pairs_using_anchors(self, model, batch, params=None):
+        """Posterior match probabilities of every alignment of `batch` (host in, host out).
+
+        Software-pipelined by one chunk: the kernels of chunk k+1 are queued before the host waits for the pair count
+        of chunk k, sizes its pinned blocks and starts their D2H copies on the copy stream, so the GPU never waits for
+        the host."""
+        # Default: one host sync per chunk (the pair count).  The sync-free, software-pipelined variant below is what
+        # PairHmmEngine.realign builds on; for plain posteriors it measured slower (254 vs 227 ms per 1 M tRNA reads,
+        # profiles/r1_ncu_summary.md r1g), so it stays opt-in.
+        if os.environ.get("MAB_POSTERIOR_ASYNC") != "1":
+            return self._get_aligned_pairs_sync(model, batch, params)
+        params = params or AlignmentParameters()
+        torch = self.torch
+        offs, blocks = [np.zeros(1, dtype=np.int64)], []
+        stats = dict(cells=0, regions=0, diagonals=0, h2d_bytes=0, d2h_bytes=0, chunks=0)
+        pending = []  # D2H copies in flight: (first alignment, n alignments, pinned tensors, event, device tensors)
+
+        def start_copy(st, a0):
+            t1 = time.perf_counter()
+            total = self.posteriors_settle(st)
+            dev = (st["d_off"], st["d_x"][:total], st["d_y"][:total], st["d_p"][:total])
+            host = [torch.empty(t.shape, dtype=t.dtype, pin_memory=True) for t in dev]
+            done = torch.cuda.Event()
+            done.record(torch.cuda.current_stream(self.device))
+            with torch.cuda.stream(self._copy_stream):
+                self._copy_stream.wait_event(done)
+                for h, t in zip(host, dev):
+                    h.copy_(t, non_blocking=True)
+                    t.record_stream(self._copy_stream)
+                ev = torch.cuda.Event()
+                ev.record(self._copy_stream)
+            pending.append((a0, st["n"], host, ev, dev))
+            st["dplan"] = None
+            self._t["host_alloc_s"] += time.perf_counter() - t1
+
+        first, prev = 0, None
+        with torch.cuda.device(self.device):
+            for k in self._t:
+                self._t[k] = 0.0
+            for dplan in self._device_plans(batch, params, False):
+                info = dplan.plan.info
+                t0 = time.perf_counter()
+                st = self.posteriors_async(model, dplan)
+                self._t["compute_s"] += time.perf_counter() - t0
+                if prev is not None:
+                    start_copy(*prev)
+                prev = (st, first)
+                first += info.n_alignments
+                stats["cells"] += info.n_cells
+                stats["regions"] += info.n_regions
+                stats["diagonals"] += info.n_diagonals
+                stats["h2d_bytes"] += dplan.h2d_bytes
+                stats["chunks"] += 1
+                del dplan, st
+            if prev is not None:
+                start_copy(*prev)
+                prev = None
             t_drain = time.perf_counter()
             for a0, na, host, ev, _keep in pending:
                 ev.synchronize()
@@ -622,74 +751,123 @@ def jitter_table(n_draws):
     return have
 
 
-def _realign_chunk(engine, d_off_x, d_off_y, len_x, len_y, d_pair_off, d_x, d_y, d_p, gap_gamma, match_gamma,
-                   want_chain):
-    """Device half of the realign tail for one chunk; returns host arrays (off_ops, ops, lens, chain_off, cx, cy)."""
+def _realign_launch(engine, model, dplan, sub, expansion, gap_gamma, match_gamma, want_chain):
+    """Queues everything one chunk needs -- posteriors, realign chain, cigar emission -- without a host sync: the
+    outputs are sized by bounds (at most 2 (lX + lY) + 1 operations and min(lX, lY) chain pairs per alignment)."""
     torch, L = engine.torch, capi.load()
     dev = engine.device
-    n = int(d_off_x.numel()) - 1
-    n_pairs = int(d_x.numel())
-    max_pairs = int((d_pair_off[1:] - d_pair_off[:-1]).max().item()) if n else 0
-    table = jitter_table(2 * max_pairs + 2)
+    st = engine.posteriors_async(model, dplan)
+    n = st["n"]
+    off_x = np.ascontiguousarray(sub.off_x, dtype=np.int64)
+    off_y = np.ascontiguousarray(sub.off_y, dtype=np.int64)
+    len_x, len_y = (int(off_x[-1]), int(off_y[-1])) if n else (0, 0)
+    h_offs = torch.from_numpy(np.stack([off_x, off_y])).pin_memory()
+    d_offs = h_offs.to(dev, non_blocking=True)
+    # jitter stream: two draws per pair; an alignment has at most one pair per band cell
+    est = int(((off_x[1:] - off_x[:-1]) + (off_y[1:] - off_y[:-1]) + 1).max() * (expansion + 4)) if n else 0
+    table = jitter_table(min(2 * est + 2, 1 << 25))
     key = (str(dev), len(table))
     if engine._jitter_dev is None or engine._jitter_dev[0] != key:
         engine._jitter_dev = (key, torch.from_numpy(table).to(dev))
     d_rand = engine._jitter_dev[1]
-    ws_bytes = int(L.mab_realign_workspace_bytes(n, n_pairs, len_x, len_y))
+    cap = st["cap"]
+    ws_bytes = int(L.mab_realign_workspace_bytes(n, cap, len_x, len_y))
     d_ws = torch.empty(ws_bytes + 256, dtype=torch.uint8, device=dev)
     ws_ptr = (d_ws.data_ptr() + 255) & ~255
-    d_op_off = torch.empty(n + 1, dtype=torch.int64, device=dev)
-    d_ch_off = torch.empty(n + 1, dtype=torch.int64, device=dev)
-    sp = engine._stream_ptr()
-    capi.check(L.mab_realign_chain(n, d_off_x.data_ptr(), d_off_y.data_ptr(), len_x, len_y, d_pair_off.data_ptr(),
-                                   d_x.data_ptr(), d_y.data_ptr(), d_p.data_ptr(), n_pairs, gap_gamma, match_gamma,
-                                   d_rand.data_ptr(), d_rand.numel(), ws_ptr, ws_bytes, d_op_off.data_ptr(),
-                                   d_ch_off.data_ptr(), sp))
-    totals = torch.stack([d_op_off[n], d_ch_off[n]]).cpu()  # one sync: output sizes are data dependent
-    n_ops, n_chain = int(totals[0]), int(totals[1])
-    d_ops = torch.empty(max(n_ops, 1), dtype=torch.uint8, device=dev)
-    d_lens = torch.empty(max(n_ops, 1), dtype=torch.int32, device=dev)
-    d_cx = torch.empty(max(n_chain, 1), dtype=torch.int32, device=dev) if want_chain else None
-    d_cy = torch.empty(max(n_chain, 1), dtype=torch.int32, device=dev) if want_chain else None
-    capi.check(L.mab_realign_emit(n, d_off_x.data_ptr(), d_off_y.data_ptr(), len_x, len_y, n_pairs, ws_ptr, ws_bytes,
-                                  d_op_off.data_ptr(), d_ch_off.data_ptr(), d_ops.data_ptr(), d_lens.data_ptr(),
-                                  d_cx.data_ptr() if want_chain else None, d_cy.data_ptr() if want_chain else None, sp))
-    out = [d_op_off.cpu().numpy(), d_ops[:n_ops].cpu().numpy(), d_lens[:n_ops].cpu().numpy()]
-    if want_chain:
-        out += [d_ch_off.cpu().numpy(), d_cx[:n_chain].cpu().numpy(), d_cy[:n_chain].cpu().numpy()]
-    else:
-        out += [None, None, None]
-    return out
+    cap_ops = 2 * (len_x + len_y) + n + 1
+    cap_chain = min(len_x, len_y) + 1
+    st.update(len_x=len_x, len_y=len_y, d_offs=d_offs, h_offs=h_offs, d_ws=d_ws, ws_ptr=ws_ptr, ws_bytes=ws_bytes,
+              d_op_off=torch.empty(n + 1, dtype=torch.int64, device=dev),
+              d_ch_off=torch.empty(n + 1, dtype=torch.int64, device=dev),
+              d_ops=torch.empty(cap_ops, dtype=torch.uint8, device=dev),
+              d_lens=torch.empty(cap_ops, dtype=torch.int32, device=dev),
+              d_cx=torch.empty(cap_chain, dtype=torch.int32, device=dev) if want_chain else None,
+              d_cy=torch.empty(cap_chain, dtype=torch.int32, device=dev) if want_chain else None,
+              h_tot=torch.empty(2, dtype=torch.int64, pin_memory=True), d_rand=d_rand,
+              gammas=(gap_gamma, match_gamma), want_chain=want_chain)
+    _realign_kernels(engine, st)
+    return st
+
+
+def _realign_kernels(engine, st):
+    torch, L = engine.torch, capi.load()
+    n, sp = st["n"], engine._stream_ptr()
+    ox, oy = st["d_offs"][0], st["d_offs"][1]
+    capi.check(L.mab_realign_chain(n, ox.data_ptr(), oy.data_ptr(), st["len_x"], st["len_y"], st["d_off"].data_ptr(),
+                                   st["d_x"].data_ptr(), st["d_y"].data_ptr(), st["d_p"].data_ptr(), st["cap"],
+                                   st["gammas"][0], st["gammas"][1], st["d_rand"].data_ptr(), st["d_rand"].numel(),
+                                   st["ws_ptr"], st["ws_bytes"], st["d_op_off"].data_ptr(),
+                                   st["d_ch_off"].data_ptr(), sp))
+    wc = st["want_chain"]
+    capi.check(L.mab_realign_emit(n, ox.data_ptr(), oy.data_ptr(), st["len_x"], st["len_y"], st["cap"], st["ws_ptr"],
+                                  st["ws_bytes"], st["d_op_off"].data_ptr(), st["d_ch_off"].data_ptr(),
+                                  st["d_ops"].data_ptr(), st["d_lens"].data_ptr(),
+                                  st["d_cx"].data_ptr() if wc else None, st["d_cy"].data_ptr() if wc else None, sp))
+    st["h_tot"].copy_(torch.stack([st["d_op_off"][n], st["d_ch_off"][n]]), non_blocking=True)
+    st["done"] = torch.cuda.Event()
+    st["done"].record(torch.cuda.current_stream(engine.device))
+
+
+def _realign_finish(engine, st):
+    """Waits for a launched chunk and brings its cigars to the host (copy stream: overlaps the next chunk's kernels)."""
+    torch, L = engine.torch, capi.load()
+    before = st["cap"]
+    engine.posteriors_settle(st)
+    if st["cap"] != before:  # the pair bound was too small (never seen at threshold 0.01): redo the tail, exact sizes
+        ws_bytes = int(L.mab_realign_workspace_bytes(st["n"], st["cap"], st["len_x"], st["len_y"]))
+        st["d_ws"] = torch.empty(ws_bytes + 256, dtype=torch.uint8, device=engine.device)
+        st["ws_ptr"], st["ws_bytes"] = (st["d_ws"].data_ptr() + 255) & ~255, ws_bytes
+        _realign_kernels(engine, st)
+    st["done"].synchronize()
+    n_ops, n_chain = int(st["h_tot"][0]), int(st["h_tot"][1])
+    dev = [st["d_op_off"], st["d_ops"][:n_ops], st["d_lens"][:n_ops]]
+    if st["want_chain"]:
+        dev += [st["d_ch_off"], st["d_cx"][:n_chain], st["d_cy"][:n_chain]]
+    host = [torch.empty(t.shape, dtype=t.dtype, pin_memory=True) for t in dev]
+    with torch.cuda.stream(engine._copy_stream):
+        for h, t in zip(host, dev):
+            h.copy_(t, non_blocking=True)
+            t.record_stream(engine._copy_stream)
+        ev = torch.cuda.Event()
+        ev.record(engine._copy_stream)
+    st["dplan"] = None
+    return host, ev, st
 
 
 def _engine_realign(self, model, batch, params=None, gap_gamma=0.5, match_gamma=0.0, want_chain=False):
     """Realigns every guide alignment of `batch`: posterior pairs -> AMAP reweight -> maximum-expected-accuracy chain
     -> cigar, all on the GPU (cPecanRealign's default mode as marginAlignLib.py:315-318 drives it: --gapGamma,
-    --matchGamma, --diagonalExpansion 10 --splitMatrixBiggerThanThis 3000 --loadHmm).  Only the cigars come back."""
+    --matchGamma, --diagonalExpansion 10 --splitMatrixBiggerThanThis 3000 --loadHmm).  Only the cigars come back.
+    Software-pipelined by one chunk like get_aligned_pairs_using_anchors."""
     params = params or AlignmentParameters()
     torch = self.torch
-    parts = []
+    copies = []
     stats = dict(cells=0, chunks=0, h2d_bytes=0, d2h_bytes=0, pairs=0)
-    first = 0
+    first, prev = 0, None
     with torch.cuda.device(self.device):
         for dplan in self._device_plans(batch, params, False):
             info = dplan.plan.info
             n = info.n_alignments
-            sub = batch.slice(first, first + n)
-            d_off, d_x, d_y, d_p = self.posteriors_device(model, dplan)
-            offs = torch.from_numpy(np.stack([np.ascontiguousarray(sub.off_x, dtype=np.int64),
-                                              np.ascontiguousarray(sub.off_y, dtype=np.int64)])).to(self.device)
-            len_x, len_y = (int(sub.off_x[-1]), int(sub.off_y[-1])) if n else (0, 0)
-            res = _realign_chunk(self, offs[0], offs[1], len_x, len_y, d_off, d_x, d_y, d_p, gap_gamma, match_gamma,
-                                 want_chain)
-            parts.append(res)
+            st = _realign_launch(self, model, dplan, batch.slice(first, first + n), params.diagonal_expansion, gap_gamma,
+                                 match_gamma, want_chain)
+            if prev is not None:
+                copies.append(_realign_finish(self, prev))
+            prev = st
             first += n
             stats["cells"] += info.n_cells
             stats["chunks"] += 1
-            stats["pairs"] += int(d_x.numel())
-            stats["h2d_bytes"] += dplan.h2d_bytes + offs.numel() * 8
-            stats["d2h_bytes"] += sum(a.nbytes for a in res if a is not None)
-            del dplan, d_off, d_x, d_y, d_p
+            stats["h2d_bytes"] += dplan.h2d_bytes + 16 * (n + 1)
+            del dplan, st
+        if prev is not None:
+            copies.append(_realign_finish(self, prev))
+            prev = None
+        parts = []
+        for host, ev, st in copies:
+            ev.synchronize()
+            arrs = [h.numpy() for h in host]
+            parts.append(arrs + [None] * (6 - len(arrs)))
+            stats["pairs"] += st["total"]
+            stats["d2h_bytes"] += sum(a.nbytes for a in arrs)
     self.last_stats = stats
 
     def cat_off(idx):

@@ -1,7 +1,12 @@
-# quick experiment matrix for the 5-state wavefront kernels (coefficient source x warps per block)
 mkdir -p gpurun_out
-timeout 900 python -m pytest tests/test_gpu_parity.py -m gpu -x -q -k "golden or batched or wide" > gpurun_out/pytest_exp.log 2>&1; echo "pytest rc=$?"; tail -3 gpurun_out/pytest_exp.log
-for cm in mixed smem const; do for nw in 4 8 16; do
-  echo "== MAB_COEF=$cm MAB_W5_WARPS=$nw"
-  MAB_COEF=$cm MAB_W5_WARPS=$nw timeout 300 python bench.py --steps 3 --warmup 2 --reads 200000 --no-e2e --no-cpu-baseline 2>&1 | python tools/bench_summary.py
-done; done
+timeout 1800 python -m pytest tests -m gpu -x -q > gpurun_out/pytest_gpu.log 2>&1; echo "pytest rc=$?"; tail -6 gpurun_out/pytest_gpu.log
+run() { name=$1; shift; timeout 900 python bench.py "$@" > gpurun_out/$name.json 2> gpurun_out/$name.err; echo "$name rc=$?"; tail -2 gpurun_out/$name.err; python tools/bench_summary.py < gpurun_out/$name.json; python - <<PY
+import json
+d=json.loads(open("gpurun_out/$name.json").read().strip().splitlines()[-1]); e=d["e2e"]; print(round(e["value"],3), round(e["ms_per_step"],1), e["host_wall_s"])
+PY
+}
+MAB_POSTERIOR_SYNC=1 run e2e_sync --steps 3 --warmup 3 --e2e-steps 3 --no-cpu-baseline
+run e2e_async --steps 3 --warmup 3 --e2e-steps 3 --no-cpu-baseline
+run e2e_realign --steps 3 --warmup 3 --e2e-steps 3 --mode realign --no-cpu-baseline
+run e2e_em --steps 3 --warmup 3 --e2e-steps 3 --mode em --reads 300000 --no-cpu-baseline
+run long_realign --steps 2 --warmup 3 --workload long --mode realign --no-cpu-baseline
