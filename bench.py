@@ -44,6 +44,9 @@ def parse_args():
     ap.add_argument("--mode", default="posterior", choices=["posterior", "em", "realign"],
                     help="posterior: getAlignedPairsUsingAnchors; em: getExpectationsUsingAnchors; realign: posterior "
                          "+ AMAP reweight + MEA chain + cigar (cPecanRealign's default mode)")
+    ap.add_argument("--states", type=int, default=5, choices=[5, 3],
+                    help="5: fiveStateAsymmetric with the tests/input.hmm values (default); 3: the built-in threeState "
+                         "model (stateMachine3_construct), our arm only")
     ap.add_argument("--reads", type=int, default=0, help="alignments per GPU per step (default: 1M tRNA / 2000 long)")
     ap.add_argument("--expansion", type=int, default=0, help="diagonalExpansion (default 10 tRNA / 50 long)")
     ap.add_argument("--e2e-steps", type=int, default=2)
@@ -251,7 +254,7 @@ def run_ours(args, rank, world, local_rank):
 
     batch, params, name = make_workload(args, rank)
     hmm = mab.Hmm.loadHmm(os.path.join(ROOT, "tests", "golden", "input_model.hmm"))
-    model = mab.PairHmmModel.from_hmm(hmm)
+    model = mab.PairHmmModel.from_hmm(hmm) if args.states == 5 else mab.PairHmmModel.default(2)
     S = model.state_number
     eng = mab.PairHmmEngine(device=dev, max_cells=args.max_cells or None)
     em = args.mode == "em"
@@ -445,7 +448,7 @@ def run_ours(args, rank, world, local_rank):
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
         "config": {"workload": name, "mode": args.mode, "alignments_per_gpu": n_reads, "cells_per_gpu": int(cells),
                    "diagonal_expansion": params.diagonal_expansion, "chunks": len(plans),
-                   "model": "fiveStateAsymmetric (tests/input.hmm values)",
+                   "model": "fiveStateAsymmetric (tests/input.hmm values)" if S == 5 else "threeState (built-in)",
                    "l2": "inputs larger than L2: %.1f GB of DP state per step" % (cells * 80 / 1e9),
                    "parallelism": "reads sharded, dp%d" % world},
         "reads_per_s": n_reads * world / (ms_step * 1e-3),

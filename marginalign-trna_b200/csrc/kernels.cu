@@ -262,6 +262,13 @@ __device__ __forceinline__ int next_item(int *counter, int lane) {
     if (lane == 0) item = atomicAdd(counter, 1);
     return __shfl_sync(FULL_MASK, item, 0);
 }
+// the same for a group of LPI lanes (32 or 16) of a warp; `mask` names the lanes of the group
+template <int LPI>
+__device__ __forceinline__ int next_item_sub(int *counter, int lane, unsigned mask) {
+    int item = 0;
+    if ((lane & (LPI - 1)) == 0) item = atomicAdd(counter, 1);
+    return __shfl_sync(mask, item, lane & ~(LPI - 1));
+}
 
 // ------------------------------------------------------------------------------------------------ forward
 // Generic one-lane-per-cell wavefront (any state count; the 3-state path).  The 5-state path uses wavefront5.cuh.
@@ -271,7 +278,7 @@ __device__ __forceinline__ int next_item(int *counter, int lane) {
 
 #include "wavefront5.cuh"
 
-template <int S, bool FULL>
+template <int S, bool FULL, int LPI>
 __global__ void __launch_bounds__(THREADS_PER_BLOCK)
 k_forward(const __grid_constant__ DevModel model, Blob bl, int n_regions, double *__restrict__ F,
           double *__restrict__ FT, int *counter, int ring_w) {
@@ -280,12 +287,15 @@ k_forward(const __grid_constant__ DevModel model, Blob bl, int n_regions, double
     for (int i = threadIdx.x; i < (int) (sizeof(DevModel) / 4); i += blockDim.x)
         ((int32_t *) &sm)[i] = ((const int32_t *) &model)[i];
     __syncthreads();
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    double *ring = reinterpret_cast<double *>(dyn_smem_raw) + (size_t) warp * 3 * ring_w * S;
+    // LPI lanes (a warp, or a half-warp when the band is at most 16 cells wide: tRNA) share one work item
+    const int lane32 = threadIdx.x & 31, lane = lane32 & (LPI - 1);
+    const int slot_id = (threadIdx.x >> 5) * (32 / LPI) + (lane32 / LPI);
+    const unsigned gmask = LPI == 32 ? FULL_MASK : (0xffffu << (lane32 & 16));
+    double *ring = reinterpret_cast<double *>(dyn_smem_raw) + (size_t) slot_id * 3 * ring_w * S;
     const double NINF = neg_inf();
 
     for (;;) {
-        const int item = next_item(counter, lane);
+        const int item = next_item_sub<LPI>(counter, lane32, gmask);
         if (item >= n_regions) break;
         const RegionDesc rg = bl.regions[bl.order_fwd[item]];
         const DiagDesc *dd = bl.diags + rg.diag_base;
@@ -296,7 +306,7 @@ k_forward(const __grid_constant__ DevModel model, Blob bl, int n_regions, double
         int L2 = 0, L1 = dd[0].xmyL, w2 = 0, w1 = (int) (c_cur - c_prev1);
         {
             const double *init = (rg.flags & 1) ? sm.ragged_start : sm.start;
-            for (int j = lane; j < w1; j += 32) {
+            for (int j = lane; j < w1; j += LPI) {
                 Cell<S> c;
 #pragma unroll
                 for (int s = 0; s < S; s++) c.v[s] = init[s];
@@ -305,7 +315,7 @@ k_forward(const __grid_constant__ DevModel model, Blob bl, int n_regions, double
                 cell_store<S>(ring + (size_t) j * S, c);
             }
         }
-        __syncwarp();
+        __syncwarp(gmask);
         for (int d = 1; d <= D; d++) {
             const DiagDesc cur = dd[d];
             const int L = cur.xmyL;
@@ -319,7 +329,7 @@ k_forward(const __grid_constant__ DevModel model, Blob bl, int n_regions, double
             double *ft = nullptr;
             if (!FULL && (cur.tot_flags & MAB_DIAG_IS_TOTAL))
                 ft = FT + (int64_t) bl.totals[cur.tot_flags & MAB_DIAG_TOT_MASK].full_off * S;
-            for (int j = lane; j < w; j += 32) {
+            for (int j = lane; j < w; j += LPI) {
                 const int xmy = L + 2 * j;
                 const int x = (d + xmy) >> 1, y = (d - xmy) >> 1;
                 const int cX = x > 0 ? sx[x - 1] : 4, cY = y > 0 ? sy[y - 1] : 4;
@@ -337,7 +347,7 @@ k_forward(const __grid_constant__ DevModel model, Blob bl, int n_regions, double
                 }
                 cell_store<S>(slot + (size_t) j * S, c);
             }
-            __syncwarp();
+            __syncwarp(gmask);
             c_cur = c_next;
             L2 = L1;
             L1 = L;
@@ -349,7 +359,7 @@ k_forward(const __grid_constant__ DevModel model, Blob bl, int n_regions, double
 
 // ------------------------------------------------------------------------------------------------ backward
 
-template <int S, bool FULL>
+template <int S, bool FULL, int LPI>
 __global__ void __launch_bounds__(THREADS_PER_BLOCK)
 k_backward(const __grid_constant__ DevModel model, Blob bl, int n_tbs, double *__restrict__ B,
            double *__restrict__ BT, double *__restrict__ edge, int *counter, int ring_w) {
@@ -358,14 +368,17 @@ k_backward(const __grid_constant__ DevModel model, Blob bl, int n_tbs, double *_
     for (int i = threadIdx.x; i < (int) (sizeof(DevModel) / 4); i += blockDim.x)
         ((int32_t *) &sm)[i] = ((const int32_t *) &model)[i];
     __syncthreads();
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    // LPI lanes (a warp, or a half-warp when the band is at most 16 cells wide: tRNA) share one work item
+    const int lane32 = threadIdx.x & 31, lane = lane32 & (LPI - 1);
+    const int slot_id = (threadIdx.x >> 5) * (32 / LPI) + (lane32 / LPI);
+    const unsigned gmask = LPI == 32 ? FULL_MASK : (0xffffu << (lane32 & 16));
     // The ring is private to the warp: the overlap diagonals (from, hi] that the reference discards must not reach
     // B, where they would collide with the next traceback's cells.
-    double *ring = reinterpret_cast<double *>(dyn_smem_raw) + (size_t) warp * 3 * ring_w * S;
+    double *ring = reinterpret_cast<double *>(dyn_smem_raw) + (size_t) slot_id * 3 * ring_w * S;
     const double NINF = neg_inf();
 
     for (;;) {
-        const int item = next_item(counter, lane);
+        const int item = next_item_sub<LPI>(counter, lane32, gmask);
         if (item >= n_tbs) break;
         const TracebackDesc tb = bl.tbs[bl.order_bwd[item]];
         const RegionDesc rg = bl.regions[tb.region];
@@ -382,7 +395,7 @@ k_backward(const __grid_constant__ DevModel model, Blob bl, int n_tbs, double *_
             double *bt = nullptr;
             if (!FULL && keep && (dd[tb.hi].tot_flags & MAB_DIAG_IS_TOTAL))
                 bt = BT + (int64_t) bl.totals[dd[tb.hi].tot_flags & MAB_DIAG_TOT_MASK].full_off * S;
-            for (int j = lane; j < w1; j += 32) {
+            for (int j = lane; j < w1; j += LPI) {
                 Cell<S> c;
 #pragma unroll
                 for (int s = 0; s < S; s++) c.v[s] = init[s];
@@ -396,7 +409,7 @@ k_backward(const __grid_constant__ DevModel model, Blob bl, int n_tbs, double *_
                 }
             }
         }
-        __syncwarp();
+        __syncwarp(gmask);
         for (int d = tb.hi - 1; d > tb.lo; d--) {
             const DiagDesc cur = dd[d];
             const int L = cur.xmyL;
@@ -412,7 +425,7 @@ k_backward(const __grid_constant__ DevModel model, Blob bl, int n_tbs, double *_
             double *bt = nullptr;
             if (!FULL && keep && (cur.tot_flags & MAB_DIAG_IS_TOTAL))
                 bt = BT + (int64_t) bl.totals[cur.tot_flags & MAB_DIAG_TOT_MASK].full_off * S;
-            for (int j = lane; j < w; j += 32) {
+            for (int j = lane; j < w; j += LPI) {
                 const int xmy = L + 2 * j;
                 const int x = (d + xmy) >> 1, y = (d - xmy) >> 1;
                 // the neighbours consume X[x] and/or Y[y] (0-based); past the end they are out of band anyway
@@ -435,7 +448,7 @@ k_backward(const __grid_constant__ DevModel model, Blob bl, int n_tbs, double *_
                     edge[tb.edge_off + j] = c.v[M];
                 }
             }
-            __syncwarp();
+            __syncwarp(gmask);
             L2 = L1;
             L1 = L;
             w2 = w1;
@@ -450,12 +463,17 @@ k_backward(const __grid_constant__ DevModel model, Blob bl, int n_tbs, double *_
 // diagonalCalculationTotalProbability (pairwiseAligner.c:566-583).  The "matches that jump over d" term rebuilds, in
 // the reference, a temporary diagonal d+1 holding only the match state reached from forward diagonal d-1; that value
 // is by construction identical to the match state of forward diagonal d+1, which we already have.
+// Four lanes per total: the per-cell dot products (S adds + S-1 logAdds each, independent) are computed four cells at a
+// time, then chained in cell order -- the chain itself stays serial because logAdd is not associative.
+// Every lane of the group carries the same chain (no broadcast needed); groups of a warp diverge freely.
 template <int S, bool FULL>
 __global__ void k_totals(Blob bl, int n_totals, const double *__restrict__ F, const double *__restrict__ B,
                          const double *__restrict__ FT, const double *__restrict__ BT,
                          const double *__restrict__ edge, double *__restrict__ totals) {
-    const int t = blockIdx.x * blockDim.x + threadIdx.x;
+    const int gt = blockIdx.x * blockDim.x + threadIdx.x;
+    const int t = gt >> 2, q = gt & 3;
     if (t >= n_totals) return;
+    const unsigned gmask = 0xFu << (threadIdx.x & 28);
     const TotalDesc td = bl.totals[t];
     const RegionDesc &rg = bl.regions[td.region];
     const DiagDesc *dd = bl.diags + rg.diag_base;
@@ -463,26 +481,42 @@ __global__ void k_totals(Blob bl, int n_totals, const double *__restrict__ F, co
     // all states of diagonal d: from the full matrices, or from the side arrays in posterior mode
     const double *f = FULL ? F + c0 * S : FT + (int64_t) td.full_off * S;
     const double *b = FULL ? B + c0 * S : BT + (int64_t) td.full_off * S;
+    const int w = (int) (c1 - c0);
     double total = neg_inf();
-    for (int64_t c = 0; c < c1 - c0; c++, f += S, b += S) {
-        double cd = __dadd_rn(f[0], b[0]);
+    for (int base = 0; base < w; base += 4) {
+        const int c = base + q;
+        double cd = neg_inf();
+        if (c < w) {
+            const double *fc = f + (int64_t) c * S, *bc = b + (int64_t) c * S;
+            cd = __dadd_rn(fc[0], bc[0]);
 #pragma unroll
-        for (int s = 1; s < S; s++) cd = la(cd, __dadd_rn(f[s], b[s]));
-        total = la(total, cd);
+            for (int s = 1; s < S; s++) cd = la(cd, __dadd_rn(fc[s], bc[s]));
+        }
+#pragma unroll
+        for (int k = 0; k < 4; k++) {
+            const double v = __shfl_sync(gmask, cd, k, 4);
+            if (base + k < w) total = la(total, v);
+        }
     }
     if (td.edge_off != MAB_THROUGH_NONE) {
         const int64_t c2 = dd[td.d + 2].cell_off;
+        const int w2 = (int) (c2 - c1);
         constexpr int STRIDE = FULL ? S : 1;  // match state of cell c: F[c*S] or the match plane F[c]
+        const double *e = td.edge_off >= 0 ? edge + td.edge_off : nullptr;  // see TracebackDesc::edge_off
         double through = neg_inf();
-        if (td.edge_off >= 0) {  // this traceback's own backward diagonal d+1 (see TracebackDesc::edge_off)
-            const double *e = edge + td.edge_off;
-            for (int64_t c = c1; c < c2; c++) through = la(through, __dadd_rn(F[c * STRIDE], e[c - c1]));
-        } else {
-            for (int64_t c = c1; c < c2; c++) through = la(through, __dadd_rn(F[c * STRIDE], B[c * STRIDE]));
+        for (int base = 0; base < w2; base += 4) {
+            const int64_t c = c1 + base + q;
+            double v = neg_inf();
+            if (base + q < w2) v = __dadd_rn(F[c * STRIDE], e != nullptr ? e[base + q] : B[c * STRIDE]);
+#pragma unroll
+            for (int k = 0; k < 4; k++) {
+                const double u = __shfl_sync(gmask, v, k, 4);
+                if (base + k < w2) through = la(through, u);
+            }
         }
         total = la(total, through);
     }
-    totals[t] = total;
+    if (q == 0) totals[t] = total;
 }
 
 // ------------------------------------------------------------------------------------------------ posteriors
@@ -1001,22 +1035,27 @@ int run_dp(const DevModel &dm, const mab_plan *plan, const Blob &bl, const Works
                 dm, bl, (int) h.n_tracebacks, w.bwd, w.bwd_tot, w.edge, w.counters + 1, ring_w);
         }
     } else {
-        if ((rc = allow_smem(k_forward<S, FULL>, lf.ring_bytes)) || (rc = allow_smem(k_backward<S, FULL>, lb.ring_bytes)))
-            return rc;
+        // generic kernels (3-state): one lane per cell; a half-warp per item when the band fits 16 lanes (tRNA), so
+        // that both halves of a warp work (measured: 3-state tRNA forward 127 -> see profiles/r1_ncu_summary.md r1h)
+        const bool half = h.n_cells <= 16 * h.n_diagonals;  // mean band width; wider diagonals take several passes
+        const int ipw = half ? 2 : 1;  // items per warp
+        auto kf = half ? k_forward<S, FULL, 16> : k_forward<S, FULL, 32>;
+        auto kb = half ? k_backward<S, FULL, 16> : k_backward<S, FULL, 32>;
+        if ((rc = allow_smem(kf, lf.ring_bytes * ipw)) || (rc = allow_smem(kb, lb.ring_bytes * ipw))) return rc;
         {
             LaunchTimer lt(K_FORWARD, st);
-            k_forward<S, FULL><<<grid_for(h.n_regions, lf.blocks_per_sm, lf.warps), lf.warps * 32, lf.ring_bytes, st>>>(
+            kf<<<grid_for(h.n_regions, lf.blocks_per_sm, lf.warps * ipw), lf.warps * 32, lf.ring_bytes * ipw, st>>>(
                 dm, bl, (int) h.n_regions, w.fwd, w.fwd_tot, w.counters + 0, ring_w);
         }
         {
             LaunchTimer lt(K_BACKWARD, st);
-            k_backward<S, FULL><<<grid_for(h.n_tracebacks, lb.blocks_per_sm, lb.warps), lb.warps * 32, lb.ring_bytes, st>>>(
+            kb<<<grid_for(h.n_tracebacks, lb.blocks_per_sm, lb.warps * ipw), lb.warps * 32, lb.ring_bytes * ipw, st>>>(
                 dm, bl, (int) h.n_tracebacks, w.bwd, w.bwd_tot, w.edge, w.counters + 1, ring_w);
         }
     }
     if (h.n_totals > 0) {
         LaunchTimer lt(K_TOTALS, st);
-        k_totals<S, FULL><<<(int) ((h.n_totals + 127) / 128), 128, 0, st>>>(bl, (int) h.n_totals, w.fwd, w.bwd, w.fwd_tot,
+        k_totals<S, FULL><<<(int) ((4 * h.n_totals + 127) / 128), 128, 0, st>>>(bl, (int) h.n_totals, w.fwd, w.bwd, w.fwd_tot,
                                                                         w.bwd_tot, w.edge, w.totals);
     }
     return check(cudaGetLastError(), "dp launch");
