@@ -278,17 +278,66 @@ __device__ __forceinline__ int next_item_sub(int *counter, int lane, unsigned ma
 
 #include "wavefront5.cuh"
 
+// 3-state cells with the branch-free logAdd of wavefront5.cuh (coefficients from a replicated shared-memory table):
+// the lanes of a (half-)warp sit on different polynomial pieces, and the branchy la() serialises them.
+struct CoefTable {
+    double2 coef[4][2][W5_COPIES];  // [piece][(c3,c2) | (c1,c0)][replica]
+};
+__device__ __forceinline__ void fill_coef_table(CoefTable &t, int tid, int nthreads) {
+    for (int i = tid; i < 4 * 2 * W5_COPIES; i += nthreads) {
+        const int piece = i / (2 * W5_COPIES), half = (i / W5_COPIES) % 2, rep = i % W5_COPIES;
+        t.coef[piece][half][rep] = make_double2(c_la_coef[piece * 4 + half * 2], c_la_coef[piece * 4 + half * 2 + 1]);
+    }
+}
+__device__ __forceinline__ Cell<3> forward_cell3_bf(const Cell<3> &lo, const Cell<3> &mi, const Cell<3> &up,
+                                                    const double *eL, const double *eM, const double *eU, unsigned cf) {
+    Cell<3> c;
+    c.v[SX] = la_bf<COEF_SMEM>(la_bf<COEF_SMEM>(__dadd_rn(lo.v[M], eL[0]), __dadd_rn(lo.v[SX], eL[1]), cf),
+                               __dadd_rn(lo.v[SY], eL[2]), cf);
+    c.v[M] = la_bf<COEF_SMEM>(la_bf<COEF_SMEM>(__dadd_rn(mi.v[M], eM[0]), __dadd_rn(mi.v[SX], eM[1]), cf),
+                              __dadd_rn(mi.v[SY], eM[2]), cf);
+    c.v[SY] = la_bf<COEF_SMEM>(la_bf<COEF_SMEM>(__dadd_rn(up.v[M], eU[0]), __dadd_rn(up.v[SY], eU[1]), cf),
+                               __dadd_rn(up.v[SX], eU[2]), cf);
+    return c;
+}
+__device__ __forceinline__ Cell<3> backward_cell3_bf(const Cell<3> &nMi, const Cell<3> &nUp, const Cell<3> &nLo,
+                                                     const double *eM, const double *eU, const double *eL, unsigned cf) {
+    Cell<3> c;
+    c.v[M] = la_bf<COEF_SMEM>(la_bf<COEF_SMEM>(__dadd_rn(nMi.v[M], eM[0]), __dadd_rn(nUp.v[SY], eU[0]), cf),
+                              __dadd_rn(nLo.v[SX], eL[0]), cf);
+    c.v[SX] = la_bf<COEF_SMEM>(la_bf<COEF_SMEM>(__dadd_rn(nMi.v[M], eM[1]), __dadd_rn(nUp.v[SY], eU[2]), cf),
+                               __dadd_rn(nLo.v[SX], eL[1]), cf);
+    c.v[SY] = la_bf<COEF_SMEM>(la_bf<COEF_SMEM>(__dadd_rn(nMi.v[M], eM[2]), __dadd_rn(nUp.v[SY], eU[1]), cf),
+                               __dadd_rn(nLo.v[SX], eL[2]), cf);
+    return c;
+}
+template <int S>
+__device__ __forceinline__ Cell<S> forward_cell_sel(const Cell<S> &lo, const Cell<S> &mi, const Cell<S> &up,
+                                                    const double *eL, const double *eM, const double *eU, unsigned cf) {
+    if constexpr (S == 3) return forward_cell3_bf(lo, mi, up, eL, eM, eU, cf);
+    else return forward_cell<S>(lo, mi, up, eL, eM, eU);
+}
+template <int S>
+__device__ __forceinline__ Cell<S> backward_cell_sel(const Cell<S> &nMi, const Cell<S> &nUp, const Cell<S> &nLo,
+                                                     const double *eM, const double *eU, const double *eL, unsigned cf) {
+    if constexpr (S == 3) return backward_cell3_bf(nMi, nUp, nLo, eM, eU, eL, cf);
+    else return backward_cell<S>(nMi, nUp, nLo, eM, eU, eL);
+}
+
 template <int S, bool FULL, int LPI>
 __global__ void __launch_bounds__(THREADS_PER_BLOCK)
 k_forward(const __grid_constant__ DevModel model, Blob bl, int n_regions, double *__restrict__ F,
           double *__restrict__ FT, int *counter, int ring_w) {
     extern __shared__ __align__(16) unsigned char dyn_smem_raw[];
     __shared__ DevModel sm;
+    __shared__ __align__(16) CoefTable ct;
     for (int i = threadIdx.x; i < (int) (sizeof(DevModel) / 4); i += blockDim.x)
         ((int32_t *) &sm)[i] = ((const int32_t *) &model)[i];
+    fill_coef_table(ct, threadIdx.x, blockDim.x);
     __syncthreads();
     // LPI lanes (a warp, or a half-warp when the band is at most 16 cells wide: tRNA) share one work item
     const int lane32 = threadIdx.x & 31, lane = lane32 & (LPI - 1);
+    const unsigned cf = (unsigned) __cvta_generic_to_shared(&ct.coef[0][0][lane32 & (W5_COPIES - 1)]);
     const int slot_id = (threadIdx.x >> 5) * (32 / LPI) + (lane32 / LPI);
     const unsigned gmask = LPI == 32 ? FULL_MASK : (0xffffu << (lane32 & 16));
     double *ring = reinterpret_cast<double *>(dyn_smem_raw) + (size_t) slot_id * 3 * ring_w * S;
@@ -338,8 +387,8 @@ k_forward(const __grid_constant__ DevModel model, Blob bl, int n_regions, double
                 const Cell<S> up = (iUp >= 0 && iUp < w1) ? cell_load<S>(slot1 + (size_t) iUp * S) : cell_fill<S>(NINF);
                 const Cell<S> mi = (d >= 2 && iMi >= 0 && iMi < w2) ? cell_load<S>(slot2 + (size_t) iMi * S)
                                                                      : cell_fill<S>(NINF);
-                const Cell<S> c = forward_cell<S>(lo, mi, up, sm.etp_lower[cX], sm.etp_middle[cX * 5 + cY],
-                                                  sm.etp_upper[cY]);
+                const Cell<S> c = forward_cell_sel<S>(lo, mi, up, sm.etp_lower[cX], sm.etp_middle[cX * 5 + cY],
+                                                      sm.etp_upper[cY], cf);
                 if (FULL) cell_store<S>(F + (c_cur + j) * S, c);
                 else {
                     F[c_cur + j] = c.v[M];
@@ -365,11 +414,14 @@ k_backward(const __grid_constant__ DevModel model, Blob bl, int n_tbs, double *_
            double *__restrict__ BT, double *__restrict__ edge, int *counter, int ring_w) {
     extern __shared__ __align__(16) unsigned char dyn_smem_raw[];
     __shared__ DevModel sm;
+    __shared__ __align__(16) CoefTable ct;
     for (int i = threadIdx.x; i < (int) (sizeof(DevModel) / 4); i += blockDim.x)
         ((int32_t *) &sm)[i] = ((const int32_t *) &model)[i];
+    fill_coef_table(ct, threadIdx.x, blockDim.x);
     __syncthreads();
     // LPI lanes (a warp, or a half-warp when the band is at most 16 cells wide: tRNA) share one work item
     const int lane32 = threadIdx.x & 31, lane = lane32 & (LPI - 1);
+    const unsigned cf = (unsigned) __cvta_generic_to_shared(&ct.coef[0][0][lane32 & (W5_COPIES - 1)]);
     const int slot_id = (threadIdx.x >> 5) * (32 / LPI) + (lane32 / LPI);
     const unsigned gmask = LPI == 32 ? FULL_MASK : (0xffffu << (lane32 & 16));
     // The ring is private to the warp: the overlap diagonals (from, hi] that the reference discards must not reach
@@ -435,8 +487,8 @@ k_backward(const __grid_constant__ DevModel model, Blob bl, int n_tbs, double *_
                 const Cell<S> nLo = (iLo >= 0 && iLo < w1) ? cell_load<S>(slot1 + (size_t) iLo * S) : cell_fill<S>(NINF);
                 const Cell<S> nMi = (have2 && iMi >= 0 && iMi < w2) ? cell_load<S>(slot2 + (size_t) iMi * S)
                                                                      : cell_fill<S>(NINF);
-                const Cell<S> c = backward_cell<S>(nMi, nUp, nLo, sm.etp_middle[cX * 5 + cY], sm.etp_upper[cY],
-                                                   sm.etp_lower[cX]);
+                const Cell<S> c = backward_cell_sel<S>(nMi, nUp, nLo, sm.etp_middle[cX * 5 + cY], sm.etp_upper[cY],
+                                                       sm.etp_lower[cX], cf);
                 cell_store<S>(slot + (size_t) j * S, c);
                 if (keep) {
                     if (FULL) cell_store<S>(B + (c0 + j) * S, c);
