@@ -280,6 +280,12 @@ __device__ __forceinline__ int next_item_sub(int *counter, int lane, unsigned ma
 
 // 3-state cells with the branch-free logAdd of wavefront5.cuh (coefficients from a replicated shared-memory table):
 // the lanes of a (half-)warp sit on different polynomial pieces, and the branchy la() serialises them.
+// One-lane-per-cell kernels: coefficient table of the branch-free logAdd of wavefront5.cuh, replicated so that a
+// 128-bit load is conflict-free whatever rows the lanes of a quarter-warp index.
+// (Measured and dropped, profiles/r1_ncu_summary.md r1h: a 16-byte packed row per piece -- the coefficients are float
+// literals, so a word can carry each one exactly -- indexed without compares through RU(d + 2^44 - 2^-8): bit-exact,
+// halves the coefficient bytes, but its 8 extra LOP3 per logAdd move the kernel from LSU-bound to issue-bound, 5 %
+// slower; mixing the two forms per logAdd was slower still.)
 struct CoefTable {
     double2 coef[4][2][W5_COPIES];  // [piece][(c3,c2) | (c1,c0)][replica]
 };
@@ -289,39 +295,73 @@ __device__ __forceinline__ void fill_coef_table(CoefTable &t, int tid, int nthre
         t.coef[piece][half][rep] = make_double2(c_la_coef[piece * 4 + half * 2], c_la_coef[piece * 4 + half * 2 + 1]);
     }
 }
+typedef unsigned CoefAddr;  // shared address of coef[0][0][replica of the lane]
+__device__ __forceinline__ double la_gap(double x, double y, CoefAddr c) { return la_bf<COEF_SMEM>(x, y, c); }
+__device__ __forceinline__ double la_chain(double x, double y, CoefAddr c) { return la_bf<COEF_SMEM>(x, y, c); }
+#define LG(x, y) la_gap((x), (y), cf)
+#define LC(x, y) la_chain((x), (y), cf)
 __device__ __forceinline__ Cell<3> forward_cell3_bf(const Cell<3> &lo, const Cell<3> &mi, const Cell<3> &up,
-                                                    const double *eL, const double *eM, const double *eU, unsigned cf) {
+                                                    const double *eL, const double *eM, const double *eU,
+                                                    const CoefAddr &cf) {
     Cell<3> c;
-    c.v[SX] = la_bf<COEF_SMEM>(la_bf<COEF_SMEM>(__dadd_rn(lo.v[M], eL[0]), __dadd_rn(lo.v[SX], eL[1]), cf),
-                               __dadd_rn(lo.v[SY], eL[2]), cf);
-    c.v[M] = la_bf<COEF_SMEM>(la_bf<COEF_SMEM>(__dadd_rn(mi.v[M], eM[0]), __dadd_rn(mi.v[SX], eM[1]), cf),
-                              __dadd_rn(mi.v[SY], eM[2]), cf);
-    c.v[SY] = la_bf<COEF_SMEM>(la_bf<COEF_SMEM>(__dadd_rn(up.v[M], eU[0]), __dadd_rn(up.v[SY], eU[1]), cf),
-                               __dadd_rn(up.v[SX], eU[2]), cf);
+    c.v[SX] = LC(LG(__dadd_rn(lo.v[M], eL[0]), __dadd_rn(lo.v[SX], eL[1])), __dadd_rn(lo.v[SY], eL[2]));
+    c.v[M] = LC(LG(__dadd_rn(mi.v[M], eM[0]), __dadd_rn(mi.v[SX], eM[1])), __dadd_rn(mi.v[SY], eM[2]));
+    c.v[SY] = LC(LG(__dadd_rn(up.v[M], eU[0]), __dadd_rn(up.v[SY], eU[1])), __dadd_rn(up.v[SX], eU[2]));
     return c;
 }
 __device__ __forceinline__ Cell<3> backward_cell3_bf(const Cell<3> &nMi, const Cell<3> &nUp, const Cell<3> &nLo,
-                                                     const double *eM, const double *eU, const double *eL, unsigned cf) {
+                                                     const double *eM, const double *eU, const double *eL,
+                                                     const CoefAddr &cf) {
     Cell<3> c;
-    c.v[M] = la_bf<COEF_SMEM>(la_bf<COEF_SMEM>(__dadd_rn(nMi.v[M], eM[0]), __dadd_rn(nUp.v[SY], eU[0]), cf),
-                              __dadd_rn(nLo.v[SX], eL[0]), cf);
-    c.v[SX] = la_bf<COEF_SMEM>(la_bf<COEF_SMEM>(__dadd_rn(nMi.v[M], eM[1]), __dadd_rn(nUp.v[SY], eU[2]), cf),
-                               __dadd_rn(nLo.v[SX], eL[1]), cf);
-    c.v[SY] = la_bf<COEF_SMEM>(la_bf<COEF_SMEM>(__dadd_rn(nMi.v[M], eM[2]), __dadd_rn(nUp.v[SY], eU[1]), cf),
-                               __dadd_rn(nLo.v[SX], eL[2]), cf);
+    // lower: M->X(0) X->X(1) Y->X(2); middle: M->M(0) X->M(1) Y->M(2); upper: M->Y(0) Y->Y(1) X->Y(2)
+    c.v[M] = LC(LG(__dadd_rn(nMi.v[M], eM[0]), __dadd_rn(nUp.v[SY], eU[0])), __dadd_rn(nLo.v[SX], eL[0]));
+    c.v[SX] = LC(LG(__dadd_rn(nMi.v[M], eM[1]), __dadd_rn(nUp.v[SY], eU[2])), __dadd_rn(nLo.v[SX], eL[1]));
+    c.v[SY] = LC(LG(__dadd_rn(nMi.v[M], eM[2]), __dadd_rn(nUp.v[SY], eU[1])), __dadd_rn(nLo.v[SX], eL[2]));
     return c;
 }
+__device__ __forceinline__ Cell<5> forward_cell5_bf(const Cell<5> &lo, const Cell<5> &mi, const Cell<5> &up,
+                                                    const double *eL, const double *eM, const double *eU,
+                                                    const CoefAddr &cf) {
+    Cell<5> c;
+    c.v[SX] = LG(__dadd_rn(lo.v[M], eL[0]), __dadd_rn(lo.v[SX], eL[1]));
+    c.v[LX] = LG(__dadd_rn(lo.v[M], eL[2]), __dadd_rn(lo.v[LX], eL[3]));
+    double m = LC(__dadd_rn(mi.v[M], eM[0]), __dadd_rn(mi.v[SX], eM[1]));
+    m = LC(m, __dadd_rn(mi.v[SY], eM[2]));
+    m = LC(m, __dadd_rn(mi.v[LX], eM[3]));
+    c.v[M] = LC(m, __dadd_rn(mi.v[LY], eM[4]));
+    c.v[SY] = LG(__dadd_rn(up.v[M], eU[0]), __dadd_rn(up.v[SY], eU[1]));
+    c.v[LY] = LG(__dadd_rn(up.v[M], eU[2]), __dadd_rn(up.v[LY], eU[3]));
+    return c;
+}
+__device__ __forceinline__ Cell<5> backward_cell5_bf(const Cell<5> &nMi, const Cell<5> &nUp, const Cell<5> &nLo,
+                                                     const double *eM, const double *eU, const double *eL,
+                                                     const CoefAddr &cf) {
+    Cell<5> c;
+    double m = LC(__dadd_rn(nMi.v[M], eM[0]), __dadd_rn(nUp.v[SY], eU[0]));
+    m = LC(m, __dadd_rn(nUp.v[LY], eU[2]));
+    m = LC(m, __dadd_rn(nLo.v[SX], eL[0]));
+    c.v[M] = LC(m, __dadd_rn(nLo.v[LX], eL[2]));
+    c.v[SX] = LG(__dadd_rn(nMi.v[M], eM[1]), __dadd_rn(nLo.v[SX], eL[1]));
+    c.v[SY] = LG(__dadd_rn(nMi.v[M], eM[2]), __dadd_rn(nUp.v[SY], eU[1]));
+    c.v[LX] = LG(__dadd_rn(nMi.v[M], eM[3]), __dadd_rn(nLo.v[LX], eL[3]));
+    c.v[LY] = LG(__dadd_rn(nMi.v[M], eM[4]), __dadd_rn(nUp.v[LY], eU[3]));
+    return c;
+}
+#undef LG
+#undef LC
 template <int S>
 __device__ __forceinline__ Cell<S> forward_cell_sel(const Cell<S> &lo, const Cell<S> &mi, const Cell<S> &up,
-                                                    const double *eL, const double *eM, const double *eU, unsigned cf) {
+                                                    const double *eL, const double *eM, const double *eU,
+                                                    const CoefAddr &cf) {
     if constexpr (S == 3) return forward_cell3_bf(lo, mi, up, eL, eM, eU, cf);
-    else return forward_cell<S>(lo, mi, up, eL, eM, eU);
+    else return forward_cell5_bf(lo, mi, up, eL, eM, eU, cf);
 }
 template <int S>
 __device__ __forceinline__ Cell<S> backward_cell_sel(const Cell<S> &nMi, const Cell<S> &nUp, const Cell<S> &nLo,
-                                                     const double *eM, const double *eU, const double *eL, unsigned cf) {
+                                                     const double *eM, const double *eU, const double *eL,
+                                                     const CoefAddr &cf) {
     if constexpr (S == 3) return backward_cell3_bf(nMi, nUp, nLo, eM, eU, eL, cf);
-    else return backward_cell<S>(nMi, nUp, nLo, eM, eU, eL);
+    else return backward_cell5_bf(nMi, nUp, nLo, eM, eU, eL, cf);
 }
 
 template <int S, bool FULL, int LPI>
@@ -337,7 +377,7 @@ k_forward(const __grid_constant__ DevModel model, Blob bl, int n_regions, double
     __syncthreads();
     // LPI lanes (a warp, or a half-warp when the band is at most 16 cells wide: tRNA) share one work item
     const int lane32 = threadIdx.x & 31, lane = lane32 & (LPI - 1);
-    const unsigned cf = (unsigned) __cvta_generic_to_shared(&ct.coef[0][0][lane32 & (W5_COPIES - 1)]);
+    const CoefAddr cf = (unsigned) __cvta_generic_to_shared(&ct.coef[0][0][lane32 & (W5_COPIES - 1)]);
     const int slot_id = (threadIdx.x >> 5) * (32 / LPI) + (lane32 / LPI);
     const unsigned gmask = LPI == 32 ? FULL_MASK : (0xffffu << (lane32 & 16));
     double *ring = reinterpret_cast<double *>(dyn_smem_raw) + (size_t) slot_id * 3 * ring_w * S;
@@ -421,7 +461,7 @@ k_backward(const __grid_constant__ DevModel model, Blob bl, int n_tbs, double *_
     __syncthreads();
     // LPI lanes (a warp, or a half-warp when the band is at most 16 cells wide: tRNA) share one work item
     const int lane32 = threadIdx.x & 31, lane = lane32 & (LPI - 1);
-    const unsigned cf = (unsigned) __cvta_generic_to_shared(&ct.coef[0][0][lane32 & (W5_COPIES - 1)]);
+    const CoefAddr cf = (unsigned) __cvta_generic_to_shared(&ct.coef[0][0][lane32 & (W5_COPIES - 1)]);
     const int slot_id = (threadIdx.x >> 5) * (32 / LPI) + (lane32 / LPI);
     const unsigned gmask = LPI == 32 ? FULL_MASK : (0xffffu << (lane32 & 16));
     // The ring is private to the warp: the overlap diagonals (from, hi] that the reference discards must not reach
@@ -1001,13 +1041,14 @@ struct WaveLaunch {
     int G, groups, warps, blocks_per_sm;
     int64_t ring_bytes;
 };
-WaveLaunch wave_launch_for(int S, int G, const BlobHeader &h) {
+WaveLaunch wave_launch_for(int S, int G, const BlobHeader &h, bool wave5 = true) {
+    wave5 = wave5 && S == 5;
     static const int w5_warps = getenv("MAB_W5_WARPS") ? std::max(1, std::min(32, atoi(getenv("MAB_W5_WARPS")))) : 8;
     const DeviceInfo &di = device_info();
     WaveLaunch l;
     l.G = G;
-    const int want_warps = S == 5 ? std::max(w5_warps / G, 1) * G : WARPS_PER_BLOCK;
-    const int64_t static_bytes = S == 5 ? (int64_t) sizeof(Wave5Shared) + 1024 : 8 * 1024;
+    const int want_warps = wave5 ? std::max(w5_warps / G, 1) * G : WARPS_PER_BLOCK;
+    const int64_t static_bytes = wave5 ? (int64_t) sizeof(Wave5Shared) + 1024 : 10 * 1024;
     const int64_t ring_per_group = (int64_t) 3 * (h.max_width + 2) * S * 8;
     const int64_t budget = (int64_t) di.max_smem_optin - static_bytes;
     l.groups = (int) std::min<int64_t>(want_warps / G, budget / std::max<int64_t>(1, ring_per_group));
@@ -1045,7 +1086,15 @@ int run_dp(const DevModel &dm, const mab_plan *plan, const Blob &bl, const Works
     const DeviceInfo &di = device_info();
     // shared-memory ring per work item: 3 diagonals x (max_width + 2 guard) cells x S doubles.  The 5-state kernels
     // also hold ~27 KB of replicated tables per block and may give one item to G warps (wave_launch).
-    const WaveLaunch lf = wave_launch(S, h.n_regions, h), lb = wave_launch(S, h.n_tracebacks, h);
+    // 5-state: narrow bands (mean width <= 16: tRNA, any read at expansion 10) run on the one-lane-per-cell kernels with
+    // a half-warp per item -- measured faster than the pair-lane kernels of wavefront5.cuh there (fewer instructions
+    // per diagonal, the shared-memory pipe binds both) -- wide bands on the pair-lane kernels with warp groups.
+    // MAB_W5=1 forces the pair-lane kernels, MAB_W5=0 the one-lane kernels.
+    static const int w5_env = getenv("MAB_W5") ? atoi(getenv("MAB_W5")) : -1;
+    const bool narrow = h.n_cells <= 16 * h.n_diagonals;
+    const bool wave5 = S == 5 && (w5_env == 1 || (w5_env != 0 && !narrow) || g_w5_group > 0);
+    const WaveLaunch lf = wave5 ? wave_launch(S, h.n_regions, h) : wave_launch_for(S, 1, h, false),
+                     lb = wave5 ? wave_launch(S, h.n_tracebacks, h) : wave_launch_for(S, 1, h, false);
     if (lf.warps < 1 || lb.warps < 1) {
         mab_set_error("band too wide for the shared-memory ring (max width %lld cells); lower diagonalExpansion or "
                       "splitMatrixBiggerThanThis", (long long) h.max_width);
@@ -1054,7 +1103,7 @@ int run_dp(const DevModel &dm, const mab_plan *plan, const Blob &bl, const Works
     const int ring_w = (int) h.max_width;
     int rc;
     if ((rc = check(cudaMemsetAsync(w.counters, 0, 256, st), "memset counters"))) return rc;
-    if (S == 5) {
+    if (wave5) {
         // where the logAdd coefficients are fetched from (wavefront5.cuh): smem (default, fastest measured) |
         // mixed | const -- kept switchable for profiling (single-warp items only)
         static const int cm = [] {

@@ -16,6 +16,7 @@ timeout 600 python bench.py --impl reference --steps 2 --warmup 1 > gpurun_out/r
 timeout 600 python bench.py --impl reference --mode realign --steps 1 --warmup 1 > gpurun_out/r1h_bench_ref_realign.json 2>> gpurun_out/r1h_bench_ref.err; echo "ref realign rc=$?"
 CMD="python bench.py --steps 1 --warmup 1 --reads 200000 --mode realign --no-e2e --no-cpu-baseline"
 $CMD > gpurun_out/plain.log 2>&1 && ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file gpurun_out/r1h_launches_trna_realign.csv $CMD > gpurun_out/ncu_l.log 2>&1; echo "ncu list rc=$?"; python tools/bench_summary.py < gpurun_out/plain.log
+ncu --set full --clock-control none --import-source on -k regex:'k_(forward|backward)$' -s 2 -c 2 -o gpurun_out/r1h_dp_trna -f $CMD > gpurun_out/ncu_f.log 2>&1; echo "ncu full trna rc=$?"
 CMD3="python bench.py --steps 1 --warmup 1 --reads 200000 --states 3 --no-e2e --no-cpu-baseline"
 $CMD3 > gpurun_out/plain3.log 2>&1 && ncu --set full --clock-control none --import-source on -k regex:'k_(forward|backward)' -s 2 -c 2 -o gpurun_out/r1h_dp_trna3 -f $CMD3 > gpurun_out/ncu_3.log 2>&1; echo "ncu full 3-state rc=$?"
 ncu --set full --clock-control none --import-source on -k regex:'k_(totals|posterior_diag|rl_chain|rl_weights)' -s 8 -c 4 -o gpurun_out/r1h_post_trna -f $CMD > gpurun_out/ncu_p.log 2>&1; echo "ncu post rc=$?"
