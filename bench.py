@@ -423,13 +423,15 @@ def run_ours(args, rank, world, local_rank):
         # denominator is nominal (148 x 64 x sm_max_mhz) and says so.
         smax = (clocks or {}).get("sm_max_mhz") or peaks.get("sm_max_mhz") or 1965.0
         peak = 148 * 64 * smax * 1e6 / 1e12
-        bytes_cell = S * 8  # forward/backward each write S doubles per cell to HBM
+        # algorithmic HBM bytes per cell of one DP kernel: posterior mode writes the match plane (8 B) and
+        # all S states on the diagonals that carry a total (1 in 10); expectation mode writes all S states
+        bytes_cell = S * 8 if em else 8 + S * 8 / 10.0
         roof = {"bound": "fp64", "kernel": dom, "achieved": achieved, "peak": peak, "unit": "TFLOP/s",
                 "frac": achieved / peak,
                 # dram__bytes_read.sum + dram__bytes_write.sum of this kernel from the ncu --set full capture
-                # (profiles/r1_ncu_summary.md r1b: 0.48 + 2.87 GB per launch of 2.8e8 cells = 11.9 B per cell; posterior
-                # mode stores the match plane + all states on 1 diagonal in 10), scaled to this run's cells per launch
-                "traffic": (cells_per_launch * 11.9 if (S == 5 and not em) else None),
+                # (profiles/r1_ncu_summary.md r1h: k_forward<5,0,16>, 0.62 GB read + 3.76 GB written for a chunk of
+                # 3.13e8 cells = 14.0 B per cell against 12 B algorithmic), scaled to this run's cells per launch
+                "traffic": (cells_per_launch * 14.0 if (S == 5 and not em and args.workload == "trna") else None),
                 "peak_source": "nominal non-FMA FP64 issue rate 148 SM x 64 lanes x %.0f MHz (no measured FP64 peak "
                                "in MEASURED_PEAKS.json)" % smax,
                 "flops_per_cell": flops_cell_kernel, "ms_per_launch": per_launch_ms,
