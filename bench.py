@@ -462,6 +462,8 @@ def run_ours(args, rank, world, local_rank):
 
 
 def main():
+    if os.environ.get("MAB_SWITCH_INTERVAL"):  # experiment knob: GIL hand-over latency between the engine's threads
+        sys.setswitchinterval(float(os.environ["MAB_SWITCH_INTERVAL"]))
     args = parse_args()
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))

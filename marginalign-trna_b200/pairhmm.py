@@ -9,6 +9,7 @@ operations raise RuntimeError.
 """
 import ctypes as C
 import os
+import threading
 import time
 from concurrent.futures import ThreadPoolExecutor
 from dataclasses import dataclass
@@ -357,8 +358,10 @@ class DevicePlan:
         else:
             raise RuntimeError("mab_plan_build_device: arena sizing did not converge")
         plan = Plan(h)
-        return cls(plan, device, expectations=expectations, _resident=(arena, aptr, total, (d_in, h_in)),
-                   _alloc_ws=alloc_ws)
+        out = cls(plan, device, expectations=expectations, _resident=(arena, aptr, total, (d_in, h_in)),
+                  _alloc_ws=alloc_ws)
+        out.input_offsets = (ptr[0], ptr[1], len_x, len_y)  # device addresses of off_x, off_y (int64 [n+1]) in d_in
+        return out
 
 
 class _Staging:
@@ -397,13 +400,15 @@ class PairHmmEngine:
             raise ValueError("plan_on must be 'device' or 'host'")
         self.plan_on = plan_on
         self.last_stats = {}
-        self._t = {"wait_plan_s": 0.0, "plan_s": 0.0, "compute_s": 0.0, "host_alloc_s": 0.0, "drain_s": 0.0}
+        self._t = {"wait_plan_s": 0.0, "plan_s": 0.0, "pack_s": 0.0, "compute_s": 0.0, "host_alloc_s": 0.0, "drain_s": 0.0}
         self._stagings = (_Staging(), _Staging())
         self._copy_stream = torch.cuda.Stream(device=self.device)
-        self._plan_stream = torch.cuda.Stream(device=self.device)
+        self._plan_streams = [torch.cuda.Stream(device=self.device)]
+        self._t_lock = threading.Lock()
 
     # ---------------------------------------------------------------- chunking
-    BASE_CELLS = 400_000_000  # chunk size that pipelines well for short reads (tRNA: ~140 k alignments per chunk)
+    PLAN_AHEAD = int(os.environ.get("MAB_PLAN_AHEAD", "2"))  # chunks planned ahead of the one computing
+    BASE_CELLS = int(os.environ.get("MAB_BASE_CELLS", "400000000"))  # chunk size that pipelines well for short reads (tRNA: ~140 k alignments per chunk)
 
     def _auto_max_cells(self, est, params, expectations):
         """Chunk size when the caller gave none.  The forward sweep of one region is sequential over its diagonals, so
@@ -454,27 +459,41 @@ class PairHmmEngine:
         chunks = self._chunks(batch, params, expectations)
         torch = self.torch
         if self.plan_on == "device":
-            # chunk k+1 is packed into pinned memory, uploaded and planned by a helper thread on its own stream while
-            # the DP kernels of chunk k run on the caller's stream (two staging buffers alternate: the H2D copy of a
-            # buffer has completed before the helper hands the plan over)
+            # chunks k+1 .. k+PLAN_AHEAD are packed into pinned memory, uploaded and planned by helper threads, each on
+            # its own stream, while the DP kernels of chunk k run on the caller's stream.  Packing (host memcpy, GIL
+            # released) of one chunk overlaps the planner kernels and their host round trips of another.  Staging
+            # buffers rotate over PLAN_AHEAD + 1 slots: the H2D copy of a buffer has completed before its helper hands
+            # the plan over, and the slot is not packed again before that plan has been consumed.
+            ahead = max(1, min(self.PLAN_AHEAD, len(chunks)))
+            while len(self._stagings) < ahead + 1:
+                self._stagings += (_Staging(),)
+            while len(self._plan_streams) < ahead:
+                self._plan_streams.append(torch.cuda.Stream(device=self.device))
+
             def make(i):
                 t0 = time.perf_counter()
-                with torch.cuda.device(self.device), torch.cuda.stream(self._plan_stream):
-                    packed = DevicePlan.pack_inputs(batch.slice(*chunks[i]), self._stagings[i % 2])
+                stream = self._plan_streams[i % ahead]
+                with torch.cuda.device(self.device), torch.cuda.stream(stream):
+                    packed = DevicePlan.pack_inputs(batch.slice(*chunks[i]), self._stagings[i % (ahead + 1)])
+                    t1 = time.perf_counter()
                     dplan = DevicePlan.build_on_device(None, params, self.device, expectations, packed=packed,
                                                        alloc_ws=False)
-                    self._plan_stream.synchronize()
-                self._t["plan_s"] += time.perf_counter() - t0
+                    stream.synchronize()
+                t2 = time.perf_counter()
+                with self._t_lock:
+                    self._t["pack_s"] += t1 - t0
+                    self._t["plan_s"] += t2 - t0
                 return dplan
 
-            with ThreadPoolExecutor(1) as pool:
-                fut = pool.submit(make, 0)
+            with ThreadPoolExecutor(ahead) as pool:
+                futs = [pool.submit(make, i) for i in range(ahead)]
                 for ci in range(len(chunks)):
                     t0 = time.perf_counter()
-                    dplan = fut.result()
+                    dplan = futs[ci].result()
+                    futs[ci] = None
                     self._t["wait_plan_s"] += time.perf_counter() - t0
-                    if ci + 1 < len(chunks):
-                        fut = pool.submit(make, ci + 1)
+                    if ci + ahead < len(chunks):
+                        futs.append(pool.submit(make, ci + ahead))
                     dplan.adopt(torch.cuda.current_stream(self.device))
                     yield dplan
             return
@@ -505,43 +524,68 @@ class PairHmmEngine:
         return d_off, d_x, d_y, d_p
 
     def _get_aligned_pairs_sync(self, model, batch, params=None):
-        """Posterior match probabilities of every alignment of `batch` (host in, host out)."""
+        """Posterior match probabilities of every alignment of `batch` (host in, host out).
+
+        One host sync per chunk (the pair count, which sizes the outputs).  The host-side work for the results of
+        chunk k (pinned blocks, queueing the D2H copies on the copy stream) is done after the DP kernels of chunk k+1
+        have been queued, so the GPU does not wait for it."""
         params = params or AlignmentParameters()
-        torch = self.torch
+        torch, L = self.torch, capi.load()
         offs, blocks = [np.zeros(1, dtype=np.int64)], []
         stats = dict(cells=0, regions=0, diagonals=0, h2d_bytes=0, d2h_bytes=0, chunks=0)
-        pending = []  # D2H copies in flight: (first alignment, n alignments, pinned tensors)
-        first = 0
+        pending = []  # D2H copies in flight: (first alignment, n alignments, pinned tensors, event, device tensors)
+
+        def start_copy(a0, na, dev, done):
+            t1 = time.perf_counter()
+            # pinned host blocks (torch's pinned allocator recycles them between calls); the D2H copies run on a
+            # second stream so they overlap the kernels of the next chunks
+            host = [torch.empty(t.shape, dtype=t.dtype, pin_memory=True) for t in dev]
+            with torch.cuda.stream(self._copy_stream):
+                self._copy_stream.wait_event(done)
+                for h, t in zip(host, dev):
+                    h.copy_(t, non_blocking=True)
+                    t.record_stream(self._copy_stream)
+                ev = torch.cuda.Event()
+                ev.record(self._copy_stream)
+            pending.append((a0, na, host, ev, dev))
+            self._t["host_alloc_s"] += time.perf_counter() - t1
+
+        first, prev = 0, None
         with torch.cuda.device(self.device):
             for k in self._t:
                 self._t[k] = 0.0
             for dplan in self._device_plans(batch, params, False):
                 info = dplan.plan.info
+                n = info.n_alignments
                 t0 = time.perf_counter()
-                d_off, d_x, d_y, d_p = self.posteriors_device(model, dplan)
+                d_off = torch.empty(n + 1, dtype=torch.int64, device=self.device)
+                d_np = torch.empty(1, dtype=torch.int64, device=self.device)
+                capi.check(L.mab_posteriors_compute(model._h, dplan.plan._h, dplan.blob_ptr, dplan.ws_ptr,
+                                                    dplan.ws_bytes, d_off.data_ptr(), d_np.data_ptr(),
+                                                    self._stream_ptr()))
+                if prev is not None:
+                    start_copy(*prev)
                 t1 = time.perf_counter()
-                self._t["compute_s"] += t1 - t0
-                # pinned host blocks (torch's pinned allocator recycles them between calls); the D2H copies run on a
-                # second stream so they overlap the kernels of the next chunk
-                host = [torch.empty(t.shape, dtype=t.dtype, pin_memory=True) for t in (d_off, d_x, d_y, d_p)]
+                total = int(d_np.item())  # the sync: the output size is data dependent
+                d_x = torch.empty(total, dtype=torch.int32, device=self.device)
+                d_y = torch.empty(total, dtype=torch.int32, device=self.device)
+                d_p = torch.empty(total, dtype=torch.int32, device=self.device)
+                capi.check(L.mab_posteriors_emit(dplan.plan._h, dplan.blob_ptr, dplan.ws_ptr, dplan.ws_bytes,
+                                                 d_x.data_ptr(), d_y.data_ptr(), d_p.data_ptr(), total,
+                                                 self._stream_ptr()))
                 done = torch.cuda.Event()
                 done.record(torch.cuda.current_stream(self.device))
-                with torch.cuda.stream(self._copy_stream):
-                    self._copy_stream.wait_event(done)
-                    for h, t in zip(host, (d_off, d_x, d_y, d_p)):
-                        h.copy_(t, non_blocking=True)
-                        t.record_stream(self._copy_stream)
-                    ev = torch.cuda.Event()
-                    ev.record(self._copy_stream)
-                self._t["host_alloc_s"] += time.perf_counter() - t1
-                pending.append((first, info.n_alignments, host, ev, (d_off, d_x, d_y, d_p)))
-                first += info.n_alignments
+                self._t["compute_s"] += time.perf_counter() - t1
+                prev = (first, n, (d_off, d_x, d_y, d_p), done)
+                first += n
                 stats["cells"] += info.n_cells
                 stats["regions"] += info.n_regions
                 stats["diagonals"] += info.n_diagonals
                 stats["h2d_bytes"] += dplan.h2d_bytes
                 stats["chunks"] += 1
                 del dplan
+            if prev is not None:
+                start_copy(*prev)
             t_drain = time.perf_counter()
             for a0, na, host, ev, _keep in pending:
                 ev.synchronize()
@@ -720,8 +764,21 @@ class RealignedCigars:
     chain of aligned pairs when it was asked for."""
 
     def __init__(self, off_ops, ops, lens, chain_off=None, chain_x=None, chain_y=None):
-        self.off_ops, self.ops, self.lens = off_ops, ops, lens
-        self.chain_off, self.chain_x, self.chain_y = chain_off, chain_x, chain_y
+        # ops, lens, chain_x, chain_y: arrays, or lists of per-chunk arrays (pinned host blocks) that are joined the
+        # first time they are read -- the engine does not pay for a copy the caller may never need
+        self.off_ops, self.chain_off = off_ops, chain_off
+        self._v = dict(ops=ops, lens=lens, chain_x=chain_x, chain_y=chain_y)
+
+    def _get(self, k):
+        v = self._v[k]
+        if isinstance(v, list):
+            v = self._v[k] = np.concatenate(v) if len(v) > 1 else v[0]
+        return v
+
+    ops = property(lambda self: self._get("ops"))
+    lens = property(lambda self: self._get("lens"))
+    chain_x = property(lambda self: self._get("chain_x"))
+    chain_y = property(lambda self: self._get("chain_y"))
 
     @property
     def n(self):
@@ -758,11 +815,16 @@ def _realign_launch(engine, model, dplan, sub, expansion, gap_gamma, match_gamma
     dev = engine.device
     st = engine.posteriors_async(model, dplan)
     n = st["n"]
-    off_x = np.ascontiguousarray(sub.off_x, dtype=np.int64)
-    off_y = np.ascontiguousarray(sub.off_y, dtype=np.int64)
-    len_x, len_y = (int(off_x[-1]), int(off_y[-1])) if n else (0, 0)
-    h_offs = torch.from_numpy(np.stack([off_x, off_y])).pin_memory()
-    d_offs = h_offs.to(dev, non_blocking=True)
+    off_x, off_y = sub.off_x, sub.off_y
+    if getattr(dplan, "input_offsets", None) is not None:  # planned on the device: the offsets are already in HBM
+        ox_ptr, oy_ptr, len_x, len_y = dplan.input_offsets
+        h_offs = d_offs = None
+    else:
+        len_x, len_y = (int(off_x[-1]), int(off_y[-1])) if n else (0, 0)
+        h_offs = torch.from_numpy(np.stack([np.ascontiguousarray(off_x, dtype=np.int64),
+                                            np.ascontiguousarray(off_y, dtype=np.int64)])).pin_memory()
+        d_offs = h_offs.to(dev, non_blocking=True)
+        ox_ptr, oy_ptr = d_offs[0].data_ptr(), d_offs[1].data_ptr()
     # jitter stream: two draws per pair; an alignment has at most one pair per band cell
     est = int(((off_x[1:] - off_x[:-1]) + (off_y[1:] - off_y[:-1]) + 1).max() * (expansion + 4)) if n else 0
     table = jitter_table(min(2 * est + 2, 1 << 25))
@@ -776,7 +838,7 @@ def _realign_launch(engine, model, dplan, sub, expansion, gap_gamma, match_gamma
     ws_ptr = (d_ws.data_ptr() + 255) & ~255
     cap_ops = 2 * (len_x + len_y) + n + 1
     cap_chain = min(len_x, len_y) + 1
-    st.update(len_x=len_x, len_y=len_y, d_offs=d_offs, h_offs=h_offs, d_ws=d_ws, ws_ptr=ws_ptr, ws_bytes=ws_bytes,
+    st.update(len_x=len_x, len_y=len_y, d_offs=d_offs, h_offs=h_offs, ox_ptr=ox_ptr, oy_ptr=oy_ptr, d_ws=d_ws, ws_ptr=ws_ptr, ws_bytes=ws_bytes,
               d_op_off=torch.empty(n + 1, dtype=torch.int64, device=dev),
               d_ch_off=torch.empty(n + 1, dtype=torch.int64, device=dev),
               d_ops=torch.empty(cap_ops, dtype=torch.uint8, device=dev),
@@ -792,14 +854,14 @@ def _realign_launch(engine, model, dplan, sub, expansion, gap_gamma, match_gamma
 def _realign_kernels(engine, st):
     torch, L = engine.torch, capi.load()
     n, sp = st["n"], engine._stream_ptr()
-    ox, oy = st["d_offs"][0], st["d_offs"][1]
-    capi.check(L.mab_realign_chain(n, ox.data_ptr(), oy.data_ptr(), st["len_x"], st["len_y"], st["d_off"].data_ptr(),
+    ox, oy = st["ox_ptr"], st["oy_ptr"]
+    capi.check(L.mab_realign_chain(n, ox, oy, st["len_x"], st["len_y"], st["d_off"].data_ptr(),
                                    st["d_x"].data_ptr(), st["d_y"].data_ptr(), st["d_p"].data_ptr(), st["cap"],
                                    st["gammas"][0], st["gammas"][1], st["d_rand"].data_ptr(), st["d_rand"].numel(),
                                    st["ws_ptr"], st["ws_bytes"], st["d_op_off"].data_ptr(),
                                    st["d_ch_off"].data_ptr(), sp))
     wc = st["want_chain"]
-    capi.check(L.mab_realign_emit(n, ox.data_ptr(), oy.data_ptr(), st["len_x"], st["len_y"], st["cap"], st["ws_ptr"],
+    capi.check(L.mab_realign_emit(n, ox, oy, st["len_x"], st["len_y"], st["cap"], st["ws_ptr"],
                                   st["ws_bytes"], st["d_op_off"].data_ptr(), st["d_ch_off"].data_ptr(),
                                   st["d_ops"].data_ptr(), st["d_lens"].data_ptr(),
                                   st["d_cx"].data_ptr() if wc else None, st["d_cy"].data_ptr() if wc else None, sp))
@@ -845,13 +907,19 @@ def _engine_realign(self, model, batch, params=None, gap_gamma=0.5, match_gamma=
     stats = dict(cells=0, chunks=0, h2d_bytes=0, d2h_bytes=0, pairs=0)
     first, prev = 0, None
     with torch.cuda.device(self.device):
+        for k in self._t:
+            self._t[k] = 0.0
         for dplan in self._device_plans(batch, params, False):
             info = dplan.plan.info
             n = info.n_alignments
+            t0 = time.perf_counter()
             st = _realign_launch(self, model, dplan, batch.slice(first, first + n), params.diagonal_expansion, gap_gamma,
                                  match_gamma, want_chain)
+            t1 = time.perf_counter()
+            self._t["host_alloc_s"] += t1 - t0  # queueing a chunk: buffers + launches, no sync
             if prev is not None:
                 copies.append(_realign_finish(self, prev))
+            self._t["compute_s"] += time.perf_counter() - t1  # waiting for the previous chunk's kernels
             prev = st
             first += n
             stats["cells"] += info.n_cells
@@ -859,15 +927,20 @@ def _engine_realign(self, model, batch, params=None, gap_gamma=0.5, match_gamma=
             stats["h2d_bytes"] += dplan.h2d_bytes + 16 * (n + 1)
             del dplan, st
         if prev is not None:
+            t1 = time.perf_counter()
             copies.append(_realign_finish(self, prev))
+            self._t["compute_s"] += time.perf_counter() - t1
             prev = None
         parts = []
+        t_drain = time.perf_counter()
         for host, ev, st in copies:
             ev.synchronize()
             arrs = [h.numpy() for h in host]
             parts.append(arrs + [None] * (6 - len(arrs)))
             stats["pairs"] += st["total"]
             stats["d2h_bytes"] += sum(a.nbytes for a in arrs)
+        self._t["drain_s"] = time.perf_counter() - t_drain
+    stats["host_wall"] = dict(self._t)
     self.last_stats = stats
 
     def cat_off(idx):
@@ -877,8 +950,8 @@ def _engine_realign(self, model, batch, params=None, gap_gamma=0.5, match_gamma=
             base += int(p[idx][-1])
         return np.concatenate(out)
 
-    def cat(idx, dtype):
-        return np.concatenate([p[idx] for p in parts]) if parts else np.zeros(0, dtype=dtype)
+    def cat(idx, dtype):  # joined lazily by RealignedCigars
+        return [p[idx] for p in parts] if parts else np.zeros(0, dtype=dtype)
 
     if want_chain:
         return RealignedCigars(cat_off(0), cat(1, np.uint8), cat(2, np.int32), cat_off(3), cat(4, np.int32),
