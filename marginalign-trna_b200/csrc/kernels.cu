@@ -772,6 +772,7 @@ k_emit_diag(Blob bl, int64_t n_diagonals, const int32_t *__restrict__ pint, cons
 // read-modify-writes (lanes 0-15, then 16-31), so there is no atomic and no conflict.  One global atomic per bin per
 // warp at the very end.
 #define EXP_WARPS 4
+#define EXP_COLS 8     // bin columns per warp: lanes with the same (lane % EXP_COLS) take turns
 #define EXP_SEGMENT 4096  // cells per work item of k_expect
 
 template <int S>
@@ -801,8 +802,8 @@ struct TransTable<3> {  // stateMachine3 cellCalculate order (stateMachine.c:636
     }
 };
 
-template <int S>
-__global__ void __launch_bounds__(EXP_WARPS * 32)
+template <int S, int NB>
+__global__ void __launch_bounds__(EXP_WARPS * 32, NB)
 k_expect(const __grid_constant__ DevModel model, Blob bl, int64_t n_cells, int64_t n_diagonals,
          const double *__restrict__ F, const double *__restrict__ B, const double *__restrict__ totals,
          double *__restrict__ out, int *counter) {
@@ -810,14 +811,14 @@ k_expect(const __grid_constant__ DevModel model, Blob bl, int64_t n_cells, int64
     constexpr int NT = TT::N, NL = TT::NL, NM = TT::NM;
     constexpr int NE = S * 16, NOUT = S * S + NE + 1;
     __shared__ DevModel sm;
-    __shared__ double bins_all[EXP_WARPS][NE][16];
+    __shared__ double bins_all[EXP_WARPS][NE][EXP_COLS];
     for (int i = threadIdx.x; i < (int) (sizeof(DevModel) / 4); i += blockDim.x)
         ((int32_t *) &sm)[i] = ((const int32_t *) &model)[i];
-    for (int i = threadIdx.x; i < EXP_WARPS * NE * 16; i += blockDim.x) (&bins_all[0][0][0])[i] = 0.0;
+    for (int i = threadIdx.x; i < EXP_WARPS * NE * EXP_COLS; i += blockDim.x) (&bins_all[0][0][0])[i] = 0.0;
     __syncthreads();
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    double(*bins)[16] = bins_all[warp];
-    const int col = lane & 15;
+    double(*bins)[EXP_COLS] = bins_all[warp];
+    const int col = lane & (EXP_COLS - 1);
     const double NINF = neg_inf();
     double tacc[NT];
 #pragma unroll
@@ -915,17 +916,15 @@ k_expect(const __grid_constant__ DevModel model, Blob bl, int64_t n_cells, int64
                     e_to[TT::to(k)] += p;
                 }
             }
-            // emission bins: lanes 0-15 first, then 16-31 on the same columns
-            if (row >= 0 && lane < 16) {
+            // emission bins: the lanes that share a column take turns (conflict-free: one lane per column per turn)
 #pragma unroll
-                for (int s = 0; s < S; s++) bins[s * 16 + row][col] += e_to[s];
-            }
-            __syncwarp();
-            if (row >= 0 && lane >= 16) {
+            for (int q = 0; q < 32 / EXP_COLS; q++) {
+                if (row >= 0 && lane / EXP_COLS == q) {
 #pragma unroll
-                for (int s = 0; s < S; s++) bins[s * 16 + row][col] += e_to[s];
+                    for (int s = 0; s < S; s++) bins[s * 16 + row][col] += e_to[s];
+                }
+                __syncwarp();
             }
-            __syncwarp();
         }
         if (c0 >= region_end) c0 = region_end;  // region finished: go on with the next one (else the segment ended)
         }
@@ -945,7 +944,7 @@ k_expect(const __grid_constant__ DevModel model, Blob bl, int64_t n_cells, int64
     for (int i = lane; i < NE; i += 32) {
         double v = 0.0;
 #pragma unroll
-        for (int q = 0; q < 16; q++) v += bins[i][q];
+        for (int q = 0; q < EXP_COLS; q++) v += bins[i][q];
         if (v != 0.0) atomicAdd(&out[S * S + i], v);
     }
 }
@@ -1204,8 +1203,11 @@ int run_expectations(const DevModel &dm, const mab_plan *plan, const void *d_blo
     {
         LaunchTimer lt(K_EXPECT, st);
         const int64_t n_segments = (h.n_cells + EXP_SEGMENT - 1) / EXP_SEGMENT;
-        k_expect<S><<<grid_for(n_segments, 4, EXP_WARPS), EXP_WARPS * 32, 0, st>>>(dm, bl, h.n_cells, h.n_diagonals, w.fwd,
-                                                                                 w.bwd, w.totals, d_out, w.counters + 4);
+        // resident blocks per SM (= the register budget the kernel is compiled for): measured on 300 k tRNA reads, 4 / 5 / 6
+        // blocks give 38.4 / 37.9 / 40.4 ms for S = 5 (10 kb reads: 80.9 / 83.0 / 89.6) and 30.5 / 27.5 / 28.8 ms for S = 3
+        constexpr int NB = S == 3 ? 5 : 4;
+        k_expect<S, NB><<<grid_for(n_segments, NB, EXP_WARPS), EXP_WARPS * 32, 0, st>>>(
+            dm, bl, h.n_cells, h.n_diagonals, w.fwd, w.bwd, w.totals, d_out, w.counters + 4);
     }
     return check(cudaGetLastError(), "expectation launch");
 }
