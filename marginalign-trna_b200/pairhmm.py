@@ -410,7 +410,7 @@ class PairHmmEngine:
     PLAN_AHEAD = int(os.environ.get("MAB_PLAN_AHEAD", "2"))  # chunks planned ahead of the one computing
     BASE_CELLS = int(os.environ.get("MAB_BASE_CELLS", "400000000"))  # chunk size that pipelines well for short reads (tRNA: ~140 k alignments per chunk)
 
-    def _auto_max_cells(self, est, params, expectations):
+    def _auto_max_cells(self, mean_est, params, expectations):
         """Chunk size when the caller gave none.  The forward sweep of one region is sequential over its diagonals, so
         a chunk must hold enough regions to fill the GPU (~6000 resident warps / the warps one region gets, see
         wave_launch in csrc/kernels.cu): a few hundred 10 kb reads per chunk would leave the forward kernel
@@ -420,7 +420,7 @@ class PairHmmEngine:
         mem_cap = min(int(0.55 * free / (170 if expectations else 40)), 2_000_000_000)  # 32-bit side offsets
         group = min(8, max(1, -(-(params.diagonal_expansion + 2) // 16)))
         want_alignments = 6144 // group
-        target = int(float(est.mean()) * want_alignments) if len(est) else 0
+        target = int(mean_est * want_alignments)
         return max(min(max(self.BASE_CELLS, target), mem_cap), 1), want_alignments
 
     def _chunks(self, batch, params, expectations=False):
@@ -428,19 +428,24 @@ class PairHmmEngine:
         exact count comes from the plan)."""
         if batch.n == 0:
             return [(0, 0)]
-        est = ((batch.off_x[1:] - batch.off_x[:-1]) + (batch.off_y[1:] - batch.off_y[:-1]) + 1) * (
-            params.diagonal_expansion + 4)
+        # estimate per alignment: (lX + lY + 1) (expansion + 4); its running sum telescopes over the offsets, so it is
+        # built without the per-alignment array (this runs before any GPU work can start: 1 M reads, 14 -> 5 ms)
+        cum = np.asarray(batch.off_x[1:], dtype=np.int64) + batch.off_y[1:]
+        cum += np.arange(1, batch.n + 1, dtype=np.int64)
+        cum -= int(batch.off_x[0]) + int(batch.off_y[0])
+        cum *= params.diagonal_expansion + 4
+        mean_est = float(cum[-1]) / batch.n
         if self.max_cells:
             max_cells, want_alignments = self.max_cells, 0
         else:
-            max_cells, want_alignments = self._auto_max_cells(est, params, expectations)
-        cum = np.cumsum(est.astype(np.int64))
+            max_cells, want_alignments = self._auto_max_cells(mean_est, params, expectations)
         bounds, start, base = [], 0, 0
         # the first chunk is a quarter of the others: nothing overlaps its packing, upload and planning, so the
         # pipeline (helper thread plans chunk k+1 while chunk k computes) should fill quickly -- unless a quarter
         # chunk would hold too few alignments to fill the GPU
         limit = max(max_cells // 4, 1)
-        if want_alignments and limit < float(est.mean()) * want_alignments:
+        quarter_ok = not (want_alignments and limit < mean_est * want_alignments)
+        if not quarter_ok:
             limit = max_cells
         while start < batch.n:
             end = int(np.searchsorted(cum, base + limit, side="right"))
@@ -449,6 +454,15 @@ class PairHmmEngine:
             start = bounds[-1][1]
             base = int(cum[start - 1])
             limit = max_cells
+        # ... and so is the last one where results go back to the host (posterior mode): nothing overlaps the D2H copy
+        # of its pairs
+        if quarter_ok and not expectations and len(bounds) >= 3:
+            a, b = bounds[-1]
+            first_cell = int(cum[a - 1])
+            if int(cum[b - 1]) - first_cell > max_cells // 2:
+                mid = int(np.searchsorted(cum, int(cum[b - 1]) - max_cells // 4, side="right"))
+                if a < mid < b:
+                    bounds[-1:] = [(a, mid), (mid, b)]
         return bounds
 
     def _stream_ptr(self):
@@ -531,7 +545,7 @@ class PairHmmEngine:
         have been queued, so the GPU does not wait for it."""
         params = params or AlignmentParameters()
         torch, L = self.torch, capi.load()
-        offs, blocks = [np.zeros(1, dtype=np.int64)], []
+        offsets, blocks = np.zeros(batch.n + 1, dtype=np.int64), []
         stats = dict(cells=0, regions=0, diagonals=0, h2d_bytes=0, d2h_bytes=0, chunks=0)
         pending = []  # D2H copies in flight: (first alignment, n alignments, pinned tensors, event, device tensors)
 
@@ -590,8 +604,8 @@ class PairHmmEngine:
             for a0, na, host, ev, _keep in pending:
                 ev.synchronize()
                 off = host[0].numpy()
-                base = int(offs[-1][-1])
-                offs.append(off[1:] + base)
+                base = int(offsets[a0])
+                np.add(off[1:], base, out=offsets[a0 + 1:a0 + na + 1])
                 blocks.append((a0, a0 + na, base, host[1].numpy(), host[2].numpy(), host[3].numpy()))
                 stats["d2h_bytes"] += sum(h.numel() * h.element_size() for h in host)
             self._t["drain_s"] = time.perf_counter() - t_drain
@@ -599,7 +613,7 @@ class PairHmmEngine:
         if not blocks:
             blocks = [(0, 0, 0, np.zeros(0, np.int32), np.zeros(0, np.int32), np.zeros(0, np.int32))]
         self.last_stats = stats
-        return PosteriorPairs(np.concatenate(offs), blocks=blocks)
+        return PosteriorPairs(offsets, blocks=blocks)
 
     PAIRS_PER_CELL_CAP = float(os.environ.get("MAB_PAIR_CAP", "0.25"))  # output capacity of the sync-free path (measured: 0.07 pairs per cell at threshold 0.01)
 

@@ -144,3 +144,32 @@ def test_no_cpu_fallback_without_gpu():
     plan = mab.Plan.from_anchors(["ACGT"], ["ACGT"], [[]], mab.AlignmentParameters())
     rc = L.mab_posteriors_compute(m._h, plan._h, 1, 256, 1 << 30, 8, 8, None)
     assert rc == -5 and b"no CPU fallback" in L.mab_last_error()
+
+
+def test_chunker_tiles_the_batch_in_order():
+    """PairHmmEngine._chunks is host logic: ranges tile [0, n) in order, the first and (posterior mode) the last chunk
+    are short so the pipeline fills and drains quickly, and no chunk exceeds the cell budget by more than one read."""
+    from marginalign_trna_b200 import synth
+    from marginalign_trna_b200.pairhmm import PairHmmEngine
+    batch = synth.trna_batch(3000, seed=5) if hasattr(synth, "trna_batch") else None
+    if batch is None:
+        rng = np.random.default_rng(5)
+        xs = ["".join(rng.choice(list("ACGT"), int(n))) for n in rng.integers(70, 150, 3000)]
+        batch = mab.AlignmentBatch.from_lists(xs, xs, [([0], [len(x)]) for x in xs])
+    eng = object.__new__(PairHmmEngine)  # no GPU: only the chunker is exercised
+    P = mab.AlignmentParameters(diagonal_expansion=10)
+    est = ((batch.off_x[1:] - batch.off_x[:-1]) + (batch.off_y[1:] - batch.off_y[:-1]) + 1) * 14
+    for budget in (50_000, 400_000, 10 ** 9):
+        eng.max_cells = budget
+        for expectations in (False, True):
+            bounds = eng._chunks(batch, P, expectations)
+            assert bounds[0][0] == 0 and bounds[-1][1] == batch.n
+            assert all(a < b for a, b in bounds) and all(bounds[i][1] == bounds[i + 1][0] for i in range(len(bounds) - 1))
+            sizes = [int(est[a:b].sum()) for a, b in bounds]
+            assert all(s <= budget + int(est.max()) for s in sizes)
+            if len(bounds) >= 4:
+                assert sizes[0] <= budget // 4 + int(est.max())
+                if not expectations:
+                    assert sizes[-1] <= budget // 2 + int(est.max())
+    eng.max_cells = 1000
+    assert eng._chunks(mab.AlignmentBatch.from_lists([], [], []), P) == [(0, 0)]
