@@ -407,6 +407,7 @@ class PairHmmEngine:
         self._t_lock = threading.Lock()
 
     # ---------------------------------------------------------------- chunking
+    CHUNK_RAMP = tuple(int(d) for d in os.environ.get("MAB_CHUNK_RAMP", "4").split(",") if d)  # see _chunks
     PLAN_AHEAD = int(os.environ.get("MAB_PLAN_AHEAD", "2"))  # chunks planned ahead of the one computing
     BASE_CELLS = int(os.environ.get("MAB_BASE_CELLS", "400000000"))  # chunk size that pipelines well for short reads (tRNA: ~140 k alignments per chunk)
 
@@ -440,20 +441,19 @@ class PairHmmEngine:
         else:
             max_cells, want_alignments = self._auto_max_cells(mean_est, params, expectations)
         bounds, start, base = [], 0, 0
-        # the first chunk is a quarter of the others: nothing overlaps its packing, upload and planning, so the
-        # pipeline (helper thread plans chunk k+1 while chunk k computes) should fill quickly -- unless a quarter
-        # chunk would hold too few alignments to fill the GPU
-        limit = max(max_cells // 4, 1)
-        quarter_ok = not (want_alignments and limit < mean_est * want_alignments)
-        if not quarter_ok:
-            limit = max_cells
+        # the first chunk is a quarter of the others: nothing overlaps its packing, upload and planning, so the pipeline
+        # should fill quickly -- unless such a chunk would hold too few alignments to fill the GPU.  (CHUNK_RAMP can
+        # ask for a longer ramp, e.g. 8,4,2; measured equal on 1 M tRNA reads: 190 vs 186 ms.)
+        ramp = [max(max_cells // d, 1) for d in self.CHUNK_RAMP]
+        ramp = [r for r in ramp if not (want_alignments and r < mean_est * want_alignments)]
+        quarter_ok = any(r <= max(max_cells // 4, 1) for r in ramp)
         while start < batch.n:
+            limit = ramp.pop(0) if ramp else max_cells
             end = int(np.searchsorted(cum, base + limit, side="right"))
             end = max(end, start + 1)
             bounds.append((start, min(end, batch.n)))
             start = bounds[-1][1]
             base = int(cum[start - 1])
-            limit = max_cells
         # ... and so is the last one where results go back to the host (posterior mode): nothing overlaps the D2H copy
         # of its pairs
         if quarter_ok and not expectations and len(bounds) >= 3:
