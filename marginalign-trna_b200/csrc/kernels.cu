@@ -772,6 +772,7 @@ k_emit_diag(Blob bl, int64_t n_diagonals, const int32_t *__restrict__ pint, cons
 // read-modify-writes (lanes 0-15, then 16-31), so there is no atomic and no conflict.  One global atomic per bin per
 // warp at the very end.
 #define EXP_WARPS 4
+#define EXP_NB 5
 #define EXP_COLS 8     // bin columns per warp: lanes with the same (lane % EXP_COLS) take turns
 #define EXP_SEGMENT 4096  // cells per work item of k_expect
 
@@ -802,6 +803,31 @@ struct TransTable<3> {  // stateMachine3 cellCalculate order (stateMachine.c:636
     }
 };
 
+// exp(x) for the expectation kernel: x = log of a posterior transition probability (<= ~0).  Table-driven
+// (exp(x) = 2^k 2^(j/64) e^r, |r| <= ln2/128, degree-5 polynomial; max relative error 2.2e-16 against libm over
+// [-700, 1], checked on the host): 10 FP64 operations in a dependent chain of 9 instead of the ~20 of the library
+// routine, which is what k_expect waits on.  Below -700 (and for -inf) the result is 0: such terms cannot change a sum
+// of probabilities.  The expectation sums are not bit-exact quantities (their order differs from the reference's
+// anyway); the posterior kernel, whose p_int must match bit for bit, keeps the library exp.
+__device__ __forceinline__ double exp_tab(double x, const double *__restrict__ pow2_64) {
+    const double INV = 0x1.71547652b82fep+6, C1 = 0x1.62e42fe000000p-7, C2 = 0x1.f473de6af278fp-36;  // 64/ln2, ln2/64 hi + lo
+    const double MAGIC = 6755399441055744.0;  // 1.5 * 2^52: the integer lands in the low word
+    const double t = __fma_rn(x, INV, MAGIC);
+    const int n = __double2loint(t);
+    const double tn = __dsub_rn(t, MAGIC);
+    double r = __fma_rn(tn, -C1, x);
+    r = __fma_rn(tn, -C2, r);
+    double q = __fma_rn(r, 1.0 / 120, 1.0 / 24);
+    q = __fma_rn(q, r, 1.0 / 6);
+    q = __fma_rn(q, r, 0.5);
+    q = __fma_rn(q, r, 1.0);
+    const double p = __dmul_rn(q, r);
+    const double tj = pow2_64[n & 63];
+    const double res = __fma_rn(tj, p, tj);
+    const double scaled = __hiloint2double(__double2hiint(res) + ((n >> 6) << 20), __double2loint(res));
+    return x < -700.0 ? 0.0 : scaled;
+}
+
 template <int S, int NB>
 __global__ void __launch_bounds__(EXP_WARPS * 32, NB)
 k_expect(const __grid_constant__ DevModel model, Blob bl, int64_t n_cells, int64_t n_diagonals,
@@ -812,6 +838,8 @@ k_expect(const __grid_constant__ DevModel model, Blob bl, int64_t n_cells, int64
     constexpr int NE = S * 16, NOUT = S * S + NE + 1;
     __shared__ DevModel sm;
     __shared__ double bins_all[EXP_WARPS][NE][EXP_COLS];
+    __shared__ double pow2_64[64];
+    if (threadIdx.x < 64) pow2_64[threadIdx.x] = exp2((double) threadIdx.x / 64.0);
     for (int i = threadIdx.x; i < (int) (sizeof(DevModel) / 4); i += blockDim.x)
         ((int32_t *) &sm)[i] = ((const int32_t *) &model)[i];
     for (int i = threadIdx.x; i < EXP_WARPS * NE * EXP_COLS; i += blockDim.x) (&bins_all[0][0][0])[i] = 0.0;
@@ -911,7 +939,7 @@ k_expect(const __grid_constant__ DevModel model, Blob bl, int64_t n_cells, int64
                     const double f = k < NL ? lo.v[TT::from(k)] : (k < NL + NM ? mi.v[TT::from(k)] : up.v[TT::from(k)]);
                     const double e = k < NL ? eL[k] : (k < NL + NM ? eM[k - NL] : eU[k - NL - NM]);
                     // exp(fromCells[from] + toCells[to] + (eP + tP) - totalProbability), left to right (:356)
-                    const double p = exp(__dsub_rn(__dadd_rn(__dadd_rn(f, b.v[TT::to(k)]), e), total));
+                    const double p = exp_tab(__dsub_rn(__dadd_rn(__dadd_rn(f, b.v[TT::to(k)]), e), total), pow2_64);
                     tacc[k] += p;
                     e_to[TT::to(k)] += p;
                 }
@@ -1205,7 +1233,9 @@ int run_expectations(const DevModel &dm, const mab_plan *plan, const void *d_blo
         const int64_t n_segments = (h.n_cells + EXP_SEGMENT - 1) / EXP_SEGMENT;
         // resident blocks per SM (= the register budget the kernel is compiled for): measured on 300 k tRNA reads, 4 / 5 / 6
         // blocks give 38.4 / 37.9 / 40.4 ms for S = 5 (10 kb reads: 80.9 / 83.0 / 89.6) and 30.5 / 27.5 / 28.8 ms for S = 3
-        constexpr int NB = S == 3 ? 5 : 4;
+        // resident blocks per SM (= the register budget the kernel is compiled for).  Measured with the table-driven exp
+        // on 300 k tRNA reads: 4 / 5 blocks = 29.2 / 26.5 ms (S = 5), 24.7 / 23.2 ms (S = 3); 10 kb reads 67.4 / 63.1 ms
+        constexpr int NB = EXP_NB;
         k_expect<S, NB><<<grid_for(n_segments, NB, EXP_WARPS), EXP_WARPS * 32, 0, st>>>(
             dm, bl, h.n_cells, h.n_diagonals, w.fwd, w.bwd, w.totals, d_out, w.counters + 4);
     }
