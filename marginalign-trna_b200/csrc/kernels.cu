@@ -805,7 +805,7 @@ struct TransTable<3> {  // stateMachine3 cellCalculate order (stateMachine.c:636
 
 // exp(x) for the expectation kernel: x = log of a posterior transition probability (<= ~0).  Table-driven
 // (exp(x) = 2^k 2^(j/64) e^r, |r| <= ln2/128, degree-5 polynomial; max relative error 2.2e-16 against libm over
-// [-700, 1], checked on the host): 10 FP64 operations in a dependent chain of 9 instead of the ~20 of the library
+// [-700, 1], tools/exp_tab_check.c): 10 FP64 operations in a dependent chain of 9 instead of the ~20 of the library
 // routine, which is what k_expect waits on.  Below -700 (and for -inf) the result is 0: such terms cannot change a sum
 // of probabilities.  The expectation sums are not bit-exact quantities (their order differs from the reference's
 // anyway); the posterior kernel, whose p_int must match bit for bit, keeps the library exp.
