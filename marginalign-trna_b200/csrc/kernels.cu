@@ -772,7 +772,6 @@ k_emit_diag(Blob bl, int64_t n_diagonals, const int32_t *__restrict__ pint, cons
 // read-modify-writes (lanes 0-15, then 16-31), so there is no atomic and no conflict.  One global atomic per bin per
 // warp at the very end.
 #define EXP_WARPS 4
-#define EXP_NB 5
 #define EXP_COLS 8     // bin columns per warp: lanes with the same (lane % EXP_COLS) take turns
 #define EXP_SEGMENT 4096  // cells per work item of k_expect
 
@@ -1234,8 +1233,9 @@ int run_expectations(const DevModel &dm, const mab_plan *plan, const void *d_blo
         // resident blocks per SM (= the register budget the kernel is compiled for): measured on 300 k tRNA reads, 4 / 5 / 6
         // blocks give 38.4 / 37.9 / 40.4 ms for S = 5 (10 kb reads: 80.9 / 83.0 / 89.6) and 30.5 / 27.5 / 28.8 ms for S = 3
         // resident blocks per SM (= the register budget the kernel is compiled for).  Measured with the table-driven exp
-        // on 300 k tRNA reads: 4 / 5 blocks = 29.2 / 26.5 ms (S = 5), 24.7 / 23.2 ms (S = 3); 10 kb reads 67.4 / 63.1 ms
-        constexpr int NB = EXP_NB;
+        // on 300 k tRNA reads, 4 / 5 / 6 blocks: S = 5: 29.2 / 26.5 / 27.1 ms (10 kb reads 67.4 / 63.1 / 65.0), S = 3:
+        // 24.7 / 23.2 / 18.5 ms (80 registers without spills)
+        constexpr int NB = S == 3 ? 6 : 5;
         k_expect<S, NB><<<grid_for(n_segments, NB, EXP_WARPS), EXP_WARPS * 32, 0, st>>>(
             dm, bl, h.n_cells, h.n_diagonals, w.fwd, w.bwd, w.totals, d_out, w.counters + 4);
     }
