@@ -213,6 +213,10 @@ int mab_debug_copy_matrices(const mab_plan *plan, const void *d_ws, double *h_fw
 /* Debug/test hook: warps that share one 5-state work item (region / traceback) in the wavefront kernels.
  * 0 = chosen from the mean band width (default), 1, 2, 4 or 8 = forced.  Results do not depend on it. */
 int mab_debug_set_warp_group(int warps);
+/* Debug/test hook: work items are dispatched by band class (0: a half-warp per item, 1: a warp per item, both on the
+ * register-resident wavefront kernels; 2: wide bands on the shared-memory-ring kernels).  cls = 1 runs class-0 items as
+ * class 1, cls = 2 runs everything as class 2; 0 restores the default.  Results do not depend on it. */
+int mab_debug_set_min_band_class(int cls);
 /* Kernel launches issued by this library on the calling thread since the last reset (bench.py's gpu_launches). */
 int64_t mab_launch_count(int reset);
 /* Per-kernel timing for the roofline report: when enabled every launch is bracketed by CUDA events on its stream.

@@ -364,6 +364,8 @@ __device__ __forceinline__ Cell<S> backward_cell_sel(const Cell<S> &nMi, const C
     else return backward_cell5_bf(nMi, nUp, nLo, eM, eU, eL, cf);
 }
 
+#include "wavefront_reg.cuh"
+
 template <int S, bool FULL, int LPI>
 __global__ void __launch_bounds__(THREADS_PER_BLOCK)
 k_forward(const __grid_constant__ DevModel model, Blob bl, int n_regions, double *__restrict__ F,
@@ -1105,80 +1107,112 @@ WaveLaunch wave_launch(int S, int64_t items, const BlobHeader &h) {
     return best;
 }
 
-// forward + backward + totals: shared by posterior mode (FULL = false) and expectation mode (FULL = true)
+// test hook (mab_debug_set_min_band_class): 1 runs class-0 items on the warp-per-item kernel, 2 everything on the
+// shared-memory-ring kernels; results must not depend on it
+int g_min_band_class = 0;
+
+// register-resident kernels (wavefront_reg.cuh): resident blocks per SM from the occupancy calculator, once per kernel
+template <typename K>
+int rr_grid(K kernel, int64_t items, int items_per_block) {
+    static thread_local int blocks_per_sm = 0;
+    if (blocks_per_sm == 0) {
+        if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&blocks_per_sm, kernel, RR_THREADS, 0) != cudaSuccess ||
+            blocks_per_sm < 1)
+            blocks_per_sm = 1;
+    }
+    const int64_t want = (items + items_per_block - 1) / items_per_block;
+    const int64_t cap = (int64_t) device_info().sm_count * blocks_per_sm;
+    return (int) std::max<int64_t>(1, std::min(want, cap));
+}
+
+// forward + backward + totals: shared by posterior mode (FULL = false) and expectation mode (FULL = true).
+// The order arrays list the work items by band class (mab_internal.h): class 2 (wide bands) first -- they run on the
+// shared-memory-ring kernels, G warps per item -- then class 1 (a warp per item) and class 0 (a half-warp per item) on
+// the register-resident kernels.
 template <int S, bool FULL>
 int run_dp(const DevModel &dm, const mab_plan *plan, const Blob &bl, const Workspace &w, cudaStream_t st) {
     const BlobHeader &h = plan->hdr;
-    const DeviceInfo &di = device_info();
-    // shared-memory ring per work item: 3 diagonals x (max_width + 2 guard) cells x S doubles.  The 5-state kernels
-    // also hold ~27 KB of replicated tables per block and may give one item to G warps (wave_launch).
-    // 5-state: narrow bands (mean width <= 16: tRNA, any read at expansion 10) run on the one-lane-per-cell kernels with
-    // a half-warp per item -- measured faster than the pair-lane kernels of wavefront5.cuh there (fewer instructions
-    // per diagonal, the shared-memory pipe binds both) -- wide bands on the pair-lane kernels with warp groups.
-    // MAB_W5=1 forces the pair-lane kernels, MAB_W5=0 the one-lane kernels.
-    static const int w5_env = getenv("MAB_W5") ? atoi(getenv("MAB_W5")) : -1;
-    const bool narrow = h.n_cells <= 16 * h.n_diagonals;
-    const bool wave5 = S == 5 && (w5_env == 1 || (w5_env != 0 && !narrow) || g_w5_group > 0);
-    const WaveLaunch lf = wave5 ? wave_launch(S, h.n_regions, h) : wave_launch_for(S, 1, h, false),
-                     lb = wave5 ? wave_launch(S, h.n_tracebacks, h) : wave_launch_for(S, 1, h, false);
-    if (lf.warps < 1 || lb.warps < 1) {
-        mab_set_error("band too wide for the shared-memory ring (max width %lld cells); lower diagonalExpansion or "
-                      "splitMatrixBiggerThanThis", (long long) h.max_width);
+    int nR2 = (int) h.n_class_regions[2], nR1 = (int) h.n_class_regions[1], nR0 = (int) h.n_class_regions[0];
+    int nT2 = (int) h.n_class_tbs[2], nT1 = (int) h.n_class_tbs[1], nT0 = (int) h.n_class_tbs[0];
+    if (g_min_band_class >= 1) nR1 += nR0, nT1 += nT0, nR0 = nT0 = 0;
+    if (g_min_band_class >= 2) nR2 += nR1, nT2 += nT1, nR1 = nT1 = 0;
+    if ((int64_t) nR2 + nR1 + nR0 != h.n_regions || (int64_t) nT2 + nT1 + nT0 != h.n_tracebacks) {
+        mab_set_error("plan header: band classes do not add up (%d + %d + %d regions of %lld)", nR2, nR1, nR0,
+                      (long long) h.n_regions);
         return MAB_E_ARG;
     }
-    const int ring_w = (int) h.max_width;
     int rc;
     if ((rc = check(cudaMemsetAsync(w.counters, 0, 256, st), "memset counters"))) return rc;
-    if (wave5) {
-        // where the logAdd coefficients are fetched from (wavefront5.cuh): smem (default, fastest measured) |
-        // mixed | const -- kept switchable for profiling (single-warp items only)
-        static const int cm = [] {
-            const char *e = getenv("MAB_COEF");
-            if (e && !strcmp(e, "const")) return (int) COEF_CONST;
-            if (e && !strcmp(e, "mixed")) return (int) COEF_MIXED;
-            return (int) COEF_SMEM;
-        }();
-        auto kf = k_forward5<FULL, COEF_SMEM, 1>;
-        auto kb = k_backward5<FULL, COEF_SMEM, 1>;
-        if (lf.G == 1 && cm == COEF_CONST) kf = k_forward5<FULL, COEF_CONST, 1>;
-        if (lf.G == 1 && cm == COEF_MIXED) kf = k_forward5<FULL, COEF_MIXED, 1>;
-        if (lb.G == 1 && cm == COEF_CONST) kb = k_backward5<FULL, COEF_CONST, 1>;
-        if (lb.G == 1 && cm == COEF_MIXED) kb = k_backward5<FULL, COEF_MIXED, 1>;
-        if (lf.G == 2) kf = k_forward5<FULL, COEF_SMEM, 2>;
-        if (lf.G == 4) kf = k_forward5<FULL, COEF_SMEM, 4>;
-        if (lf.G == 8) kf = k_forward5<FULL, COEF_SMEM, 8>;
-        if (lb.G == 2) kb = k_backward5<FULL, COEF_SMEM, 2>;
-        if (lb.G == 4) kb = k_backward5<FULL, COEF_SMEM, 4>;
-        if (lb.G == 8) kb = k_backward5<FULL, COEF_SMEM, 8>;
-        if ((rc = allow_smem(kf, lf.ring_bytes)) || (rc = allow_smem(kb, lb.ring_bytes))) return rc;
-        {
-            LaunchTimer lt(K_FORWARD, st);
-            kf<<<grid_for(h.n_regions, lf.blocks_per_sm, lf.groups), lf.warps * 32, lf.ring_bytes, st>>>(
-                dm, bl, (int) h.n_regions, w.fwd, w.fwd_tot, w.counters + 0, ring_w);
+    if (nR2 > 0) {
+        // shared-memory ring per work item: 3 diagonals x (max_width + 2 guard) cells x S doubles.  The 5-state kernels
+        // also hold ~27 KB of replicated tables per block and may give one item to G warps (wave_launch).
+        const bool wave5 = S == 5;
+        const WaveLaunch lf = wave5 ? wave_launch(S, nR2, h) : wave_launch_for(S, 1, h, false),
+                         lb = wave5 ? wave_launch(S, nT2, h) : wave_launch_for(S, 1, h, false);
+        if (lf.warps < 1 || lb.warps < 1) {
+            mab_set_error("band too wide for the shared-memory ring (max width %lld cells); lower diagonalExpansion or "
+                          "splitMatrixBiggerThanThis", (long long) h.max_width);
+            return MAB_E_ARG;
         }
-        {
-            LaunchTimer lt(K_BACKWARD, st);
-            kb<<<grid_for(h.n_tracebacks, lb.blocks_per_sm, lb.groups), lb.warps * 32, lb.ring_bytes, st>>>(
-                dm, bl, (int) h.n_tracebacks, w.bwd, w.bwd_tot, w.edge, w.counters + 1, ring_w);
+        const int ring_w = (int) h.max_width;
+        if constexpr (S == 5) {
+            auto kf = k_forward5<FULL, COEF_SMEM, 1>;
+            auto kb = k_backward5<FULL, COEF_SMEM, 1>;
+            if (lf.G == 2) kf = k_forward5<FULL, COEF_SMEM, 2>;
+            if (lf.G == 4) kf = k_forward5<FULL, COEF_SMEM, 4>;
+            if (lf.G == 8) kf = k_forward5<FULL, COEF_SMEM, 8>;
+            if (lb.G == 2) kb = k_backward5<FULL, COEF_SMEM, 2>;
+            if (lb.G == 4) kb = k_backward5<FULL, COEF_SMEM, 4>;
+            if (lb.G == 8) kb = k_backward5<FULL, COEF_SMEM, 8>;
+            if ((rc = allow_smem(kf, lf.ring_bytes)) || (rc = allow_smem(kb, lb.ring_bytes))) return rc;
+            {
+                LaunchTimer lt(K_FORWARD, st);
+                kf<<<grid_for(nR2, lf.blocks_per_sm, lf.groups), lf.warps * 32, lf.ring_bytes, st>>>(
+                    dm, bl, nR2, w.fwd, w.fwd_tot, w.counters + 0, ring_w);
+            }
+            {
+                LaunchTimer lt(K_BACKWARD, st);
+                kb<<<grid_for(nT2, lb.blocks_per_sm, lb.groups), lb.warps * 32, lb.ring_bytes, st>>>(
+                    dm, bl, nT2, w.bwd, w.bwd_tot, w.edge, w.counters + 1, ring_w);
+            }
+        } else {
+            auto kf = k_forward<S, FULL, 32>;
+            auto kb = k_backward<S, FULL, 32>;
+            if ((rc = allow_smem(kf, lf.ring_bytes)) || (rc = allow_smem(kb, lb.ring_bytes))) return rc;
+            {
+                LaunchTimer lt(K_FORWARD, st);
+                kf<<<grid_for(nR2, lf.blocks_per_sm, lf.warps), lf.warps * 32, lf.ring_bytes, st>>>(
+                    dm, bl, nR2, w.fwd, w.fwd_tot, w.counters + 0, ring_w);
+            }
+            {
+                LaunchTimer lt(K_BACKWARD, st);
+                kb<<<grid_for(nT2, lb.blocks_per_sm, lb.warps), lb.warps * 32, lb.ring_bytes, st>>>(
+                    dm, bl, nT2, w.bwd, w.bwd_tot, w.edge, w.counters + 1, ring_w);
+            }
         }
-    } else {
-        // generic kernels (3-state): one lane per cell; a half-warp per item when the band fits 16 lanes (tRNA), so
-        // that both halves of a warp work (measured: 3-state tRNA forward 127 -> see profiles/r1_ncu_summary.md r1h)
-        const bool half = h.n_cells <= 16 * h.n_diagonals;  // mean band width; wider diagonals take several passes
-        const int ipw = half ? 2 : 1;  // items per warp
-        auto kf = half ? k_forward<S, FULL, 16> : k_forward<S, FULL, 32>;
-        auto kb = half ? k_backward<S, FULL, 16> : k_backward<S, FULL, 32>;
-        if ((rc = allow_smem(kf, lf.ring_bytes * ipw)) || (rc = allow_smem(kb, lb.ring_bytes * ipw))) return rc;
-        {
-            LaunchTimer lt(K_FORWARD, st);
-            kf<<<grid_for(h.n_regions, lf.blocks_per_sm, lf.warps * ipw), lf.warps * 32, lf.ring_bytes * ipw, st>>>(
-                dm, bl, (int) h.n_regions, w.fwd, w.fwd_tot, w.counters + 0, ring_w);
-        }
-        {
-            LaunchTimer lt(K_BACKWARD, st);
-            kb<<<grid_for(h.n_tracebacks, lb.blocks_per_sm, lb.warps * ipw), lb.warps * 32, lb.ring_bytes * ipw, st>>>(
-                dm, bl, (int) h.n_tracebacks, w.bwd, w.bwd_tot, w.edge, w.counters + 1, ring_w);
-        }
+    }
+    constexpr int WPB = RR_THREADS / 32;
+    if (nR1 > 0) {
+        LaunchTimer lt(K_FORWARD, st);
+        auto k = k_forward_rr<S, FULL, 32>;
+        k<<<rr_grid(k, nR1, WPB), RR_THREADS, 0, st>>>(dm, bl, nR2, nR2 + nR1, w.fwd, w.fwd_tot, w.counters + 8);
+    }
+    if (nR0 > 0) {
+        LaunchTimer lt(K_FORWARD, st);
+        auto k = k_forward_rr<S, FULL, 16>;
+        k<<<rr_grid(k, nR0, 2 * WPB), RR_THREADS, 0, st>>>(dm, bl, nR2 + nR1, nR2 + nR1 + nR0, w.fwd, w.fwd_tot,
+                                                          w.counters + 9);
+    }
+    if (nT1 > 0) {
+        LaunchTimer lt(K_BACKWARD, st);
+        auto k = k_backward_rr<S, FULL, 32>;
+        k<<<rr_grid(k, nT1, WPB), RR_THREADS, 0, st>>>(dm, bl, nT2, nT2 + nT1, w.bwd, w.bwd_tot, w.edge, w.counters + 10);
+    }
+    if (nT0 > 0) {
+        LaunchTimer lt(K_BACKWARD, st);
+        auto k = k_backward_rr<S, FULL, 16>;
+        k<<<rr_grid(k, nT0, 2 * WPB), RR_THREADS, 0, st>>>(dm, bl, nT2 + nT1, nT2 + nT1 + nT0, w.bwd, w.bwd_tot, w.edge,
+                                                          w.counters + 11);
     }
     if (h.n_totals > 0) {
         LaunchTimer lt(K_TOTALS, st);
@@ -1274,6 +1308,15 @@ extern "C" int mab_debug_set_warp_group(int warps) {
         return MAB_E_ARG;
     }
     g_w5_group = warps;
+    return MAB_OK;
+}
+
+extern "C" int mab_debug_set_min_band_class(int cls) {
+    if (cls < 0 || cls > 2) {
+        mab_set_error("band class must be 0, 1 or 2");
+        return MAB_E_ARG;
+    }
+    g_min_band_class = cls;
     return MAB_OK;
 }
 

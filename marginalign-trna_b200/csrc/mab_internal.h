@@ -50,6 +50,9 @@ struct DevModel {
     double etp_upper[5][5];              // [cY][k]
     double start[MAB_MAX_S], ragged_start[MAB_MAX_S], end[MAB_MAX_S], ragged_end[MAB_MAX_S];
     int32_t t_from[13], t_to[13];        // flattened transition list (lower, middle, upper) for the expectation kernel
+    // the two addends of etp_* on their own (wavefront_reg.cuh forms eP + tP in the kernel)
+    double tp[3][5];                     // [lower | middle | upper][k]
+    double em_match[25], em_gap_x[5], em_gap_y[5];
 };
 void mab_model_to_device_block(const mab_model *m, DevModel *out);
 
@@ -73,7 +76,11 @@ struct BlobHeader {  // 256 bytes
     int64_t n_edge_cells;     // cells of the diagonals from+1 of all intermediate tracebacks (see TracebackDesc)
     int64_t n_full_cells;     // cells of all diagonals that carry a total (posterior mode keeps all states there)
     int64_t off_diag_region;  // int32[n_diagonals + 1] owning region of every diagonal (sentinel: -1)
-    int64_t pad[8];
+    // Work items by band class (mab_band_class): order_fwd / order_bwd list class 2 first, then 1, then 0, each class
+    // longest first.  The register-resident wavefront kernels take classes 0 and 1, the shared-memory-ring kernels 2.
+    int64_t n_class_regions[3];
+    int64_t n_class_tbs[3];
+    int64_t pad[2];
 };
 static_assert(sizeof(BlobHeader) == 256, "BlobHeader must be 256 bytes");
 
@@ -83,11 +90,27 @@ struct RegionDesc {  // 64 bytes
     int32_t lX, lY;
     int32_t x1, y1;                // origin inside the alignment (alignedPairCoordinateCorrectionFn)
     int32_t aln;
-    int32_t flags;                 // bit0 ragged left, bit1 ragged right (after the split rule of :1121-1122)
+    int32_t flags;                 // bit0 ragged left, bit1 ragged right (after the split rule of :1121-1122);
+                                   // bits 8..30: band span (plan_core::SpanTracker), see mab_band_class
     int32_t tb_base, n_tb;
     int32_t tot_base, n_tot;
 };
 static_assert(sizeof(RegionDesc) == 64, "RegionDesc must be 64 bytes");
+
+// Band span of a region: the largest x-y extent (max xmyR - min xmyL) over any three consecutive diagonals.  The
+// register-resident kernels map x-y to lanes circularly (lane = (xmy >> 1) mod LPI); a region fits LPI lanes iff its
+// span is at most 2 * LPI - 2 (no two live cells of three consecutive diagonals then share a lane, and an out-of-band
+// neighbour is always a lane that holds -inf).
+#define MAB_SPAN_SHIFT 8
+#define MAB_SPAN_MAX 0x7fffff
+#ifdef __CUDACC__
+#define MAB_HDI __host__ __device__ static inline
+#else
+#define MAB_HDI static inline
+#endif
+MAB_HDI int mab_region_span(int32_t flags) { return (int) (((uint32_t) flags >> MAB_SPAN_SHIFT) & MAB_SPAN_MAX); }
+// 0: fits a half-warp (16 lanes), 1: fits a warp (32 lanes), 2: wider (shared-memory ring kernels)
+MAB_HDI int mab_band_class(int span) { return span <= 30 ? 0 : (span <= 62 ? 1 : 2); }
 
 #define MAB_DIAG_NO_MIDDLE 0x80000000u  // forward diagonal xay-2 was already freed when the reference visits xay
 #define MAB_DIAG_IS_TOTAL 0x40000000u   // a total probability is evaluated ON this diagonal (index = its own total)

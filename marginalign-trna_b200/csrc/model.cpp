@@ -309,6 +309,13 @@ void mab_model_to_device_block(const mab_model *m, DevModel *d) {
         d->end[s] = m->end[s];
         d->ragged_end[s] = m->ragged_end[s];
     }
+    for (int g = 0; g < 3; g++)
+        for (int k = 0; k < m->n_trans[g]; k++) d->tp[g][k] = m->tp[g][k];
+    for (int c = 0; c < 25; c++) d->em_match[c] = m->em_match[c];
+    for (int c = 0; c < 5; c++) {
+        d->em_gap_x[c] = m->em_gap_x[c];
+        d->em_gap_y[c] = m->em_gap_y[c];
+    }
     int n = 0;
     for (int g = 0; g < 3; g++)
         for (int k = 0; k < m->n_trans[g]; k++, n++) {

@@ -61,6 +61,7 @@ void plan_region(Piece &pc, const mab_params &p, const AlnInput &in, int32_t aln
     const size_t d0 = pc.diags.size();
     pc.diags.resize(d0 + D + 1);
     int64_t cell = pc.n_cells;
+    plan_core::SpanTracker span;
     plan_core::band_walk(in, p, sp, cur, [&](int64_t xay, int64_t l, int64_t w) {
         DiagDesc &dd = pc.diags[d0 + xay];
         dd.cell_off = cell;
@@ -68,8 +69,10 @@ void plan_region(Piece &pc, const mab_params &p, const AlnInput &in, int32_t aln
         dd.tot_flags = MAB_DIAG_TOT_MASK;  // "none" until the schedule below assigns one
         cell += w;
         if (w > pc.max_width) pc.max_width = w;
+        span.add(l, w);
     });
     pc.n_cells = cell;
+    rg.flags |= span.flag_bits();
 
     auto width = [&](int64_t d) {
         const int64_t next = d == D ? cell : pc.diags[d0 + d + 1].cell_off;
@@ -309,12 +312,17 @@ int build_plan(const mab_params *p, const BatchInput &in, int n_threads, mab_pla
     // processing orders: longest first, so the dynamic work queue ends on short items
     plan->order_fwd.resize(nR);
     std::iota(plan->order_fwd.begin(), plan->order_fwd.end(), 0);
+    auto region_class = [&](int32_t r) { return mab_band_class(mab_region_span(plan->regions[r].flags)); };
     std::stable_sort(plan->order_fwd.begin(), plan->order_fwd.end(), [&](int32_t a, int32_t b) {
+        const int ca = region_class(a), cb = region_class(b);
+        if (ca != cb) return ca > cb;
         return plan->regions[a].lX + plan->regions[a].lY > plan->regions[b].lX + plan->regions[b].lY;
     });
     plan->order_bwd.resize(nT);
     std::iota(plan->order_bwd.begin(), plan->order_bwd.end(), 0);
     std::stable_sort(plan->order_bwd.begin(), plan->order_bwd.end(), [&](int32_t a, int32_t b) {
+        const int ca = region_class(plan->tbs[a].region), cb = region_class(plan->tbs[b].region);
+        if (ca != cb) return ca > cb;
         return plan->tbs[a].hi - plan->tbs[a].lo > plan->tbs[b].hi - plan->tbs[b].lo;
     });
 
@@ -331,6 +339,8 @@ int build_plan(const mab_params *p, const BatchInput &in, int n_threads, mab_pla
     h.n_edge_cells = nE;
     h.n_full_cells = nF;
     h.max_width = maxW;
+    for (int64_t r = 0; r < nR; r++) h.n_class_regions[region_class((int32_t) r)]++;
+    for (int64_t t = 0; t < nT; t++) h.n_class_tbs[region_class(plan->tbs[t].region)]++;
     h.len_sym_x = lenX;
     h.len_sym_y = lenY;
     int64_t off = sizeof(BlobHeader);

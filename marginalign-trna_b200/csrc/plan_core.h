@@ -244,6 +244,30 @@ MAB_HD void band_walk(const AlnInput &in, const mab_params &p, const Split &sp, 
     }
 }
 
+// Band span of a region (mab_internal.h, mab_band_class): feed the diagonals in order.
+struct SpanTracker {
+    int64_t l1 = 0, r1 = 0, l2 = 0, r2 = 0, span = 0;
+    int n = 0;
+    MAB_HD void add(int64_t l, int64_t w) {
+        const int64_t r = l + 2 * (w - 1);
+        int64_t lo = l, hi = r;
+        if (n >= 1) {
+            if (l1 < lo) lo = l1;
+            if (r1 > hi) hi = r1;
+        }
+        if (n >= 2) {
+            if (l2 < lo) lo = l2;
+            if (r2 > hi) hi = r2;
+        }
+        if (hi - lo > span) span = hi - lo;
+        l2 = l1, r2 = r1, l1 = l, r1 = r;
+        if (n < 2) n++;
+    }
+    MAB_HD int32_t flag_bits() const {
+        return (int32_t) ((span > MAB_SPAN_MAX ? MAB_SPAN_MAX : span) << MAB_SPAN_SHIFT);
+    }
+};
+
 // Traceback schedule of one region with D = lX + lY >= 1 diagonals after diagonal 0.  width(d) returns the number of
 // cells of diagonal d.  Sink methods:
 //   traceback(lo, hi, from, at_end, n_tot_of_this_tb, edge_cells)   called once per traceback, after its totals

@@ -84,6 +84,7 @@ struct Status {  // device-side status block (256 B), read back by the host
     int pad0;
     long long error_aln;
     long long max_width;
+    unsigned long long n_class_regions[3], n_class_tbs[3];  // work items by band class (mab_band_class)
 };
 
 // ------------------------------------------------------------------------------------------------ kernels
@@ -188,7 +189,7 @@ struct CountSink {
     }
 };
 
-__global__ void k_bands(DevInput in, mab_params p, int64_t n_regions, const RegionDesc *regions, const RegionTmp *tmp,
+__global__ void k_bands(DevInput in, mab_params p, int64_t n_regions, RegionDesc *regions, const RegionTmp *tmp,
                         const int64_t *diag_base, DiagDesc *diags, int32_t *diag_region, RegionCounts *counts,
                         Status *status) {
     const int64_t r = (int64_t) blockIdx.x * blockDim.x + threadIdx.x;
@@ -204,6 +205,7 @@ __global__ void k_bands(DevInput in, mab_params p, int64_t n_regions, const Regi
     DiagDesc *dd = diags + diag_base[r];
     int32_t *dr = diag_region + diag_base[r];
     int64_t cell = 0, max_w = 0;
+    plan_core::SpanTracker span;
     plan_core::band_walk(ai, p, Split{t.x1, t.y1, t.x2, t.y2}, cur, [&](int64_t xay, int64_t l, int64_t w) {
         DiagDesc d;
         d.cell_off = cell;
@@ -213,7 +215,9 @@ __global__ void k_bands(DevInput in, mab_params p, int64_t n_regions, const Regi
         dr[xay] = (int32_t) r;
         cell += w;
         if (w > max_w) max_w = w;
+        span.add(l, w);
     });
+    regions[r].flags = rg.flags | span.flag_bits();
     const int64_t D = (int64_t) rg.lX + rg.lY;
     CountSink sink;
     plan_core::schedule_walk(p, D, WidthFromDiags{dd, D, cell}, sink);
@@ -262,7 +266,7 @@ struct WriteSink {
 __global__ void k_schedule(mab_params p, int64_t n_regions, RegionDesc *regions, const int64_t *diag_base,
                            const RegionCounts *base /* exclusive scan, [n_regions + 1] */, DiagDesc *diags,
                            TracebackDesc *tbs, TotalDesc *totals, int32_t *region_key, int32_t *tb_key,
-                           int64_t n_diagonals) {
+                           int64_t n_diagonals, Status *status) {
     const int64_t r = (int64_t) blockIdx.x * blockDim.x + threadIdx.x;
     if (r == 0) {  // sentinel diagonal carrying the total cell count
         DiagDesc s;
@@ -279,14 +283,20 @@ __global__ void k_schedule(mab_params p, int64_t n_regions, RegionDesc *regions,
     WriteSink sink{dd, tbs + b.tbs, totals + b.tots, (int32_t) r, b.tots, b.edge, b.full};
     plan_core::schedule_walk(p, D, WidthFromDiags{dd, D, n_cells}, sink);
     for (int64_t d = 0; d <= D; d++) dd[d].cell_off += b.cells;  // region-local -> global
-    for (int64_t t = 0; t < sink.n_tb; t++) tb_key[b.tbs + t] = tbs[b.tbs + t].hi - tbs[b.tbs + t].lo;
+    // sort keys: band class first (class 2 leads the order arrays), then length
+    const int cls = mab_band_class(mab_region_span(rg.flags));
+    const int32_t key_cap = (1 << 28) - 1;
+    for (int64_t t = 0; t < sink.n_tb; t++)
+        tb_key[b.tbs + t] = (cls << 28) | min(tbs[b.tbs + t].hi - tbs[b.tbs + t].lo, key_cap);
+    atomicAdd(&status->n_class_regions[cls], 1ull);
+    atomicAdd(&status->n_class_tbs[cls], (unsigned long long) sink.n_tb);
     rg.diag_base = diag_base[r];
     rg.tb_base = (int32_t) b.tbs;
     rg.n_tb = (int32_t) sink.n_tb;
     rg.tot_base = (int32_t) b.tots;
     rg.n_tot = (int32_t) sink.n_tot;
     regions[r] = rg;
-    region_key[r] = (int32_t) D;
+    region_key[r] = (cls << 28) | (int32_t) min(D, (int64_t) key_cap);
 }
 
 __global__ void k_symbols(const uint8_t *seq, int64_t n, uint8_t *sym /* 16 guard bytes on both sides */) {
@@ -468,7 +478,7 @@ extern "C" int mab_plan_build_device(const mab_params *p, int64_t n, const uint8
         int32_t *tkey = ar.ptr<int32_t>(at_tkey), *tkey2 = ar.ptr<int32_t>(at_tkey2), *tiota = ar.ptr<int32_t>(at_tiota);
         k_schedule<<<grid(nR, 128), 128, 0, st>>>(*p, nR, d_regions, d_diag_base, d_bases, d_diags,
                                                   ar.ptr<TracebackDesc>(h.off_tracebacks),
-                                                  ar.ptr<TotalDesc>(h.off_totals), rkey, tkey, nD);
+                                                  ar.ptr<TotalDesc>(h.off_totals), rkey, tkey, nD, d_status);
         if ((rc = cuda_fail(cudaMemcpyAsync(&totals, d_bases + nR, sizeof(totals), cudaMemcpyDeviceToHost, st), "copy")))
             return rc;
         if ((rc = cuda_fail(cudaMemcpyAsync(&hs, d_status, sizeof(hs), cudaMemcpyDeviceToHost, st), "copy"))) return rc;
@@ -498,6 +508,10 @@ extern "C" int mab_plan_build_device(const mab_params *p, int64_t n, const uint8
     h.n_edge_cells = totals.edge;
     h.n_full_cells = totals.full;
     h.max_width = hs.max_width;
+    for (int c = 0; c < 3; c++) {
+        h.n_class_regions[c] = nR > 0 ? (int64_t) hs.n_class_regions[c] : 0;
+        h.n_class_tbs[c] = nR > 0 ? (int64_t) hs.n_class_tbs[c] : 0;
+    }
     h.n_anchors = -1;  // not materialised on the device
 
     mab_plan *plan = new mab_plan();

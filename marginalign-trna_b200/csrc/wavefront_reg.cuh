@@ -1,0 +1,325 @@
+// wavefront_reg.cuh -- register-resident forward / backward wavefront kernels for narrow bands (band classes 0 and 1,
+// mab_internal.h: every tRNA read, any read at diagonalExpansion 10).  Included by kernels.cu.
+//
+// Mapping.  A group of LPI lanes (a half-warp for class 0, a warp for class 1) owns one work item (a split region in
+// the forward sweep, a traceback in the backward sweep).  The x-y coordinate of a cell picks its lane CIRCULARLY,
+//     lane(xmy) = (xmy >> 1) mod LPI                      (arithmetic shift: 2k and 2k + 1 share lane k)
+// so a lane alternates between x-y = 2k (even anti-diagonals) and 2k + 1 (odd ones), and the band may drift along the
+// read without ever being re-based: it wraps around the lane ring.  The two previous anti-diagonals live in the
+// registers of the lane that computed them:
+//     middle neighbour (d-2, xmy)      own lane, two steps ago
+//     even d: upper (d-1, xmy+1) own lane, lower (d-1, xmy-1) lane k-1        (one shuffle of the states it feeds)
+//     odd  d: lower (d-1, xmy-1) own lane, upper (d-1, xmy+1) lane k+1
+// The loop is unrolled over the two parities, so which neighbour is shuffled is static and the two register cells
+// swap roles without moves.  A lane whose cell is outside the band looks up the "out of band" symbol 5, whose emission
+// rows are -inf: every addend becomes -inf and the branch-free logAdd returns -inf, so the lane stores -inf for its
+// neighbours without a single select (the reference skips transitions from cells outside the band,
+// pairwiseAligner.c:419-425, 527-554, which is the same as adding log(0)).  The plan guarantees (band span <= 2 LPI - 2)
+// that live cells never alias on the ring.
+//
+// (eP + tP) is formed here from the emission (one conflict-free LDS.64 per symbol pair) and the transition (an
+// immediate constant-bank operand): the same double addition the host used to tabulate, so the sums are bit-identical
+// to the reference's `eP + tP` (pairwiseAligner.c:314, 324), and 13 table loads per cell leave the shared-memory pipe,
+// which bounds these kernels (profiles/r1_ncu_summary.md r1h).
+#pragma once
+
+#define RR_REPL 16  // replicas of the emission tables: lane l reads replica l & 15 -> LDS.64 is conflict-free
+
+struct RegTables {
+    double em[31][RR_REPL];  // match emission by cX * 5 + cY (symbols 0..4); 25..30 = -inf (cX = cY = 5: out of band)
+    double ex[6][RR_REPL];   // gap-X emission by cX; [5] = -inf
+    double ey[6][RR_REPL];   // gap-Y emission by cY; [5] = -inf
+};
+
+__device__ __forceinline__ void fill_reg_tables(RegTables &t, const DevModel &m, int tid, int nthreads) {
+    const double NINF = neg_inf();
+    for (int i = tid; i < 31 * RR_REPL; i += nthreads) t.em[i / RR_REPL][i % RR_REPL] = i / RR_REPL < 25 ? m.em_match[i / RR_REPL] : NINF;
+    for (int i = tid; i < 6 * RR_REPL; i += nthreads) {
+        t.ex[i / RR_REPL][i % RR_REPL] = i / RR_REPL < 5 ? m.em_gap_x[i / RR_REPL] : NINF;
+        t.ey[i / RR_REPL][i % RR_REPL] = i / RR_REPL < 5 ? m.em_gap_y[i / RR_REPL] : NINF;
+    }
+}
+
+__device__ __forceinline__ double lds_f64(unsigned addr) {
+    double v;
+    asm("ld.shared.f64 %0, [%1];" : "=d"(v) : "r"(addr));
+    return v;
+}
+
+__device__ __forceinline__ double shfl_f64(unsigned mask, double v, int src) {
+    return __hiloint2double(__shfl_sync(mask, __double2hiint(v), src), __shfl_sync(mask, __double2loint(v), src));
+}
+
+// what a lane needs to know about its group
+struct RegLane {
+    int lane;          // inside the group
+    int src_dn, src_up;  // warp lanes of the ring neighbours k-1 / k+1
+    unsigned gmask;
+    CoefAddr cf;
+    unsigned em_addr, ex_addr, ey_addr;  // shared addresses of this lane's replica of row 0
+};
+
+template <int LPI>
+__device__ __forceinline__ RegLane reg_lane(const RegTables &t, const CoefTable &ct) {
+    RegLane r;
+    const int lane32 = threadIdx.x & 31;
+    r.lane = lane32 & (LPI - 1);
+    const int base = lane32 & ~(LPI - 1);
+    r.src_dn = base | ((r.lane - 1) & (LPI - 1));
+    r.src_up = base | ((r.lane + 1) & (LPI - 1));
+    r.gmask = LPI == 32 ? FULL_MASK : (0xffffu << (lane32 & 16));
+    r.cf = (unsigned) __cvta_generic_to_shared(&ct.coef[0][0][lane32 & (W5_COPIES - 1)]);
+    r.em_addr = (unsigned) __cvta_generic_to_shared(&t.em[0][lane32 & (RR_REPL - 1)]);
+    r.ex_addr = (unsigned) __cvta_generic_to_shared(&t.ex[0][lane32 & (RR_REPL - 1)]);
+    r.ey_addr = (unsigned) __cvta_generic_to_shared(&t.ey[0][lane32 & (RR_REPL - 1)]);
+    return r;
+}
+
+// One diagonal's geometry for a lane: its cell index j inside the diagonal (j < w: in band) and the cell coordinates.
+struct RegGeom {
+    int j, x, y;
+    bool active;
+};
+template <int LPI>
+__device__ __forceinline__ RegGeom reg_geom(int lane, int d, int L, int w) {
+    RegGeom g;
+    g.j = (lane - (L >> 1)) & (LPI - 1);
+    g.active = g.j < w;
+    const int xmy = L + 2 * g.j;
+    g.x = (d + xmy) >> 1;
+    g.y = d - g.x;
+    return g;
+}
+
+#define RR_LG(x, y) la_bf<COEF_SMEM>((x), (y), ln.cf)
+
+// ---- forward cell from register neighbours.  `p1` = this lane's cell on diagonal d-1, `p2` = on d-2 (overwritten with
+// the new cell).  Q = d & 1.  Transition order as forward_cell<S> (stateMachine.c:399-429, 636-661).
+template <int S, int Q>
+__device__ __forceinline__ void reg_forward_cell(const DevModel &m, const RegLane &ln, const Cell<S> &p1, Cell<S> &p2,
+                                                 double em, double ex, double ey) {
+    const int src = Q ? ln.src_up : ln.src_dn;
+    if constexpr (S == 5) {
+        // the shuffled neighbour feeds M + two gap states; the own-lane neighbour the other two
+        const double sM = shfl_f64(ln.gmask, p1.v[M], src);
+        const double sA = shfl_f64(ln.gmask, p1.v[Q ? SY : SX], src);
+        const double sB = shfl_f64(ln.gmask, p1.v[Q ? LY : LX], src);
+        const double loM = Q ? p1.v[M] : sM, loSX = Q ? p1.v[SX] : sA, loLX = Q ? p1.v[LX] : sB;
+        const double upM = Q ? sM : p1.v[M], upSY = Q ? sA : p1.v[SY], upLY = Q ? sB : p1.v[LY];
+        Cell<5> c;
+        c.v[SX] = RR_LG(__dadd_rn(loM, __dadd_rn(ex, m.tp[0][0])), __dadd_rn(loSX, __dadd_rn(ex, m.tp[0][1])));
+        c.v[LX] = RR_LG(__dadd_rn(loM, __dadd_rn(ex, m.tp[0][2])), __dadd_rn(loLX, __dadd_rn(ex, m.tp[0][3])));
+        double t = RR_LG(__dadd_rn(p2.v[M], __dadd_rn(em, m.tp[1][0])), __dadd_rn(p2.v[SX], __dadd_rn(em, m.tp[1][1])));
+        t = RR_LG(t, __dadd_rn(p2.v[SY], __dadd_rn(em, m.tp[1][2])));
+        t = RR_LG(t, __dadd_rn(p2.v[LX], __dadd_rn(em, m.tp[1][3])));
+        c.v[M] = RR_LG(t, __dadd_rn(p2.v[LY], __dadd_rn(em, m.tp[1][4])));
+        c.v[SY] = RR_LG(__dadd_rn(upM, __dadd_rn(ey, m.tp[2][0])), __dadd_rn(upSY, __dadd_rn(ey, m.tp[2][1])));
+        c.v[LY] = RR_LG(__dadd_rn(upM, __dadd_rn(ey, m.tp[2][2])), __dadd_rn(upLY, __dadd_rn(ey, m.tp[2][3])));
+        p2 = c;
+    } else {
+        const double sM = shfl_f64(ln.gmask, p1.v[M], src);
+        const double sX = shfl_f64(ln.gmask, p1.v[SX], src);
+        const double sY = shfl_f64(ln.gmask, p1.v[SY], src);
+        const double loM = Q ? p1.v[M] : sM, loSX = Q ? p1.v[SX] : sX, loSY = Q ? p1.v[SY] : sY;
+        const double upM = Q ? sM : p1.v[M], upSX = Q ? sX : p1.v[SX], upSY = Q ? sY : p1.v[SY];
+        Cell<3> c;
+        c.v[SX] = RR_LG(RR_LG(__dadd_rn(loM, __dadd_rn(ex, m.tp[0][0])), __dadd_rn(loSX, __dadd_rn(ex, m.tp[0][1]))),
+                        __dadd_rn(loSY, __dadd_rn(ex, m.tp[0][2])));
+        c.v[M] = RR_LG(RR_LG(__dadd_rn(p2.v[M], __dadd_rn(em, m.tp[1][0])), __dadd_rn(p2.v[SX], __dadd_rn(em, m.tp[1][1]))),
+                       __dadd_rn(p2.v[SY], __dadd_rn(em, m.tp[1][2])));
+        c.v[SY] = RR_LG(RR_LG(__dadd_rn(upM, __dadd_rn(ey, m.tp[2][0])), __dadd_rn(upSY, __dadd_rn(ey, m.tp[2][1]))),
+                        __dadd_rn(upSX, __dadd_rn(ey, m.tp[2][2])));
+        p2 = c;
+    }
+}
+
+// ---- backward cell (gather form, backward_cell<S> in kernels.cu).  `p1` = this lane's cell on d+1, `p2` = on d+2
+// (only its match state is read; overwritten with the new cell).  nUp = (d+1, xmy-1), nLo = (d+1, xmy+1).
+template <int S, int Q>
+__device__ __forceinline__ void reg_backward_cell(const DevModel &m, const RegLane &ln, const Cell<S> &p1, Cell<S> &p2,
+                                                  double em, double ex, double ey) {
+    const int src = Q ? ln.src_up : ln.src_dn;
+    const double miM = p2.v[M];
+    if constexpr (S == 5) {
+        // even d: nUp lives in lane k-1 (shuffle its SY, LY), nLo in this lane; odd d: nLo in lane k+1 (SX, LX)
+        const double sA = shfl_f64(ln.gmask, p1.v[Q ? SX : SY], src);
+        const double sB = shfl_f64(ln.gmask, p1.v[Q ? LX : LY], src);
+        const double upSY = Q ? p1.v[SY] : sA, upLY = Q ? p1.v[LY] : sB;
+        const double loSX = Q ? sA : p1.v[SX], loLX = Q ? sB : p1.v[LX];
+        const double mM = __dadd_rn(miM, __dadd_rn(em, m.tp[1][0]));
+        Cell<5> c;
+        double t = RR_LG(mM, __dadd_rn(upSY, __dadd_rn(ey, m.tp[2][0])));
+        t = RR_LG(t, __dadd_rn(upLY, __dadd_rn(ey, m.tp[2][2])));
+        t = RR_LG(t, __dadd_rn(loSX, __dadd_rn(ex, m.tp[0][0])));
+        c.v[M] = RR_LG(t, __dadd_rn(loLX, __dadd_rn(ex, m.tp[0][2])));
+        c.v[SX] = RR_LG(__dadd_rn(miM, __dadd_rn(em, m.tp[1][1])), __dadd_rn(loSX, __dadd_rn(ex, m.tp[0][1])));
+        c.v[SY] = RR_LG(__dadd_rn(miM, __dadd_rn(em, m.tp[1][2])), __dadd_rn(upSY, __dadd_rn(ey, m.tp[2][1])));
+        c.v[LX] = RR_LG(__dadd_rn(miM, __dadd_rn(em, m.tp[1][3])), __dadd_rn(loLX, __dadd_rn(ex, m.tp[0][3])));
+        c.v[LY] = RR_LG(__dadd_rn(miM, __dadd_rn(em, m.tp[1][4])), __dadd_rn(upLY, __dadd_rn(ey, m.tp[2][3])));
+        p2 = c;
+    } else {
+        const double s = shfl_f64(ln.gmask, p1.v[Q ? SX : SY], src);
+        const double upSY = Q ? p1.v[SY] : s, loSX = Q ? s : p1.v[SX];
+        // lower: M->X(0) X->X(1) Y->X(2); middle: M->M(0) X->M(1) Y->M(2); upper: M->Y(0) Y->Y(1) X->Y(2)
+        Cell<3> c;
+        c.v[M] = RR_LG(RR_LG(__dadd_rn(miM, __dadd_rn(em, m.tp[1][0])), __dadd_rn(upSY, __dadd_rn(ey, m.tp[2][0]))),
+                       __dadd_rn(loSX, __dadd_rn(ex, m.tp[0][0])));
+        c.v[SX] = RR_LG(RR_LG(__dadd_rn(miM, __dadd_rn(em, m.tp[1][1])), __dadd_rn(upSY, __dadd_rn(ey, m.tp[2][2]))),
+                        __dadd_rn(loSX, __dadd_rn(ex, m.tp[0][1])));
+        c.v[SY] = RR_LG(RR_LG(__dadd_rn(miM, __dadd_rn(em, m.tp[1][2])), __dadd_rn(upSY, __dadd_rn(ey, m.tp[2][1]))),
+                        __dadd_rn(loSX, __dadd_rn(ex, m.tp[0][2])));
+        p2 = c;
+    }
+}
+#undef RR_LG
+
+#define RR_THREADS 128
+
+// ------------------------------------------------------------------------------------------------ forward
+// Work items: order_fwd[item0 .. item1).  Outputs exactly what k_forward writes (F match plane + FT on total diagonals,
+// or all states when FULL).
+template <int S, bool FULL, int LPI>
+__global__ void __launch_bounds__(RR_THREADS)
+k_forward_rr(const __grid_constant__ DevModel model, Blob bl, int item0, int item1, double *__restrict__ F,
+             double *__restrict__ FT, int *counter) {
+    __shared__ RegTables tb;
+    __shared__ __align__(16) CoefTable ct;
+    fill_reg_tables(tb, model, threadIdx.x, blockDim.x);
+    fill_coef_table(ct, threadIdx.x, blockDim.x);
+    __syncthreads();
+    const RegLane ln = reg_lane<LPI>(tb, ct);
+    const int lane32 = threadIdx.x & 31;
+    const double NINF = neg_inf();
+
+    for (;;) {
+        const int item = item0 + next_item_sub<LPI>(counter, lane32, ln.gmask);
+        if (item >= item1) break;
+        const RegionDesc rg = bl.regions[bl.order_fwd[item]];
+        const DiagDesc *dd = bl.diags + rg.diag_base;
+        const uint8_t *sx = bl.sym_x + rg.sym_x_off, *sy = bl.sym_y + rg.sym_y_off;
+        const int D = rg.lX + rg.lY;
+        DiagDesc cur = dd[0], nxt = dd[1];
+        Cell<S> a, b = cell_fill<S>(NINF);
+        {  // diagonal 0: (ragged)startStateProb on every cell, pairwiseAligner.c:658-659
+            const double *init = (rg.flags & 1) ? model.ragged_start : model.start;
+            const RegGeom g = reg_geom<LPI>(ln.lane, 0, cur.xmyL, (int) (nxt.cell_off - cur.cell_off));
+#pragma unroll
+            for (int s = 0; s < S; s++) a.v[s] = g.active ? init[s] : NINF;
+            if (g.active) {
+                if (FULL) cell_store<S>(F + (cur.cell_off + g.j) * S, a);
+                else F[cur.cell_off + g.j] = a.v[M];
+            }
+        }
+        // one diagonal: p1 = diagonal d-1, p2 = diagonal d-2, replaced by diagonal d
+        auto step = [&](auto q_tag, int d, const Cell<S> &p1, Cell<S> &p2) {
+            constexpr int Q = decltype(q_tag)::value;
+            cur = nxt;
+            nxt = dd[d + 1];
+            const RegGeom g = reg_geom<LPI>(ln.lane, d, cur.xmyL, (int) (nxt.cell_off - cur.cell_off));
+            int cX = 5, cY = 5;
+            if (g.active) {
+                cX = g.x > 0 ? sx[g.x - 1] : 4;
+                cY = g.y > 0 ? sy[g.y - 1] : 4;
+            }
+            const double em = lds_f64(ln.em_addr + (cX * 5 + cY) * (RR_REPL * 8));
+            const double ex = lds_f64(ln.ex_addr + cX * (RR_REPL * 8));
+            const double ey = lds_f64(ln.ey_addr + cY * (RR_REPL * 8));
+            reg_forward_cell<S, Q>(model, ln, p1, p2, em, ex, ey);
+            if (g.active) {
+                const int64_t c = cur.cell_off + g.j;
+                if (FULL) cell_store<S>(F + c * S, p2);
+                else {
+                    F[c] = p2.v[M];
+                    if (cur.tot_flags & MAB_DIAG_IS_TOTAL)
+                        cell_store<S>(FT + ((int64_t) bl.totals[cur.tot_flags & MAB_DIAG_TOT_MASK].full_off + g.j) * S, p2);
+                }
+            }
+        };
+        int d = 1;
+        for (; d + 1 <= D; d += 2) {
+            step(std::integral_constant<int, 1>(), d, a, b);
+            step(std::integral_constant<int, 0>(), d + 1, b, a);
+        }
+        if (d <= D) step(std::integral_constant<int, 1>(), d, a, b);
+    }
+}
+
+// ------------------------------------------------------------------------------------------------ backward
+// Work items: order_bwd[item0 .. item1).  Outputs exactly what k_backward writes (B, BT, edge).
+template <int S, bool FULL, int LPI>
+__global__ void __launch_bounds__(RR_THREADS)
+k_backward_rr(const __grid_constant__ DevModel model, Blob bl, int item0, int item1, double *__restrict__ B,
+              double *__restrict__ BT, double *__restrict__ edge, int *counter) {
+    __shared__ RegTables tb;
+    __shared__ __align__(16) CoefTable ct;
+    fill_reg_tables(tb, model, threadIdx.x, blockDim.x);
+    fill_coef_table(ct, threadIdx.x, blockDim.x);
+    __syncthreads();
+    const RegLane ln = reg_lane<LPI>(tb, ct);
+    const int lane32 = threadIdx.x & 31;
+    const double NINF = neg_inf();
+
+    for (;;) {
+        const int item = item0 + next_item_sub<LPI>(counter, lane32, ln.gmask);
+        if (item >= item1) break;
+        const TracebackDesc t = bl.tbs[bl.order_bwd[item]];
+        const RegionDesc rg = bl.regions[t.region];
+        const DiagDesc *dd = bl.diags + rg.diag_base;
+        const uint8_t *sx = bl.sym_x + rg.sym_x_off, *sy = bl.sym_y + rg.sym_y_off;
+        const int lX = rg.lX, lY = rg.lY;
+        DiagDesc cur = dd[t.hi], nxt = dd[t.hi - 1];  // hi >= 1 always
+        int64_t c_above = dd[t.hi + 1].cell_off;      // first cell of the diagonal after `cur`
+        Cell<S> a, b = cell_fill<S>(NINF);
+        auto store = [&](int d, const DiagDesc &dg, const RegGeom &g, const Cell<S> &c) {
+            if (!g.active) return;
+            if (d <= t.from) {
+                const int64_t cell = dg.cell_off + g.j;
+                if (FULL) cell_store<S>(B + cell * S, c);
+                else {
+                    B[cell] = c.v[M];
+                    if (dg.tot_flags & MAB_DIAG_IS_TOTAL)
+                        cell_store<S>(BT + ((int64_t) bl.totals[dg.tot_flags & MAB_DIAG_TOT_MASK].full_off + g.j) * S, c);
+                }
+            } else if (d == t.from + 1) {
+                edge[t.edge_off + g.j] = c.v[M];
+            }
+        };
+        {  // diagonal hi: (ragged)endStateProb on every cell, pairwiseAligner.c:680-681
+            const double *init = (t.at_end && (rg.flags & 2)) ? model.ragged_end : model.end;
+            const RegGeom g = reg_geom<LPI>(ln.lane, t.hi, cur.xmyL, (int) (c_above - cur.cell_off));
+#pragma unroll
+            for (int s = 0; s < S; s++) a.v[s] = g.active ? init[s] : NINF;
+            store(t.hi, cur, g, a);
+        }
+        auto step = [&](auto q_tag, int d, const Cell<S> &p1, Cell<S> &p2) {
+            constexpr int Q = decltype(q_tag)::value;
+            c_above = cur.cell_off;
+            cur = nxt;
+            nxt = dd[d - 1];  // d >= 1: dd[0] exists
+            const RegGeom g = reg_geom<LPI>(ln.lane, d, cur.xmyL, (int) (c_above - cur.cell_off));
+            int cX = 5, cY = 5;
+            if (g.active) {  // the neighbours consume X[x] and / or Y[y] (0-based); past the end they are out of band
+                cX = g.x < lX ? sx[g.x] : 4;
+                cY = g.y < lY ? sy[g.y] : 4;
+            }
+            const double em = lds_f64(ln.em_addr + (cX * 5 + cY) * (RR_REPL * 8));
+            const double ex = lds_f64(ln.ex_addr + cX * (RR_REPL * 8));
+            const double ey = lds_f64(ln.ey_addr + cY * (RR_REPL * 8));
+            reg_backward_cell<S, Q>(model, ln, p1, p2, em, ex, ey);
+            store(d, cur, g, p2);
+        };
+        int d = t.hi - 1;
+        if (d > t.lo && !(d & 1)) {  // peel an even diagonal so that the unrolled pair starts on an odd one
+            step(std::integral_constant<int, 0>(), d, a, b);
+            const Cell<S> tmp = a;
+            a = b;
+            b = tmp;
+            d--;
+        }
+        for (; d - 1 > t.lo; d -= 2) {
+            step(std::integral_constant<int, 1>(), d, a, b);
+            step(std::integral_constant<int, 0>(), d - 1, b, a);
+        }
+        if (d > t.lo) step(std::integral_constant<int, 1>(), d, a, b);
+    }
+}

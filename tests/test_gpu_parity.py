@@ -274,7 +274,8 @@ def _blob_arrays(raw):
     names = ["magic", "n_alignments", "n_regions", "n_diagonals", "n_cells", "n_tracebacks", "n_totals", "n_anchors",
              "max_width", "len_sym_x", "len_sym_y", "off_regions", "off_diags", "off_tracebacks", "off_totals",
              "off_sym_x", "off_sym_y", "off_order_fwd", "off_order_bwd", "off_aln_region", "blob_bytes", "n_edge_cells",
-             "n_full_cells", "off_diag_region"]
+             "n_full_cells", "off_diag_region", "n_class_regions0", "n_class_regions1", "n_class_regions2",
+             "n_class_tbs0", "n_class_tbs1", "n_class_tbs2"]
     H = {k: int(h[i]) for i, k in enumerate(names)}
     cut = lambda off, nbytes: raw[off:off + nbytes]
     return H, {
@@ -303,7 +304,8 @@ def _assert_device_plan_equals_host_plan(batch, P, device):
     Hh, Ah = _blob_arrays(hb)
     Hd, Ad = _blob_arrays(db)
     for k in ("n_alignments", "n_regions", "n_diagonals", "n_cells", "n_tracebacks", "n_totals", "max_width",
-              "len_sym_x", "len_sym_y", "n_edge_cells", "n_full_cells"):
+              "len_sym_x", "len_sym_y", "n_edge_cells", "n_full_cells", "n_class_regions0", "n_class_regions1",
+              "n_class_regions2", "n_class_tbs0", "n_class_tbs1", "n_class_tbs2"):
         assert Hh[k] == Hd[k], (k, Hh[k], Hd[k])
     for k in Ah:
         assert np.array_equal(Ah[k], Ad[k]), k
@@ -342,3 +344,102 @@ def test_host_and_device_planned_runs_agree(golden):
     r2 = mab.PairHmmEngine(plan_on="device", max_cells=300_000).get_aligned_pairs_using_anchors(model, b)
     for a in ("offsets", "x", "y", "p"):
         assert np.array_equal(getattr(r1, a), getattr(r2, a)), a
+
+
+# ---------------------------------------------------------------------------------------------- round-2 additions
+
+def _oracle_check(engine, model, om, b, P, oP, ctx, expectations=True):
+    res = engine.get_aligned_pairs_using_anchors(model, b, P)
+    S = om.S
+    oT, oE, olik = np.full(S * S, 1e-12), np.full(S * 16, 1e-12), 0.0
+    for i in range(b.n):
+        anc = po.anchors_from_cigar(*b.cigar(i), b.x(i), b.y(i))
+        assert_pairs_match(res.pairs(i), po.aligned_pairs(om, b.x(i), b.y(i), anc, oP), P.threshold, (ctx, i))
+        if expectations:
+            oT, oE, olik = po.expectations(om, b.x(i), b.y(i), anc, oP, T=oT, E=oE, lik=olik)
+    if expectations:
+        T, E, lik = engine.get_expectations_using_anchors(model, b, P)
+        assert_exp_match(np.concatenate([T, E, [lik]]), np.concatenate([oT, oE, [olik]]), ctx)
+    return res
+
+
+@pytest.mark.parametrize("expansion", [200, 500])
+def test_band_sweep_wide_expansions(engine, golden, expansion):
+    """BASELINE config 4's band sweep beyond expansion 100: two 3 kb reads at expansion 200 and 500, posteriors and
+    expectations against the oracle, with the launch shape the library picks by itself (band_construct
+    pairwiseAligner.c:128-179, driver :638-759)."""
+    b = mab.synth.make_long_batch(2, read_len=3000, genome_len=50_000, seed=80 + expansion)
+    spec = golden.model_arrays("fixture5asym")
+    model, om = gpu_model(spec), oracle_model(po, spec)
+    P = mab.AlignmentParameters(diagonal_expansion=expansion, split_matrix_bigger_than=300)
+    _oracle_check(engine, model, om, b, P, po.make_params(expansion=expansion, split=300 ** 2), ("exp", expansion))
+
+
+def _with_gap_box(b, gap):
+    """Appends one tRNA-like alignment whose guide cigar holds a `gap`-base deletion followed by a `gap`-base insertion:
+    an unanchored gap x gap box inside an otherwise narrow batch (one wide diagonal in a narrow batch)."""
+    rng = np.random.default_rng(gap)
+    acgt = np.frombuffer(b"ACGT", dtype=np.uint8)
+    left = acgt[rng.integers(0, 4, 40)].tobytes().decode()
+    right = acgt[rng.integers(0, 4, 40)].tobytes().decode()
+    gx = acgt[rng.integers(0, 4, gap)].tobytes().decode()
+    gy = acgt[rng.integers(0, 4, gap)].tobytes().decode()
+    xs = [bytes(b.x(i)).decode() for i in range(b.n)] + [left + gx + right]
+    ys = [bytes(b.y(i)).decode() for i in range(b.n)] + [left + gy + right]
+    cig = [b.cigar(i) for i in range(b.n)] + [([0, 1, 2, 0], [40, gap, gap, 40])]
+    return mab.AlignmentBatch.from_lists(xs, ys, [(list(o), list(l)) for o, l in cig])
+
+
+@pytest.mark.parametrize("key", ["fixture5asym", "three_asym"])
+def test_wide_box_inside_a_narrow_batch(engine, golden, key):
+    """Band classes mixed in one batch: 60 tRNA reads (half-warp items), plus alignments with a 12 x 12 (a warp per
+    item) and a 300 x 300 unanchored box (shared-memory-ring kernels), for both state counts."""
+    b = _with_gap_box(_with_gap_box(mab.synth.make_trna_batch(60, seed=41), 12), 300)
+    spec = golden.model_arrays(key)
+    model, om = gpu_model(spec), oracle_model(po, spec)
+    P = mab.AlignmentParameters()
+    plan = mab.Plan.from_batch(b, P)
+    raw = np.zeros(plan.info.blob_bytes, dtype=np.uint8)
+    plan.write_blob(raw.ctypes.data, raw.nbytes)
+    classes = raw[:256].view(np.int64)[24:27]
+    assert classes.sum() == plan.info.n_regions and (classes > 0).all(), classes
+    _oracle_check(engine, model, om, b, P, po.make_params(expansion=10, split=3000 ** 2), key)
+
+
+def test_band_class_dispatch_does_not_change_results(engine, golden):
+    """Register-resident kernels (half-warp / warp per item) and shared-memory-ring kernels are bit-identical: the same
+    batch forced through each family (mab_debug_set_min_band_class), 5- and 3-state, posteriors and DP matrices."""
+    L = mab.capi.load()
+    b = _with_gap_box(mab.synth.make_trna_batch(500, seed=43), 25)
+    try:
+        for key in ("fixture5asym", "three_asym"):
+            model = gpu_model(golden.model_arrays(key))
+            base = None
+            for cls in (0, 1, 2):
+                mab.capi.check(L.mab_debug_set_min_band_class(cls))
+                res = engine.get_aligned_pairs_using_anchors(model, b)
+                T, E, lik = engine.get_expectations_using_anchors(model, b)
+                got = (res.offsets.copy(), res.x.copy(), res.y.copy(), res.p.copy(), np.concatenate([T, E, [lik]]))
+                if base is None:
+                    base = got
+                else:
+                    for k in range(4):
+                        assert np.array_equal(base[k], got[k]), (key, cls, k)
+                    assert_exp_match(got[4], base[4], (key, cls), rtol=1e-11)
+    finally:
+        L.mab_debug_set_min_band_class(0)
+    assert L.mab_debug_set_min_band_class(3) != 0
+
+
+def test_bigmutations_all_reads_exact_against_oracle(engine):
+    """All 30 reads of inputBigMutations (marginCaller parameters: expansion 10, split 100): the pair set, its order and
+    every p_int (within one unit of 1e-7) against the oracle."""
+    with open(os.path.join(GOLDEN, "bigmutations_alignments.json")) as fh:
+        alns = json.load(fh)
+    hmm = mab.Hmm.loadHmm(os.path.join(GOLDEN, "input_model.hmm"))
+    model = mab.PairHmmModel.from_hmm(hmm)
+    om = po.model_from_hmm(1, hmm.transitions, hmm.emissions)
+    b = mab.AlignmentBatch.from_lists([a["x"] for a in alns], [a["y"] for a in alns],
+                                      [(a["ops"], a["lens"]) for a in alns])
+    P = mab.AlignmentParameters(split_matrix_bigger_than=100)
+    _oracle_check(engine, model, om, b, P, po.make_params(expansion=10, split=100 ** 2), "bigmut", expectations=False)
