@@ -1110,16 +1110,17 @@ WaveLaunch wave_launch(int S, int64_t items, const BlobHeader &h) {
 // test hook (mab_debug_set_min_band_class): 1 runs class-0 items on the warp-per-item kernel, 2 everything on the
 // shared-memory-ring kernels; results must not depend on it
 int g_min_band_class = 0;
+#define RR_LA_DEFAULT 1
+#define RR_MINB_DEFAULT 6
+int g_la_variant = getenv("MAB_LA") ? atoi(getenv("MAB_LA")) : -1;  // experiment switch, see run_dp
 
 // register-resident kernels (wavefront_reg.cuh): resident blocks per SM from the occupancy calculator, once per kernel
 template <typename K>
 int rr_grid(K kernel, int64_t items, int items_per_block) {
-    static thread_local int blocks_per_sm = 0;
-    if (blocks_per_sm == 0) {
-        if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&blocks_per_sm, kernel, RR_THREADS, 0) != cudaSuccess ||
-            blocks_per_sm < 1)
-            blocks_per_sm = 1;
-    }
+    int blocks_per_sm = 0;  // (K is a function-pointer type shared by every instantiation: no static cache here)
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&blocks_per_sm, kernel, RR_THREADS, 0) != cudaSuccess ||
+        blocks_per_sm < 1)
+        blocks_per_sm = 1;
     const int64_t want = (items + items_per_block - 1) / items_per_block;
     const int64_t cap = (int64_t) device_info().sm_count * blocks_per_sm;
     return (int) std::max<int64_t>(1, std::min(want, cap));
@@ -1192,25 +1193,44 @@ int run_dp(const DevModel &dm, const mab_plan *plan, const Blob &bl, const Works
         }
     }
     constexpr int WPB = RR_THREADS / 32;
+    constexpr int LA = RR_LA_DEFAULT, MB = RR_MINB_DEFAULT;
     if (nR1 > 0) {
         LaunchTimer lt(K_FORWARD, st);
-        auto k = k_forward_rr<S, FULL, 32>;
+        auto k = k_forward_rr<S, FULL, 32, LA, MB>;
         k<<<rr_grid(k, nR1, WPB), RR_THREADS, 0, st>>>(dm, bl, nR2, nR2 + nR1, w.fwd, w.fwd_tot, w.counters + 8);
     }
     if (nR0 > 0) {
         LaunchTimer lt(K_FORWARD, st);
-        auto k = k_forward_rr<S, FULL, 16>;
+        auto k = k_forward_rr<S, FULL, 16, LA, MB>;
+        if constexpr (S == 5 && !FULL) {  // experiment switch (MAB_LA = 10 * minBlocks + LA)
+            if (g_la_variant == 40) k = k_forward_rr<S, FULL, 16, 0, 4>;
+            if (g_la_variant == 41) k = k_forward_rr<S, FULL, 16, 1, 4>;
+            if (g_la_variant == 50) k = k_forward_rr<S, FULL, 16, 0, 5>;
+            if (g_la_variant == 51) k = k_forward_rr<S, FULL, 16, 1, 5>;
+            if (g_la_variant == 60) k = k_forward_rr<S, FULL, 16, 0, 6>;
+            if (g_la_variant == 61) k = k_forward_rr<S, FULL, 16, 1, 6>;
+            if (g_la_variant == 71) k = k_forward_rr<S, FULL, 16, 1, 7>;
+        }
         k<<<rr_grid(k, nR0, 2 * WPB), RR_THREADS, 0, st>>>(dm, bl, nR2 + nR1, nR2 + nR1 + nR0, w.fwd, w.fwd_tot,
                                                           w.counters + 9);
     }
     if (nT1 > 0) {
         LaunchTimer lt(K_BACKWARD, st);
-        auto k = k_backward_rr<S, FULL, 32>;
+        auto k = k_backward_rr<S, FULL, 32, LA, MB>;
         k<<<rr_grid(k, nT1, WPB), RR_THREADS, 0, st>>>(dm, bl, nT2, nT2 + nT1, w.bwd, w.bwd_tot, w.edge, w.counters + 10);
     }
     if (nT0 > 0) {
         LaunchTimer lt(K_BACKWARD, st);
-        auto k = k_backward_rr<S, FULL, 16>;
+        auto k = k_backward_rr<S, FULL, 16, LA, MB>;
+        if constexpr (S == 5 && !FULL) {
+            if (g_la_variant == 40) k = k_backward_rr<S, FULL, 16, 0, 4>;
+            if (g_la_variant == 41) k = k_backward_rr<S, FULL, 16, 1, 4>;
+            if (g_la_variant == 50) k = k_backward_rr<S, FULL, 16, 0, 5>;
+            if (g_la_variant == 51) k = k_backward_rr<S, FULL, 16, 1, 5>;
+            if (g_la_variant == 60) k = k_backward_rr<S, FULL, 16, 0, 6>;
+            if (g_la_variant == 61) k = k_backward_rr<S, FULL, 16, 1, 6>;
+            if (g_la_variant == 71) k = k_backward_rr<S, FULL, 16, 1, 7>;
+        }
         k<<<rr_grid(k, nT0, 2 * WPB), RR_THREADS, 0, st>>>(dm, bl, nT2 + nT1, nT2 + nT1 + nT0, w.bwd, w.bwd_tot, w.edge,
                                                           w.counters + 11);
     }

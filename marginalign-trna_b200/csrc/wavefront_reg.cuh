@@ -91,11 +91,34 @@ __device__ __forceinline__ RegGeom reg_geom(int lane, int d, int L, int w) {
     return g;
 }
 
-#define RR_LG(x, y) la_bf<COEF_SMEM>((x), (y), ln.cf)
+// logAdd for the register kernels.  LA = 0: la_bf (compare, swap, subtract).  LA = 1: d = |x - y| straight from one
+// subtraction (round-to-nearest is symmetric, so |fl(x - y)| == fl(max - min) bit for bit) and max / min picked by the
+// sign bit of the difference: the compare-and-swap leaves the dependency chain in front of the polynomial and one
+// DSETP leaves the FP64 pipe (tools/la_probe.cu: 9.0 instead of 9.6 SM cycles per warp-logAdd at saturation).
+// x == y gives +0 (max = x as in the reference); -inf - -inf gives NaN: either operand is the right result (-inf).
+template <int LA>
+__device__ __forceinline__ double la_rr(double x, double y, unsigned coef_addr) {
+    if (LA == 0) return la_bf<COEF_SMEM>(x, y, coef_addr);
+    const double df = __dsub_rn(x, y);
+    const bool lt = __double2hiint(df) < 0;
+    const double hi = lt ? y : x, lo = lt ? x : y;
+    const double d = fabs(df);
+    unsigned a = coef_addr;
+    if (d > 1.00) a += 2 * W5_COPIES * 16;
+    if (d > 2.50) a += 2 * W5_COPIES * 16;
+    if (d > 4.50) a += 2 * W5_COPIES * 16;
+    const double2 c32 = lds_v2(a), c10 = lds_v2_128(a);
+    double r = __dadd_rn(__dmul_rn(c32.x, d), c32.y);
+    r = __dadd_rn(__dmul_rn(r, d), c10.x);
+    r = __dadd_rn(__dmul_rn(r, d), c10.y);
+    r = __dadd_rn(r, lo);
+    return d < 7.5 ? r : hi;
+}
+#define RR_LG(x, y) la_rr<LA>((x), (y), ln.cf)
 
 // ---- forward cell from register neighbours.  `p1` = this lane's cell on diagonal d-1, `p2` = on d-2 (overwritten with
 // the new cell).  Q = d & 1.  Transition order as forward_cell<S> (stateMachine.c:399-429, 636-661).
-template <int S, int Q>
+template <int S, int Q, int LA>
 __device__ __forceinline__ void reg_forward_cell(const DevModel &m, const RegLane &ln, const Cell<S> &p1, Cell<S> &p2,
                                                  double em, double ex, double ey) {
     const int src = Q ? ln.src_up : ln.src_dn;
@@ -135,7 +158,7 @@ __device__ __forceinline__ void reg_forward_cell(const DevModel &m, const RegLan
 
 // ---- backward cell (gather form, backward_cell<S> in kernels.cu).  `p1` = this lane's cell on d+1, `p2` = on d+2
 // (only its match state is read; overwritten with the new cell).  nUp = (d+1, xmy-1), nLo = (d+1, xmy+1).
-template <int S, int Q>
+template <int S, int Q, int LA>
 __device__ __forceinline__ void reg_backward_cell(const DevModel &m, const RegLane &ln, const Cell<S> &p1, Cell<S> &p2,
                                                   double em, double ex, double ey) {
     const int src = Q ? ln.src_up : ln.src_dn;
@@ -178,8 +201,8 @@ __device__ __forceinline__ void reg_backward_cell(const DevModel &m, const RegLa
 // ------------------------------------------------------------------------------------------------ forward
 // Work items: order_fwd[item0 .. item1).  Outputs exactly what k_forward writes (F match plane + FT on total diagonals,
 // or all states when FULL).
-template <int S, bool FULL, int LPI>
-__global__ void __launch_bounds__(RR_THREADS)
+template <int S, bool FULL, int LPI, int LA, int MINB>
+__global__ void __launch_bounds__(RR_THREADS, MINB)
 k_forward_rr(const __grid_constant__ DevModel model, Blob bl, int item0, int item1, double *__restrict__ F,
              double *__restrict__ FT, int *counter) {
     __shared__ RegTables tb;
@@ -224,7 +247,7 @@ k_forward_rr(const __grid_constant__ DevModel model, Blob bl, int item0, int ite
             const double em = lds_f64(ln.em_addr + (cX * 5 + cY) * (RR_REPL * 8));
             const double ex = lds_f64(ln.ex_addr + cX * (RR_REPL * 8));
             const double ey = lds_f64(ln.ey_addr + cY * (RR_REPL * 8));
-            reg_forward_cell<S, Q>(model, ln, p1, p2, em, ex, ey);
+            reg_forward_cell<S, Q, LA>(model, ln, p1, p2, em, ex, ey);
             if (g.active) {
                 const int64_t c = cur.cell_off + g.j;
                 if (FULL) cell_store<S>(F + c * S, p2);
@@ -246,8 +269,8 @@ k_forward_rr(const __grid_constant__ DevModel model, Blob bl, int item0, int ite
 
 // ------------------------------------------------------------------------------------------------ backward
 // Work items: order_bwd[item0 .. item1).  Outputs exactly what k_backward writes (B, BT, edge).
-template <int S, bool FULL, int LPI>
-__global__ void __launch_bounds__(RR_THREADS)
+template <int S, bool FULL, int LPI, int LA, int MINB>
+__global__ void __launch_bounds__(RR_THREADS, MINB)
 k_backward_rr(const __grid_constant__ DevModel model, Blob bl, int item0, int item1, double *__restrict__ B,
               double *__restrict__ BT, double *__restrict__ edge, int *counter) {
     __shared__ RegTables tb;
@@ -305,7 +328,7 @@ k_backward_rr(const __grid_constant__ DevModel model, Blob bl, int item0, int it
             const double em = lds_f64(ln.em_addr + (cX * 5 + cY) * (RR_REPL * 8));
             const double ex = lds_f64(ln.ex_addr + cX * (RR_REPL * 8));
             const double ey = lds_f64(ln.ey_addr + cY * (RR_REPL * 8));
-            reg_backward_cell<S, Q>(model, ln, p1, p2, em, ex, ey);
+            reg_backward_cell<S, Q, LA>(model, ln, p1, p2, em, ex, ey);
             store(d, cur, g, p2);
         };
         int d = t.hi - 1;
