@@ -73,11 +73,13 @@ class Hmm:
         return Hmm(MODEL_NAMES[int(l[0])]).addExpectationsFile(file)
 
     def normalise(self):
+        """cPecanEm.py:61-73.  The row sums are Python's left-to-right `sum` (numpy's pairwise sum of 16 values rounds
+        differently in the last place; tests/test_py_reference.py pins this against the reference's own code)."""
         S = self.stateNumber
         T = self.transitions.reshape(S, S)
-        self.transitions = (T / T.sum(axis=1, keepdims=True)).reshape(-1)
+        self.transitions = np.array([v / sum(row) for row in T.tolist() for v in row])
         E = self.emissions.reshape(S, SYMBOL_NUMBER ** 2)
-        self.emissions = (E / E.sum(axis=1, keepdims=True)).reshape(-1)
+        self.emissions = np.array([v / sum(row) for row in E.tolist() for v in row])
 
     def randomise(self, rng=random):
         self.transitions = np.array([rng.random() for _ in range(self.stateNumber ** 2)])
@@ -99,7 +101,51 @@ class Hmm:
         n = SYMBOL_NUMBER
         E = self.emissions.reshape(self.stateNumber, n, n).copy()
         for s in range(self.stateNumber):
-            ident = float(np.trace(E[s]))
+            # cPecanEm.py:97-101: the identity mass is summed over all 16 entries in order, off-diagonals adding 0.0
+            ident = sum(float(E[s, i, i]) for i in range(n))
             E[s] = (1.0 - ident) / (n * n - n)
             np.fill_diagonal(E[s], ident / n)
         self.emissions = E.reshape(-1)
+
+
+# ---- model post-processing after EM (src/margin/marginAlignLib.py:227-263) -----------------------------------------
+
+def setHmmIndelEmissionsToBeFlat(hmm):
+    """marginAlignLib.py:251-256: every gap state emits uniformly."""
+    n2 = SYMBOL_NUMBER ** 2
+    hmm.emissions = np.asarray(hmm.emissions, dtype=np.float64).copy()
+    hmm.emissions[n2:] = 1.0 / n2
+
+
+def normaliseHmmByReferenceGCContent(hmm, gcContent):
+    """marginAlignLib.py:238-249: rows (reference base) of the match and gap-X emission blocks are rescaled so that the
+    reference bases have GC content `gcContent`; the insert states 2 and 4 (no reference base) are left alone."""
+    n = SYMBOL_NUMBER
+    E = np.asarray(hmm.emissions, dtype=np.float64).reshape(hmm.stateNumber, n, n).copy()
+    for state in range(hmm.stateNumber):
+        if state in (2, 4):
+            continue
+        for i in range(n):
+            row_sum = sum(E[state, i].tolist())
+            w = gcContent / 2.0 if i in (1, 2) else (1.0 - gcContent) / 2.0
+            E[state, i] = [(v / row_sum) * w for v in E[state, i].tolist()]
+    hmm.emissions = E.reshape(-1)
+
+
+def modifyHmmEmissionsByExpectedVariationRate(hmm, substitutionRate):
+    """marginAlignLib.py:258-263: match emissions multiplied by a uniform substitution matrix."""
+    n = SYMBOL_NUMBER
+    m = np.full((n, n), substitutionRate / (n - 1))
+    np.fill_diagonal(m, 1.0 - substitutionRate)
+    hmm.emissions = np.asarray(hmm.emissions, dtype=np.float64).copy()
+    hmm.emissions[:n * n] = np.dot(hmm.emissions[:n * n].reshape(n, n), m).reshape(-1)
+
+
+def learn_model_postprocess(unnormalised_model_path, output_model_path, py2_compat=False):
+    """learnModelFromSamFileTargetFn2 (marginAlignLib.py:227-232): what turns the model EM wrote into the one
+    marginAlign realigns with."""
+    hmm = Hmm.loadHmm(unnormalised_model_path)
+    setHmmIndelEmissionsToBeFlat(hmm)
+    normaliseHmmByReferenceGCContent(hmm, 0.5)
+    hmm.write(output_model_path, py2_compat=py2_compat)
+    return hmm

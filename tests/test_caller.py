@@ -2,8 +2,10 @@
 
 CPU: the oracle chain (oracle posteriors -> oracle/caller_oracle.py, the restated marginCallerLib.py) against the
 golden calls made from the UNMODIFIED reference C posteriors (tests/golden/caller_case.json).
-GPU: ColumnCaller (mab_columns_accumulate / mab_columns_call) against the oracle chain: identical call set,
-posteriors within 1e-9 (spec 1e-5), expected base counts exact in units of 1e-6."""
+GPU: ColumnCaller (mab_columns_accumulate / mab_columns_call) against the oracle chain: identical call set, expected
+base counts within the 1e-6 steps a last-place difference in p_int can cause, column posteriors within 1e-9 of the
+oracle's calcBasePosteriorProbs evaluated on the SAME counts and within 1e-5 (the spec) of the all-oracle chain.
+The oracle's column functions are pinned to the reference's own Python in tests/test_py_reference.py."""
 import json
 import os
 
@@ -112,8 +114,19 @@ def test_gpu_columns_match_the_oracle(case, oracle_run):
     assert n_obs == len(exp)
     err = mab.caller.load_hmm_substitution_matrix(case["hmm"])
     gp = cc.posteriors(err)
+    err_d = co.substitution_matrix(case["hmm"].emissions)
     for (name, pos), probs in post.items():
-        np.testing.assert_allclose(gp[cc.offset[name] + pos], [probs[c] for c in "ACGT"], rtol=1e-4, atol=1e-9)
+        row = gp[cc.offset[name] + pos]
+        # (1) the column kernel itself: the oracle's calcBasePosteriorProbs on the counts the GPU accumulated
+        counts = table[cc.offset[name] + pos]
+        same = co.calc_base_posterior_probs(dict(zip("ACGT", (counts / counts.sum()).tolist())),
+                                            case["references"][name][pos], co.null_matrix(), err_d)
+        np.testing.assert_allclose(row, [same[c] for c in "ACGT"], rtol=1e-9, atol=1e-300)
+        # (2) the whole chain at the spec's bar.  A count may sit one 1e-6 step away from the oracle's (see above);
+        # log P(base) is linear in the normalised counts with slopes log(err) of a few units, so one step on a column
+        # of total mass >= 1 moves a posterior by ~1e-5 relative at most: columns observed less than that are skipped
+        if counts.sum() >= 3.0:
+            np.testing.assert_allclose(row, [probs[c] for c in "ACGT"], rtol=1e-5, atol=1e-9)
     got = {(c[0], c[1], c[2]) for c in cc.calls(err, case["threshold"])}
     want = {(c[0], c[1], c[2]) for c in calls}
     near = {(c[0], c[1], c[2]) for c in calls if abs(c[3] - case["threshold"]) < 1e-4}

@@ -20,8 +20,24 @@ ITERATIONS = 10
 RTOL = 1e-7  # spec: 1e-5
 
 
+def reference_m_step(modelType, T, E, lik):
+    """calculateMaximisation (cPecanEm.py:182-202, trainEmissions, no tying) = Hmm.normalise (:61-73), written out with
+    plain lists and left-to-right sums like the reference -- independent of mab.Hmm / mab.em.maximisation, which
+    tests/test_py_reference.py pins to the reference's own code."""
+    S = 5 if modelType.startswith("five") else 3
+    T, E = list(T), list(E)
+    for s in range(S):
+        j = sum(T[s * S:(s + 1) * S])
+        T[s * S:(s + 1) * S] = [v / j for v in T[s * S:(s + 1) * S]]
+        j = sum(E[s * 16:(s + 1) * 16])
+        E[s * 16:(s + 1) * 16] = [v / j for v in E[s * 16:(s + 1) * 16]]
+    hmm = mab.Hmm(modelType)
+    hmm.transitions, hmm.emissions, hmm.likelihood = np.array(T), np.array(E), float(lik)
+    return hmm
+
+
 def oracle_em(batch, options):
-    """cPecanEm.py:107-202 with the oracle as the E-step."""
+    """cPecanEm.py:107-202 with the oracle as the E-step and reference_m_step as the M-step."""
     hmm = mab.em.initial_hmm(options)
     oP = po.make_params(expansion=options.diagonalExpansion, split=options.splitMatrixBiggerThanThis ** 2)
     running = []
@@ -32,9 +48,7 @@ def oracle_em(batch, options):
         for i in range(batch.n):
             anc = po.anchors_from_cigar(*batch.cigar(i), batch.x(i), batch.y(i))
             T, E, lik = po.expectations(om, batch.x(i), batch.y(i), anc, oP, T=T, E=E, lik=lik)
-        new = mab.Hmm(hmm.modelType)
-        new.addExpectations(T, E, lik)
-        hmm = mab.em.maximisation(new, hmm, options)
+        hmm = reference_m_step(hmm.modelType, T.tolist(), E.tolist(), lik)
         running.append(hmm.likelihood)
     return hmm, running
 
@@ -65,3 +79,24 @@ def test_em_ten_iterations_match_the_oracle(tmp_path, model_type, start):
     # the written model loads back to the same parameters (the .hmm file stays drop-in)
     back = mab.Hmm.loadHmm(out)
     np.testing.assert_allclose(back.transitions, got.transitions, rtol=1e-6)
+
+
+def test_config2_on_the_two_alignments_of_input_sam(tmp_path, golden):
+    """BASELINE config 2 as worded: fiveStateAsymmetric, 10 iterations from the shipped model, on the two alignments of
+    the reference's tests/input.sam (golden cases fixture0 / fixture1: 1751- and 6222-nt reads, ~210 k cells per
+    iteration), expansion 10, split 300, trainEmissions."""
+    cs = [next(c for c in golden.cases if c["name"] == n) for n in ("fixture0_realign", "fixture1_realign")]
+    b = mab.AlignmentBatch.from_lists([c["x"] for c in cs], [c["y"] for c in cs], [(c["ops"], c["lens"]) for c in cs])
+    kw = dict(iterations=ITERATIONS, trials=1, modelType="fiveStateAsymmetric",
+              inputModel=os.path.join(GOLDEN, "input_model.hmm"))
+    got = mab.em.expectation_maximisation_trials(mab.PairHmmEngine(), b, str(tmp_path / "m.hmm"), mab.em.EmOptions(**kw))
+    want, running = oracle_em(b, mab.em.EmOptions(**kw))
+    np.testing.assert_allclose(got.runningLikelihoods, running, rtol=RTOL)
+    np.testing.assert_allclose(got.transitions, want.transitions, rtol=RTOL, atol=1e-300)
+    np.testing.assert_allclose(got.emissions, want.emissions, rtol=RTOL, atol=1e-300)
+    assert engine_cells(b) > 200_000
+
+
+def engine_cells(b):
+    plan = mab.Plan.from_batch(b, mab.AlignmentParameters(split_matrix_bigger_than=300))
+    return plan.info.n_cells
