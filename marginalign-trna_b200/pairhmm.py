@@ -750,10 +750,15 @@ class PairHmmEngine:
         stats = dict(cells=0, regions=0, diagonals=0, h2d_bytes=0, d2h_bytes=0, chunks=0)
         with torch.cuda.device(self.device):
             d_out = torch.from_numpy(init).to(self.device)
-            for dplan in self._device_plans(batch, params, True):
+            done = []  # one event per chunk: at most two chunks' workspaces are alive, and the host never waits for
+            for dplan in self._device_plans(batch, params, True):  # the chunk it has just queued
                 info = dplan.plan.info
+                if len(done) >= 2:
+                    done[-2].synchronize()
                 self.expectations_device(model, dplan, d_out)
-                torch.cuda.current_stream(self.device).synchronize()
+                ev = torch.cuda.Event()
+                ev.record(torch.cuda.current_stream(self.device))
+                done.append(ev)
                 stats["cells"] += info.n_cells
                 stats["regions"] += info.n_regions
                 stats["diagonals"] += info.n_diagonals

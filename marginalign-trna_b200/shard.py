@@ -130,6 +130,7 @@ class ShardedPairHmm:
         self.rank, self.world = world_info(group)
         self.comm_device = comm_device if comm_device is not None else getattr(engine, "device", "cpu")
         self.last_shards = None
+        self.last_phases = None
 
     def shards(self, batch, params):
         return partition(estimate_cells(batch, params), self.world)
@@ -139,17 +140,26 @@ class ShardedPairHmm:
         params = params or AlignmentParameters()
         if self.world == 1:
             return self.engine.get_aligned_pairs_using_anchors(model, batch, params)
+        import time
+        t0 = time.perf_counter()
         shards = self.shards(batch, params)
         self.last_shards = shards
         mine = shards[self.rank]
-        res = self.engine.get_aligned_pairs_using_anchors(model, batch.subset(mine), params)
+        sub = batch.subset(mine)
+        t1 = time.perf_counter()
+        res = self.engine.get_aligned_pairs_using_anchors(model, sub, params)
+        t2 = time.perf_counter()
         cols = []
         for a in (res.offsets, res.x, res.y, res.p):
             cols.append(_gather_varlen(np.asarray(a), dst, self.comm_device, self.group))
+        t3 = time.perf_counter()
+        self.last_phases = {"partition_s": t1 - t0, "compute_s": t2 - t1, "gather_s": t3 - t2, "merge_s": 0.0}
         if self.rank != dst:
             return None
         parts = [(cols[0][r], cols[1][r], cols[2][r], cols[3][r]) for r in range(self.world)]
-        return merge_pairs(parts, shards, batch.n)
+        out = merge_pairs(parts, shards, batch.n)
+        self.last_phases["merge_s"] = time.perf_counter() - t3
+        return out
 
     def get_expectations_using_anchors(self, model, batch, params=None, pseudo_count=1e-12):
         """All ranks receive the same summed (transitions, emissions, likelihood).  The pseudo-count is added once,
