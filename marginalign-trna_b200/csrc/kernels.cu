@@ -161,71 +161,17 @@ __device__ __forceinline__ void cell_store(double *p, const Cell<S> &c) {
 
 enum { M = 0, SX = 1, SY = 2, LX = 3, LY = 4 };
 
-// Forward cell update: cell_calculateForward over stateMachine{5,3}_cellCalculate (stateMachine.c:399-429, 636-661).
-// A missing neighbour is passed as all -inf, which leaves the affected states at -inf exactly as skipping the group
-// does.  The first term of each chain replaces logAdd(-inf, t) == t.
-template <int S>
-__device__ __forceinline__ Cell<S> forward_cell(const Cell<S> &lo, const Cell<S> &mi, const Cell<S> &up,
-                                                const double *eL, const double *eM, const double *eU);
-
-template <>
-__device__ __forceinline__ Cell<5> forward_cell<5>(const Cell<5> &lo, const Cell<5> &mi, const Cell<5> &up,
-                                                   const double *eL, const double *eM, const double *eU) {
-    Cell<5> c;
-    c.v[SX] = la(__dadd_rn(lo.v[M], eL[0]), __dadd_rn(lo.v[SX], eL[1]));
-    c.v[LX] = la(__dadd_rn(lo.v[M], eL[2]), __dadd_rn(lo.v[LX], eL[3]));
-    double m = la(__dadd_rn(mi.v[M], eM[0]), __dadd_rn(mi.v[SX], eM[1]));
-    m = la(m, __dadd_rn(mi.v[SY], eM[2]));
-    m = la(m, __dadd_rn(mi.v[LX], eM[3]));
-    c.v[M] = la(m, __dadd_rn(mi.v[LY], eM[4]));
-    c.v[SY] = la(__dadd_rn(up.v[M], eU[0]), __dadd_rn(up.v[SY], eU[1]));
-    c.v[LY] = la(__dadd_rn(up.v[M], eU[2]), __dadd_rn(up.v[LY], eU[3]));
-    return c;
-}
-
-template <>
-__device__ __forceinline__ Cell<3> forward_cell<3>(const Cell<3> &lo, const Cell<3> &mi, const Cell<3> &up,
-                                                   const double *eL, const double *eM, const double *eU) {
-    Cell<3> c;
-    c.v[SX] = la(la(__dadd_rn(lo.v[M], eL[0]), __dadd_rn(lo.v[SX], eL[1])), __dadd_rn(lo.v[SY], eL[2]));
-    c.v[M] = la(la(__dadd_rn(mi.v[M], eM[0]), __dadd_rn(mi.v[SX], eM[1])), __dadd_rn(mi.v[SY], eM[2]));
-    c.v[SY] = la(la(__dadd_rn(up.v[M], eU[0]), __dadd_rn(up.v[SY], eU[1])), __dadd_rn(up.v[SX], eU[2]));
-    return c;
-}
-
-// Backward cell as a gather.  The reference scatters (doTransitionBackward, pairwiseAligner.c:322-325): while it
-// processes diagonal d+2 the target cell T=(d,xmy) receives the match group of (d+2,xmy); while it processes d+1 in
-// ascending xmy, T receives the upper group of (d+1,xmy-1) [T is that cell's "upper"] and then the lower group of
-// (d+1,xmy+1) [T is its "lower"].  nMi/nUp/nLo are those three cells; eM/eU/eL their (eP+tP) rows.
-template <int S>
-__device__ __forceinline__ Cell<S> backward_cell(const Cell<S> &nMi, const Cell<S> &nUp, const Cell<S> &nLo,
-                                                 const double *eM, const double *eU, const double *eL);
-
-template <>
-__device__ __forceinline__ Cell<5> backward_cell<5>(const Cell<5> &nMi, const Cell<5> &nUp, const Cell<5> &nLo,
-                                                    const double *eM, const double *eU, const double *eL) {
-    Cell<5> c;
-    double m = la(__dadd_rn(nMi.v[M], eM[0]), __dadd_rn(nUp.v[SY], eU[0]));
-    m = la(m, __dadd_rn(nUp.v[LY], eU[2]));
-    m = la(m, __dadd_rn(nLo.v[SX], eL[0]));
-    c.v[M] = la(m, __dadd_rn(nLo.v[LX], eL[2]));
-    c.v[SX] = la(__dadd_rn(nMi.v[M], eM[1]), __dadd_rn(nLo.v[SX], eL[1]));
-    c.v[SY] = la(__dadd_rn(nMi.v[M], eM[2]), __dadd_rn(nUp.v[SY], eU[1]));
-    c.v[LX] = la(__dadd_rn(nMi.v[M], eM[3]), __dadd_rn(nLo.v[LX], eL[3]));
-    c.v[LY] = la(__dadd_rn(nMi.v[M], eM[4]), __dadd_rn(nUp.v[LY], eU[3]));
-    return c;
-}
-
-template <>
-__device__ __forceinline__ Cell<3> backward_cell<3>(const Cell<3> &nMi, const Cell<3> &nUp, const Cell<3> &nLo,
-                                                    const double *eM, const double *eU, const double *eL) {
-    Cell<3> c;
-    // lower: M->X(0) X->X(1) Y->X(2); middle: M->M(0) X->M(1) Y->M(2); upper: M->Y(0) Y->Y(1) X->Y(2)
-    c.v[M] = la(la(__dadd_rn(nMi.v[M], eM[0]), __dadd_rn(nUp.v[SY], eU[0])), __dadd_rn(nLo.v[SX], eL[0]));
-    c.v[SX] = la(la(__dadd_rn(nMi.v[M], eM[1]), __dadd_rn(nUp.v[SY], eU[2])), __dadd_rn(nLo.v[SX], eL[1]));
-    c.v[SY] = la(la(__dadd_rn(nMi.v[M], eM[2]), __dadd_rn(nUp.v[SY], eU[1])), __dadd_rn(nLo.v[SX], eL[2]));
-    return c;
-}
+// Transition order of the cells (cell_calculateForward / cell_calculateBackward over stateMachine{5,3}_cellCalculate,
+// stateMachine.c:399-429, 636-661).  A missing neighbour is passed as all -inf, which leaves the affected states at -inf
+// exactly as skipping the group does; the first term of each chain replaces logAdd(-inf, t) == t.
+//   forward 5-state : SX = la(lo.M+eL0, lo.SX+eL1); LX = la(lo.M+eL2, lo.LX+eL3);
+//                     M = la(la(la(la(mi.M+eM0, mi.SX+eM1), mi.SY+eM2), mi.LX+eM3), mi.LY+eM4);
+//                     SY = la(up.M+eU0, up.SY+eU1); LY = la(up.M+eU2, up.LY+eU3)
+//   forward 3-state : SX = la(la(lo.M+eL0, lo.SX+eL1), lo.SY+eL2); M, SY likewise from mi / up
+// Backward is a gather.  The reference scatters (doTransitionBackward, pairwiseAligner.c:322-325): while it processes
+// diagonal d+2 the target cell T=(d,xmy) receives the match group of (d+2,xmy); while it processes d+1 in ascending xmy,
+// T receives the upper group of (d+1,xmy-1) [T is that cell's "upper"] and then the lower group of (d+1,xmy+1) [T is
+// its "lower"].  nMi/nUp/nLo are those three cells; the terms are added in exactly that order.
 
 // ------------------------------------------------------------------------------------------------ blob access
 
@@ -319,49 +265,21 @@ __device__ __forceinline__ Cell<3> backward_cell3_bf(const Cell<3> &nMi, const C
     c.v[SY] = LC(LG(__dadd_rn(nMi.v[M], eM[2]), __dadd_rn(nUp.v[SY], eU[1])), __dadd_rn(nLo.v[SX], eL[2]));
     return c;
 }
-__device__ __forceinline__ Cell<5> forward_cell5_bf(const Cell<5> &lo, const Cell<5> &mi, const Cell<5> &up,
-                                                    const double *eL, const double *eM, const double *eU,
-                                                    const CoefAddr &cf) {
-    Cell<5> c;
-    c.v[SX] = LG(__dadd_rn(lo.v[M], eL[0]), __dadd_rn(lo.v[SX], eL[1]));
-    c.v[LX] = LG(__dadd_rn(lo.v[M], eL[2]), __dadd_rn(lo.v[LX], eL[3]));
-    double m = LC(__dadd_rn(mi.v[M], eM[0]), __dadd_rn(mi.v[SX], eM[1]));
-    m = LC(m, __dadd_rn(mi.v[SY], eM[2]));
-    m = LC(m, __dadd_rn(mi.v[LX], eM[3]));
-    c.v[M] = LC(m, __dadd_rn(mi.v[LY], eM[4]));
-    c.v[SY] = LG(__dadd_rn(up.v[M], eU[0]), __dadd_rn(up.v[SY], eU[1]));
-    c.v[LY] = LG(__dadd_rn(up.v[M], eU[2]), __dadd_rn(up.v[LY], eU[3]));
-    return c;
-}
-__device__ __forceinline__ Cell<5> backward_cell5_bf(const Cell<5> &nMi, const Cell<5> &nUp, const Cell<5> &nLo,
-                                                     const double *eM, const double *eU, const double *eL,
-                                                     const CoefAddr &cf) {
-    Cell<5> c;
-    double m = LC(__dadd_rn(nMi.v[M], eM[0]), __dadd_rn(nUp.v[SY], eU[0]));
-    m = LC(m, __dadd_rn(nUp.v[LY], eU[2]));
-    m = LC(m, __dadd_rn(nLo.v[SX], eL[0]));
-    c.v[M] = LC(m, __dadd_rn(nLo.v[LX], eL[2]));
-    c.v[SX] = LG(__dadd_rn(nMi.v[M], eM[1]), __dadd_rn(nLo.v[SX], eL[1]));
-    c.v[SY] = LG(__dadd_rn(nMi.v[M], eM[2]), __dadd_rn(nUp.v[SY], eU[1]));
-    c.v[LX] = LG(__dadd_rn(nMi.v[M], eM[3]), __dadd_rn(nLo.v[LX], eL[3]));
-    c.v[LY] = LG(__dadd_rn(nMi.v[M], eM[4]), __dadd_rn(nUp.v[LY], eU[3]));
-    return c;
-}
 #undef LG
 #undef LC
 template <int S>
 __device__ __forceinline__ Cell<S> forward_cell_sel(const Cell<S> &lo, const Cell<S> &mi, const Cell<S> &up,
                                                     const double *eL, const double *eM, const double *eU,
                                                     const CoefAddr &cf) {
-    if constexpr (S == 3) return forward_cell3_bf(lo, mi, up, eL, eM, eU, cf);
-    else return forward_cell5_bf(lo, mi, up, eL, eM, eU, cf);
+    static_assert(S == 3, "5-state bands run on wavefront5.cuh / wavefront_reg.cuh");
+    return forward_cell3_bf(lo, mi, up, eL, eM, eU, cf);
 }
 template <int S>
 __device__ __forceinline__ Cell<S> backward_cell_sel(const Cell<S> &nMi, const Cell<S> &nUp, const Cell<S> &nLo,
                                                      const double *eM, const double *eU, const double *eL,
                                                      const CoefAddr &cf) {
-    if constexpr (S == 3) return backward_cell3_bf(nMi, nUp, nLo, eM, eU, eL, cf);
-    else return backward_cell5_bf(nMi, nUp, nLo, eM, eU, eL, cf);
+    static_assert(S == 3, "5-state bands run on wavefront5.cuh / wavefront_reg.cuh");
+    return backward_cell3_bf(nMi, nUp, nLo, eM, eU, eL, cf);
 }
 
 #include "wavefront_reg.cuh"
@@ -1054,7 +972,7 @@ int grid_for(int64_t items, int blocks_per_sm, int warps_per_block = WARPS_PER_B
 }
 
 // warps per 5-state work item: 0 = chosen from the mean band width (run_dp), 1/2/4/8 = forced (tests, profiling)
-int g_w5_group = getenv("MAB_W5_GROUP") ? atoi(getenv("MAB_W5_GROUP")) : 0;
+int g_w5_group = 0;
 
 template <typename K>
 int allow_smem(K kernel, int64_t bytes) {
@@ -1071,7 +989,7 @@ struct WaveLaunch {
 };
 WaveLaunch wave_launch_for(int S, int G, const BlobHeader &h, bool wave5 = true) {
     wave5 = wave5 && S == 5;
-    static const int w5_warps = getenv("MAB_W5_WARPS") ? std::max(1, std::min(32, atoi(getenv("MAB_W5_WARPS")))) : 8;
+    const int w5_warps = 8;
     const DeviceInfo &di = device_info();
     WaveLaunch l;
     l.G = G;
@@ -1110,9 +1028,8 @@ WaveLaunch wave_launch(int S, int64_t items, const BlobHeader &h) {
 // test hook (mab_debug_set_min_band_class): 1 runs class-0 items on the warp-per-item kernel, 2 everything on the
 // shared-memory-ring kernels; results must not depend on it
 int g_min_band_class = 0;
-#define RR_LA_DEFAULT 1
-#define RR_MINB_DEFAULT 6
-int g_la_variant = getenv("MAB_LA") ? atoi(getenv("MAB_LA")) : -1;  // experiment switch, see run_dp
+#define RR_LA_DEFAULT 1    // |x - y| logAdd (wavefront_reg.cuh); measured against la_bf and four other coefficient
+#define RR_MINB_DEFAULT 6  // fetches (profiles/r2_ncu_summary.md): 53.5 / 52.0 ms per 1 M tRNA reads at 6 blocks per SM
 
 // register-resident kernels (wavefront_reg.cuh): resident blocks per SM from the occupancy calculator, once per kernel
 template <typename K>
@@ -1202,15 +1119,6 @@ int run_dp(const DevModel &dm, const mab_plan *plan, const Blob &bl, const Works
     if (nR0 > 0) {
         LaunchTimer lt(K_FORWARD, st);
         auto k = k_forward_rr<S, FULL, 16, LA, MB>;
-        if constexpr (S == 5 && !FULL) {  // experiment switch (MAB_LA = 10 * minBlocks + LA)
-            if (g_la_variant == 40) k = k_forward_rr<S, FULL, 16, 0, 4>;
-            if (g_la_variant == 41) k = k_forward_rr<S, FULL, 16, 1, 4>;
-            if (g_la_variant == 50) k = k_forward_rr<S, FULL, 16, 0, 5>;
-            if (g_la_variant == 51) k = k_forward_rr<S, FULL, 16, 1, 5>;
-            if (g_la_variant == 60) k = k_forward_rr<S, FULL, 16, 0, 6>;
-            if (g_la_variant == 61) k = k_forward_rr<S, FULL, 16, 1, 6>;
-            if (g_la_variant == 71) k = k_forward_rr<S, FULL, 16, 1, 7>;
-        }
         k<<<rr_grid(k, nR0, 2 * WPB), RR_THREADS, 0, st>>>(dm, bl, nR2 + nR1, nR2 + nR1 + nR0, w.fwd, w.fwd_tot,
                                                           w.counters + 9);
     }
@@ -1222,15 +1130,6 @@ int run_dp(const DevModel &dm, const mab_plan *plan, const Blob &bl, const Works
     if (nT0 > 0) {
         LaunchTimer lt(K_BACKWARD, st);
         auto k = k_backward_rr<S, FULL, 16, LA, MB>;
-        if constexpr (S == 5 && !FULL) {
-            if (g_la_variant == 40) k = k_backward_rr<S, FULL, 16, 0, 4>;
-            if (g_la_variant == 41) k = k_backward_rr<S, FULL, 16, 1, 4>;
-            if (g_la_variant == 50) k = k_backward_rr<S, FULL, 16, 0, 5>;
-            if (g_la_variant == 51) k = k_backward_rr<S, FULL, 16, 1, 5>;
-            if (g_la_variant == 60) k = k_backward_rr<S, FULL, 16, 0, 6>;
-            if (g_la_variant == 61) k = k_backward_rr<S, FULL, 16, 1, 6>;
-            if (g_la_variant == 71) k = k_backward_rr<S, FULL, 16, 1, 7>;
-        }
         k<<<rr_grid(k, nT0, 2 * WPB), RR_THREADS, 0, st>>>(dm, bl, nT2 + nT1, nT2 + nT1 + nT0, w.bwd, w.bwd_tot, w.edge,
                                                           w.counters + 11);
     }

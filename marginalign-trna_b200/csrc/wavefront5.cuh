@@ -34,7 +34,8 @@ __constant__ double c_la_coef[16] = {
     (double) -0.004605031767994f, (double) 0.063427417320019f, (double) 0.695956496475118f, (double) 0.514272634594009f,
     (double) -0.000458661602210f, (double) 0.009695946122598f, (double) 0.930734667215156f, (double) 0.168037164329057f};
 
-enum CoefMode { COEF_CONST = 0, COEF_SMEM = 1, COEF_MIXED = 2 };
+enum CoefMode { COEF_SMEM = 1 };  // coefficients from a replicated shared-memory table (the constant bank and a mixed
+                                  // fetch were measured slower in round 1 and removed)
 
 #define W5_COPIES 8  // table replicas: lane l reads replica (l & 7), so the 8 lanes of a quarter-warp (one LDS.128
                      // phase) always hit 8 different 16-byte bank groups, whatever rows they index
@@ -64,29 +65,16 @@ __device__ __forceinline__ double la_bf(double x, double y, unsigned coef_addr) 
     const double lo = lt ? x : y;
     const double d = __dsub_rn(hi, lo);  // +inf if lo = -inf, NaN if both are -inf: both fail (d < 7.5) below
     double c3, c2, c1, c0;
-    if (CM == COEF_CONST) {
-        const int piece = (d > 1.00 ? 1 : 0) + (d > 2.50 ? 1 : 0) + (d > 4.50 ? 1 : 0);
-        c3 = c_la_coef[piece * 4];
-        c2 = c_la_coef[piece * 4 + 1];
-        c1 = c_la_coef[piece * 4 + 2];
-        c0 = c_la_coef[piece * 4 + 3];
-    } else {
+    {
         unsigned a = coef_addr;  // three predicated adds pick the row
         if (d > 1.00) a += 2 * W5_COPIES * 16;
         if (d > 2.50) a += 2 * W5_COPIES * 16;
         if (d > 4.50) a += 2 * W5_COPIES * 16;
-        const double2 c32 = lds_v2(a);
+        const double2 c32 = lds_v2(a), c10 = lds_v2_128(a);
         c3 = c32.x;
         c2 = c32.y;
-        if (CM == COEF_SMEM) {
-            const double2 c10 = lds_v2_128(a);
-            c1 = c10.x;
-            c0 = c10.y;
-        } else {
-            const int piece = (int) ((a - coef_addr) >> 8);
-            c1 = c_la_coef[piece * 4 + 2];
-            c0 = c_la_coef[piece * 4 + 3];
-        }
+        c1 = c10.x;
+        c0 = c10.y;
     }
     double r = __dadd_rn(__dmul_rn(c3, d), c2);
     r = __dadd_rn(__dmul_rn(r, d), c1);

@@ -407,9 +407,9 @@ class PairHmmEngine:
         self._t_lock = threading.Lock()
 
     # ---------------------------------------------------------------- chunking
-    CHUNK_RAMP = tuple(int(d) for d in os.environ.get("MAB_CHUNK_RAMP", "4").split(",") if d)  # see _chunks
-    PLAN_AHEAD = int(os.environ.get("MAB_PLAN_AHEAD", "2"))  # chunks planned ahead of the one computing
-    BASE_CELLS = int(os.environ.get("MAB_BASE_CELLS", "400000000"))  # chunk size that pipelines well for short reads (tRNA: ~140 k alignments per chunk)
+    CHUNK_RAMP = (4,)         # the first chunk is a quarter of the others, see _chunks
+    PLAN_AHEAD = 2            # chunks planned ahead of the one computing
+    BASE_CELLS = 400_000_000  # chunk size that pipelines well for short reads (tRNA: ~140 k alignments per chunk)
 
     def _auto_max_cells(self, mean_est, params, expectations):
         """Chunk size when the caller gave none.  The forward sweep of one region is sequential over its diagonals, so
@@ -615,7 +615,7 @@ class PairHmmEngine:
         self.last_stats = stats
         return PosteriorPairs(offsets, blocks=blocks)
 
-    PAIRS_PER_CELL_CAP = float(os.environ.get("MAB_PAIR_CAP", "0.25"))  # output capacity of the sync-free path (measured: 0.07 pairs per cell at threshold 0.01)
+    PAIRS_PER_CELL_CAP = 0.25  # output capacity of the sync-free path (measured: 0.07 pairs per cell at threshold 0.01)
 
     def posteriors_async(self, model, dplan):
         """posteriors_device without the host sync: outputs are sized by a bound (PAIRS_PER_CELL_CAP x cells; the emit
@@ -661,76 +661,10 @@ class PairHmmEngine:
         return total
 
     def get_aligned_pairs_using_anchors(self, model, batch, params=None):
-        """Posterior match probabilities of every alignment of `batch` (host in, host out).
-
-        Software-pipelined by one chunk: the kernels of chunk k+1 are queued before the host waits for the pair count
-        of chunk k, sizes its pinned blocks and starts their D2H copies on the copy stream, so the GPU never waits for
-        the host."""
-        # Default: one host sync per chunk (the pair count).  The sync-free, software-pipelined variant below is what
-        # PairHmmEngine.realign builds on; for plain posteriors it measured slower (254 vs 227 ms per 1 M tRNA reads,
-        # profiles/r1_ncu_summary.md r1g), so it stays opt-in.
-        if os.environ.get("MAB_POSTERIOR_ASYNC") != "1":
-            return self._get_aligned_pairs_sync(model, batch, params)
-        params = params or AlignmentParameters()
-        torch = self.torch
-        offs, blocks = [np.zeros(1, dtype=np.int64)], []
-        stats = dict(cells=0, regions=0, diagonals=0, h2d_bytes=0, d2h_bytes=0, chunks=0)
-        pending = []  # D2H copies in flight: (first alignment, n alignments, pinned tensors, event, device tensors)
-
-        def start_copy(st, a0):
-            t1 = time.perf_counter()
-            total = self.posteriors_settle(st)
-            dev = (st["d_off"], st["d_x"][:total], st["d_y"][:total], st["d_p"][:total])
-            host = [torch.empty(t.shape, dtype=t.dtype, pin_memory=True) for t in dev]
-            done = torch.cuda.Event()
-            done.record(torch.cuda.current_stream(self.device))
-            with torch.cuda.stream(self._copy_stream):
-                self._copy_stream.wait_event(done)
-                for h, t in zip(host, dev):
-                    h.copy_(t, non_blocking=True)
-                    t.record_stream(self._copy_stream)
-                ev = torch.cuda.Event()
-                ev.record(self._copy_stream)
-            pending.append((a0, st["n"], host, ev, dev))
-            st["dplan"] = None
-            self._t["host_alloc_s"] += time.perf_counter() - t1
-
-        first, prev = 0, None
-        with torch.cuda.device(self.device):
-            for k in self._t:
-                self._t[k] = 0.0
-            for dplan in self._device_plans(batch, params, False):
-                info = dplan.plan.info
-                t0 = time.perf_counter()
-                st = self.posteriors_async(model, dplan)
-                self._t["compute_s"] += time.perf_counter() - t0
-                if prev is not None:
-                    start_copy(*prev)
-                prev = (st, first)
-                first += info.n_alignments
-                stats["cells"] += info.n_cells
-                stats["regions"] += info.n_regions
-                stats["diagonals"] += info.n_diagonals
-                stats["h2d_bytes"] += dplan.h2d_bytes
-                stats["chunks"] += 1
-                del dplan, st
-            if prev is not None:
-                start_copy(*prev)
-                prev = None
-            t_drain = time.perf_counter()
-            for a0, na, host, ev, _keep in pending:
-                ev.synchronize()
-                off = host[0].numpy()
-                base = int(offs[-1][-1])
-                offs.append(off[1:] + base)
-                blocks.append((a0, a0 + na, base, host[1].numpy(), host[2].numpy(), host[3].numpy()))
-                stats["d2h_bytes"] += sum(h.numel() * h.element_size() for h in host)
-            self._t["drain_s"] = time.perf_counter() - t_drain
-        stats["host_wall"] = dict(self._t)
-        if not blocks:
-            blocks = [(0, 0, 0, np.zeros(0, np.int32), np.zeros(0, np.int32), np.zeros(0, np.int32))]
-        self.last_stats = stats
-        return PosteriorPairs(np.concatenate(offs), blocks=blocks)
+        """Posterior match probabilities of every alignment of `batch` (host in, host out): one host sync per chunk
+        (the pair count).  (A sync-free variant with bound-sized outputs -- what PairHmmEngine.realign builds on --
+        measured slower for plain posteriors, profiles/r1_ncu_summary.md r1g, and was removed.)"""
+        return self._get_aligned_pairs_sync(model, batch, params)
 
     # ---------------------------------------------------------------- expectations
     def expectations_device(self, model, dplan, d_out):

@@ -83,7 +83,7 @@ def test_em_ten_iterations_match_the_oracle(tmp_path, model_type, start):
 
 def test_config2_on_the_two_alignments_of_input_sam(tmp_path, golden):
     """BASELINE config 2 as worded: fiveStateAsymmetric, 10 iterations from the shipped model, on the two alignments of
-    the reference's tests/input.sam (golden cases fixture0 / fixture1: 1751- and 6222-nt reads, ~210 k cells per
+    the reference's tests/input.sam (golden cases fixture0 / fixture1: 1751- and 6222-nt reads, ~190 k cells per
     iteration), expansion 10, split 300, trainEmissions."""
     cs = [next(c for c in golden.cases if c["name"] == n) for n in ("fixture0_realign", "fixture1_realign")]
     b = mab.AlignmentBatch.from_lists([c["x"] for c in cs], [c["y"] for c in cs], [(c["ops"], c["lens"]) for c in cs])
@@ -94,7 +94,7 @@ def test_config2_on_the_two_alignments_of_input_sam(tmp_path, golden):
     np.testing.assert_allclose(got.runningLikelihoods, running, rtol=RTOL)
     np.testing.assert_allclose(got.transitions, want.transitions, rtol=RTOL, atol=1e-300)
     np.testing.assert_allclose(got.emissions, want.emissions, rtol=RTOL, atol=1e-300)
-    assert engine_cells(b) > 200_000
+    assert engine_cells(b) > 150_000
 
 
 def engine_cells(b):
