@@ -184,6 +184,8 @@ struct Blob {
     const uint8_t *sym_x, *sym_y;
     const int32_t *order_fwd, *order_bwd, *diag_region;
     const int64_t *aln_region;
+    const uint32_t *pack_x, *pack_y;      // 2-bit codes + N mask (BlobHeader::off_pack_x)
+    int64_t h_len_sym_x, h_len_sym_y;
 };
 
 __host__ __device__ inline Blob blob_view(const void *base, const BlobHeader &h) {
@@ -200,6 +202,10 @@ __host__ __device__ inline Blob blob_view(const void *base, const BlobHeader &h)
     v.order_bwd = (const int32_t *) (b + h.off_order_bwd);
     v.aln_region = (const int64_t *) (b + h.off_aln_region);
     v.diag_region = (const int32_t *) (b + h.off_diag_region);
+    v.pack_x = (const uint32_t *) (b + h.off_pack_x);
+    v.pack_y = (const uint32_t *) (b + h.off_pack_y);
+    v.h_len_sym_x = h.len_sym_x;
+    v.h_len_sym_y = h.len_sym_y;
     return v;
 }
 

@@ -80,7 +80,10 @@ struct BlobHeader {  // 256 bytes
     // longest first.  The register-resident wavefront kernels take classes 0 and 1, the shared-memory-ring kernels 2.
     int64_t n_class_regions[3];
     int64_t n_class_tbs[3];
-    int64_t pad[2];
+    // 2-bit packed symbols + N mask of the concatenated X / Y sequences (symbol_convertStringToSymbols,
+    // pairwiseAligner.c:281-289, as bits): uint32 words, mab_pack_words(len) of them per sequence -- first the 2-bit
+    // codes, 16 bases per word, then the N mask, 32 bases per word (1 = not ACGT); base i at position i + 256
+    int64_t off_pack_x, off_pack_y;
 };
 static_assert(sizeof(BlobHeader) == 256, "BlobHeader must be 256 bytes");
 
@@ -111,6 +114,13 @@ static_assert(sizeof(RegionDesc) == 64, "RegionDesc must be 64 bytes");
 MAB_HDI int mab_region_span(int32_t flags) { return (int) (((uint32_t) flags >> MAB_SPAN_SHIFT) & MAB_SPAN_MAX); }
 // 0: fits a half-warp (16 lanes), 1: fits a warp (32 lanes), 2: wider (shared-memory ring kernels)
 MAB_HDI int mab_band_class(int span) { return span <= 30 ? 0 : (span <= 62 ? 1 : 2); }
+
+// packed-symbol arrays: code words, then mask words; base i sits at bit position i + MAB_PACK_PAD_BASES and the same
+// pad follows the last base, so that a 128-base window may start anywhere around the sequence
+#define MAB_PACK_PAD_BASES 256
+MAB_HDI int64_t mab_pack_code_words(int64_t len) { return (len + 2 * MAB_PACK_PAD_BASES + 15) / 16; }
+MAB_HDI int64_t mab_pack_mask_words(int64_t len) { return (len + 2 * MAB_PACK_PAD_BASES + 31) / 32; }
+MAB_HDI int64_t mab_pack_words(int64_t len) { return mab_pack_code_words(len) + mab_pack_mask_words(len); }
 
 #define MAB_DIAG_NO_MIDDLE 0x80000000u  // forward diagonal xay-2 was already freed when the reference visits xay
 #define MAB_DIAG_IS_TOTAL 0x40000000u   // a total probability is evaluated ON this diagonal (index = its own total)
@@ -157,6 +167,7 @@ struct mab_plan {
     std::vector<TracebackDesc> tbs;
     std::vector<TotalDesc> totals;
     std::vector<uint8_t> sym_x, sym_y;
+    std::vector<uint32_t> pack_x, pack_y;  // see BlobHeader::off_pack_x
     std::vector<int32_t> order_fwd, order_bwd, diag_region;
     std::vector<int64_t> aln_region;
     // kept for introspection only

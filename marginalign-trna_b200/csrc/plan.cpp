@@ -302,6 +302,17 @@ int build_plan(const mab_params *p, const BatchInput &in, int n_threads, mab_pla
     plan->sym_y.resize(lenY);
     for (int64_t i = 0; i < lenX; i++) plan->sym_x[i] = symbol_of(in.seq_x[i]);
     for (int64_t i = 0; i < lenY; i++) plan->sym_y[i] = symbol_of(in.seq_y[i]);
+    auto pack = [](const std::vector<uint8_t> &sym, std::vector<uint32_t> &out) {
+        const int64_t len = (int64_t) sym.size(), cw = mab_pack_code_words(len);
+        out.assign(mab_pack_words(len), 0);
+        for (int64_t i = 0; i < len; i++) {
+            const int64_t p = i + MAB_PACK_PAD_BASES;
+            if (sym[i] < 4) out[p >> 4] |= (uint32_t) sym[i] << (2 * (p & 15));
+            else out[cw + (p >> 5)] |= 1u << (p & 31);
+        }
+    };
+    pack(plan->sym_x, plan->pack_x);
+    pack(plan->sym_y, plan->pack_y);
 
     plan->diag_region.assign(nD + 1, -1);
     for (int64_t r = 0; r < nR; r++) {
@@ -356,6 +367,8 @@ int build_plan(const mab_params *p, const BatchInput &in, int n_threads, mab_pla
     // one guard byte before and after each symbol array: the wavefront kernels read X[-1] / X[lX] (and ignore it)
     h.off_sym_x = place(lenX + 32) + 16;
     h.off_sym_y = place(lenY + 32) + 16;
+    h.off_pack_x = place(mab_pack_words(lenX) * 4);
+    h.off_pack_y = place(mab_pack_words(lenY) * 4);
     h.off_order_fwd = place(nR * 4);
     h.off_order_bwd = place(nT * 4);
     h.off_aln_region = place((in.n + 1) * 8);
@@ -458,6 +471,8 @@ extern "C" int mab_plan_write_blob(const mab_plan *plan, void *dst, int64_t dst_
     put(h.off_totals, plan->totals.data(), plan->totals.size() * sizeof(TotalDesc));
     put(h.off_sym_x, plan->sym_x.data(), plan->sym_x.size());
     put(h.off_sym_y, plan->sym_y.data(), plan->sym_y.size());
+    put(h.off_pack_x, plan->pack_x.data(), plan->pack_x.size() * 4);
+    put(h.off_pack_y, plan->pack_y.data(), plan->pack_y.size() * 4);
     put(h.off_order_fwd, plan->order_fwd.data(), plan->order_fwd.size() * 4);
     put(h.off_order_bwd, plan->order_bwd.data(), plan->order_bwd.size() * 4);
     put(h.off_aln_region, plan->aln_region.data(), plan->aln_region.size() * 8);

@@ -308,6 +308,25 @@ __global__ void k_symbols(const uint8_t *seq, int64_t n, uint8_t *sym /* 16 guar
     if (i < n) sym[i] = plan_core::symbol_of(seq[i]);
 }
 
+// 2-bit codes + N mask (BlobHeader::off_pack_x): one thread per mask word = 32 bases = two code words
+__global__ void k_pack_symbols(const uint8_t *seq, int64_t n, uint32_t *pack) {
+    const int64_t cw = mab_pack_code_words(n), mw = mab_pack_mask_words(n);
+    const int64_t t = (int64_t) blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= mw) return;
+    uint32_t c0 = 0, c1 = 0, m = 0;
+    for (int i = 0; i < 32; i++) {
+        const int64_t b = t * 32 + i - MAB_PACK_PAD_BASES;  // position t * 32 + i holds base b
+        if (b < 0) continue;
+        if (b >= n) break;
+        const uint32_t s = plan_core::symbol_of(seq[b]);
+        if (s < 4) (i < 16 ? c0 : c1) |= s << (2 * (i & 15));
+        else m |= 1u << i;
+    }
+    if (2 * t < cw) pack[2 * t] = c0;
+    if (2 * t + 1 < cw) pack[2 * t + 1] = c1;
+    pack[cw + t] = m;
+}
+
 __global__ void k_iota(int32_t *v, int64_t n) {
     const int64_t i = (int64_t) blockIdx.x * blockDim.x + threadIdx.x;
     if (i < n) v[i] = (int32_t) i;
@@ -346,7 +365,7 @@ extern "C" int64_t mab_plan_device_arena_hint(const mab_params *p, int64_t n, in
     (void) p;
     const int64_t nR = n + n / 8 + 64, nD = len_x + len_y + 2 * nR;
     const int64_t nT = nR + nD / 900 + 64, nTot = nD / 10 + nT + 64;
-    return 4096 + 8 * (n + 2) * 2 + (len_x + len_y + 1024) + nR * (64 + 64 + 8 * 2 + 40 * 2 + 4 * 6) + (nD + 1) * 16 +
+    return 4096 + 8 * (n + 2) * 2 + (len_x + len_y + 1024) + nR * (64 + 64 + 8 * 2 + 40 * 2 + 4 * 6) + (nD + 1) * 16 + (len_x + len_y) / 2 + 4096 +
            nT * (32 + 4 * 6) + nTot * 16 + (int64_t) 64 * 1024 * 1024 / 8 + (nR + nT) * 8;
 }
 
@@ -386,6 +405,8 @@ extern "C" int mab_plan_build_device(const mab_params *p, int64_t n, const uint8
     h.off_aln_region = ar.place((n + 1) * 8);
     h.off_sym_x = ar.place(len_x + 32) + 16;
     h.off_sym_y = ar.place(len_y + 32) + 16;
+    h.off_pack_x = ar.place(mab_pack_words(len_x) * 4);
+    h.off_pack_y = ar.place(mab_pack_words(len_y) * 4);
     size_t scan_tmp1 = 0;
     cub::DeviceScan::ExclusiveSum(nullptr, scan_tmp1, (int64_t *) nullptr, (int64_t *) nullptr, n + 1, st);
     const int64_t at_tmp1 = ar.place((int64_t) scan_tmp1);
@@ -402,6 +423,8 @@ extern "C" int mab_plan_build_device(const mab_params *p, int64_t n, const uint8
     {  // also for empty inputs: the guard bytes must be set
         k_symbols<<<grid(std::max<int64_t>(len_x, 16), 256), 256, 0, st>>>(d_seq_x, len_x, ar.ptr<uint8_t>(h.off_sym_x));
         k_symbols<<<grid(std::max<int64_t>(len_y, 16), 256), 256, 0, st>>>(d_seq_y, len_y, ar.ptr<uint8_t>(h.off_sym_y));
+        k_pack_symbols<<<grid(mab_pack_mask_words(len_x), 256), 256, 0, st>>>(d_seq_x, len_x, ar.ptr<uint32_t>(h.off_pack_x));
+        k_pack_symbols<<<grid(mab_pack_mask_words(len_y), 256), 256, 0, st>>>(d_seq_y, len_y, ar.ptr<uint32_t>(h.off_pack_y));
     }
     cub::DeviceScan::ExclusiveSum(ar.ptr<void>(at_tmp1), scan_tmp1, d_aln_region, d_aln_region, n + 1, st);
     Status hs;

@@ -198,6 +198,144 @@ __device__ __forceinline__ void reg_backward_cell(const DevModel &m, const RegLa
 
 #define RR_THREADS 128
 
+// ------------------------------------------------------------------------------------------------ staging (N1)
+// Band descriptors: the DiagDesc entries of the item being swept are staged in shared memory by the TMA engine
+// (cp.async.bulk, completion on an mbarrier) in windows of RR_DWIN diagonals, two windows per group: while the sweep
+// reads one window the next one (in sweep direction) is in flight, so no global load sits on the sequential path.
+// Symbols: the sequences live in HBM as 2-bit codes + an N mask (BlobHeader::off_pack_x); every RR_SYM_REFRESH
+// diagonals the group unpacks the 128 bases its band can reach in that stretch (the band edges move by at most one
+// base per diagonal) into a byte ring with coalesced 32-bit loads, and the per-cell symbol fetch is one LDS.U8.
+#define RR_DWIN 64
+#define RR_SYM_RING 128
+#define RR_SYM_REFRESH 32
+
+struct __align__(16) RegStage {
+    DiagDesc ring[2 * RR_DWIN];
+    unsigned long long bar[2];
+    uint8_t sx[RR_SYM_RING], sy[RR_SYM_RING];
+};
+
+__device__ __forceinline__ void mbar_init(unsigned bar, int count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count));
+}
+__device__ __forceinline__ void mbar_expect_tx(unsigned bar, unsigned bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void bulk_g2s(unsigned dst, const void *src, unsigned bytes, unsigned bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(dst),
+                 "l"(src), "r"(bytes), "r"(bar)
+                 : "memory");
+}
+__device__ __forceinline__ void mbar_wait(unsigned bar, unsigned parity) {
+    unsigned done;
+    do {
+        asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.b32 %0, 1, 0, p;\n\t}"
+                     : "=r"(done)
+                     : "r"(bar), "r"(parity)
+                     : "memory");
+    } while (!done);
+}
+
+// The staged descriptor stream of one item.  Entries are read in one direction (DIR = +1 forward, -1 backward), one
+// per diagonal; window k = entries [64 k, 64 k + 64) lives in slot k & 1.
+template <int LPI, int DIR>
+struct DescStream {
+    const DiagDesc *g;      // region's first entry in global memory
+    int n_ent;              // entries of the region that exist (lX + lY + 2)
+    int k_last;             // last window the sweep will enter
+    unsigned ring, bar;     // shared addresses of ring[0] / bar[0]
+    unsigned gmask;
+    unsigned phase;         // bit s = parity the next wait on slot s uses
+    bool leader;
+
+    __device__ __forceinline__ void issue(int k) {
+        if (leader) {
+            const int first = k * RR_DWIN, cnt = min(RR_DWIN, n_ent - first);
+            const unsigned slot = k & 1, bytes = (unsigned) cnt * (unsigned) sizeof(DiagDesc);
+            asm volatile("fence.proxy.async.shared::cta;" ::: "memory");  // earlier generic reads of the slot vs the async write
+            mbar_expect_tx(bar + 8 * slot, bytes);
+            bulk_g2s(ring + slot * RR_DWIN * (unsigned) sizeof(DiagDesc), g + first, bytes, bar + 8 * slot);
+        }
+    }
+    __device__ __forceinline__ void wait(int k) {
+        const unsigned slot = k & 1;
+        mbar_wait(bar + 8 * slot, (phase >> slot) & 1);
+        phase ^= 1u << slot;
+    }
+    // first entry index `i0`; the sweep will read down / up to entry `i_end` inclusive
+    __device__ __forceinline__ void open(const DiagDesc *g_, int n_ent_, int i0, int i_end) {
+        g = g_;
+        n_ent = n_ent_;
+        k_last = i_end / RR_DWIN;
+        const int k0 = i0 / RR_DWIN;
+        __syncwarp(gmask);  // every lane is done with the previous item's windows
+        issue(k0);
+        if (k0 != k_last) issue(k0 + DIR);
+        wait(k0);
+    }
+    // entry i; must be called with i moving by DIR each time (any entry may be read again while its window is current)
+    __device__ __forceinline__ DiagDesc get(int i, bool entering) {
+        if (entering) {  // first entry of a new window in sweep direction
+            const int k = i / RR_DWIN;
+            wait(k);
+            __syncwarp(gmask);  // the other slot (window k - DIR) is fully consumed by every lane
+            if (k != k_last) issue(k + DIR);
+        }
+        DiagDesc d;
+        const unsigned a = ring + (unsigned) (i & (2 * RR_DWIN - 1)) * (unsigned) sizeof(DiagDesc);
+        asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];"
+                     : "=r"(((uint32_t *) &d)[0]), "=r"(((uint32_t *) &d)[1]), "=r"(((uint32_t *) &d)[2]),
+                       "=r"(((uint32_t *) &d)[3])
+                     : "r"(a));
+        return d;
+    }
+};
+
+// Unpacks bases [b0, b0 + 128) of a region (b0 a multiple of 8; region-local, valid range [0, len)) into a byte ring
+// (base b at ring[b & 127]; 4 = N or outside the sequence).  pack: the region's sequence array (BlobHeader::off_pack_x),
+// off: global index of the region's base 0.
+template <int LPI>
+__device__ __forceinline__ void unpack_symbols(const uint32_t *__restrict__ pack, int64_t cw, int64_t off, int len, int b0,
+                                               int lane, unsigned ring) {
+    constexpr int K = RR_SYM_RING / LPI;  // bases per lane: 8 (half-warp) or 4 (warp)
+    const int b = b0 + lane * K;
+    const int64_t p = off + b + MAB_PACK_PAD_BASES;  // position in the padded arrays (>= 0: b0 >= -MAB_PACK_PAD_BASES)
+    const uint32_t c0 = pack[p >> 4], c1 = pack[(p >> 4) + 1];
+    const uint32_t m0 = pack[cw + (p >> 5)], m1 = pack[cw + (p >> 5) + 1];
+    const uint32_t v = __funnelshift_r(c0, c1, (unsigned) (p & 15) * 2);
+    uint32_t n = __funnelshift_r(m0, m1, (unsigned) (p & 31));
+    const int lo = min(max(-b, 0), K), hi = min(max(len - b, 0), K);
+    const uint32_t valid = hi > lo ? (((1u << hi) - 1u) & ~((1u << lo) - 1u)) : 0u;
+    n = (n | ~valid) & ((1u << K) - 1u);
+    uint32_t out[K / 4];
+#pragma unroll
+    for (int q = 0; q < K / 4; q++) {
+        uint32_t t = (v >> (8 * q)) & 0xFFu;
+        t = (t | (t << 12)) & 0x000F000Fu;
+        t = (t | (t << 6)) & 0x03030303u;
+        const uint32_t nb = (((n >> (4 * q)) & 0xFu) * 0x00204081u) & 0x01010101u;
+        out[q] = (t & ~(nb * 3u)) | (nb << 2);
+    }
+    const unsigned a = ring + (unsigned) (b & (RR_SYM_RING - 1));
+    if (K == 8) asm volatile("st.shared.v2.b32 [%0], {%1, %2};" ::"r"(a), "r"(out[0]), "r"(out[K / 4 - 1]) : "memory");
+    else asm volatile("st.shared.b32 [%0], %1;" ::"r"(a), "r"(out[0]) : "memory");
+}
+
+__device__ __forceinline__ int lds_u8(unsigned addr) {
+    unsigned v;
+    asm volatile("ld.shared.u8 %0, [%1];" : "=r"(v) : "r"(addr));
+    return (int) v;
+}
+
+// per-block setup of the staging area: one mbarrier pair per group
+template <int LPI>
+__device__ __forceinline__ void stage_init(RegStage *stage) {
+    constexpr int GROUPS = RR_THREADS / LPI;
+    if (threadIdx.x < 2 * GROUPS)
+        mbar_init((unsigned) __cvta_generic_to_shared(&stage[threadIdx.x >> 1].bar[threadIdx.x & 1]), 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+}
+
 // ------------------------------------------------------------------------------------------------ forward
 // Work items: order_fwd[item0 .. item1).  Outputs exactly what k_forward writes (F match plane + FT on total diagonals,
 // or all states when FULL).
@@ -207,21 +345,31 @@ k_forward_rr(const __grid_constant__ DevModel model, Blob bl, int item0, int ite
              double *__restrict__ FT, int *counter) {
     __shared__ RegTables tb;
     __shared__ __align__(16) CoefTable ct;
+    __shared__ RegStage stage[RR_THREADS / LPI];
     fill_reg_tables(tb, model, threadIdx.x, blockDim.x);
     fill_coef_table(ct, threadIdx.x, blockDim.x);
+    stage_init<LPI>(stage);
     __syncthreads();
     const RegLane ln = reg_lane<LPI>(tb, ct);
     const int lane32 = threadIdx.x & 31;
     const double NINF = neg_inf();
+    RegStage &sg = stage[threadIdx.x / LPI];
+    DescStream<LPI, +1> ds;
+    ds.ring = (unsigned) __cvta_generic_to_shared(&sg.ring[0]);
+    ds.bar = (unsigned) __cvta_generic_to_shared(&sg.bar[0]);
+    ds.gmask = ln.gmask;
+    ds.phase = 0;
+    ds.leader = ln.lane == 0;
+    const unsigned sxr = (unsigned) __cvta_generic_to_shared(&sg.sx[0]), syr = (unsigned) __cvta_generic_to_shared(&sg.sy[0]);
+    const int64_t cwx = mab_pack_code_words(bl.h_len_sym_x), cwy = mab_pack_code_words(bl.h_len_sym_y);
 
     for (;;) {
         const int item = item0 + next_item_sub<LPI>(counter, lane32, ln.gmask);
         if (item >= item1) break;
         const RegionDesc rg = bl.regions[bl.order_fwd[item]];
-        const DiagDesc *dd = bl.diags + rg.diag_base;
-        const uint8_t *sx = bl.sym_x + rg.sym_x_off, *sy = bl.sym_y + rg.sym_y_off;
         const int D = rg.lX + rg.lY;
-        DiagDesc cur = dd[0], nxt = dd[1];
+        ds.open(bl.diags + rg.diag_base, D + 2, 0, D + 1);
+        DiagDesc cur = ds.get(0, false), nxt = ds.get(1, false);
         Cell<S> a, b = cell_fill<S>(NINF);
         {  // diagonal 0: (ragged)startStateProb on every cell, pairwiseAligner.c:658-659
             const double *init = (rg.flags & 1) ? model.ragged_start : model.start;
@@ -237,12 +385,22 @@ k_forward_rr(const __grid_constant__ DevModel model, Blob bl, int item0, int ite
         auto step = [&](auto q_tag, int d, const Cell<S> &p1, Cell<S> &p2) {
             constexpr int Q = decltype(q_tag)::value;
             cur = nxt;
-            nxt = dd[d + 1];
-            const RegGeom g = reg_geom<LPI>(ln.lane, d, cur.xmyL, (int) (nxt.cell_off - cur.cell_off));
+            nxt = ds.get(d + 1, ((d + 1) & (RR_DWIN - 1)) == 0);
+            const int w = (int) (nxt.cell_off - cur.cell_off);
+            if (((d - 1) & (RR_SYM_REFRESH - 1)) == 0) {
+                // the cells of diagonals d .. d + 31 consume X[x - 1], Y[y - 1] with x >= x_lo(d), y >= y_lo(d) and
+                // at most 31 + band width beyond them: refresh the rings from one base before those
+                const int x_lo = (d + cur.xmyL) >> 1, y_lo = (d - (cur.xmyL + 2 * (w - 1))) >> 1;
+                __syncwarp(ln.gmask);
+                unpack_symbols<LPI>(bl.pack_x, cwx, rg.sym_x_off, rg.lX, (x_lo - 1) & ~7, ln.lane, sxr);
+                unpack_symbols<LPI>(bl.pack_y, cwy, rg.sym_y_off, rg.lY, (y_lo - 1) & ~7, ln.lane, syr);
+                __syncwarp(ln.gmask);
+            }
+            const RegGeom g = reg_geom<LPI>(ln.lane, d, cur.xmyL, w);
             int cX = 5, cY = 5;
-            if (g.active) {
-                cX = g.x > 0 ? sx[g.x - 1] : 4;
-                cY = g.y > 0 ? sy[g.y - 1] : 4;
+            if (g.active) {  // position -1 (x = 0 or y = 0) unpacks as N, like the reference's `x > 0 ? sX[x-1] : n`
+                cX = lds_u8(sxr + ((g.x - 1) & (RR_SYM_RING - 1)));
+                cY = lds_u8(syr + ((g.y - 1) & (RR_SYM_RING - 1)));
             }
             const double em = lds_f64(ln.em_addr + (cX * 5 + cY) * (RR_REPL * 8));
             const double ex = lds_f64(ln.ex_addr + cX * (RR_REPL * 8));
@@ -275,23 +433,34 @@ k_backward_rr(const __grid_constant__ DevModel model, Blob bl, int item0, int it
               double *__restrict__ BT, double *__restrict__ edge, int *counter) {
     __shared__ RegTables tb;
     __shared__ __align__(16) CoefTable ct;
+    __shared__ RegStage stage[RR_THREADS / LPI];
     fill_reg_tables(tb, model, threadIdx.x, blockDim.x);
     fill_coef_table(ct, threadIdx.x, blockDim.x);
+    stage_init<LPI>(stage);
     __syncthreads();
     const RegLane ln = reg_lane<LPI>(tb, ct);
     const int lane32 = threadIdx.x & 31;
     const double NINF = neg_inf();
+    RegStage &sg = stage[threadIdx.x / LPI];
+    DescStream<LPI, -1> ds;
+    ds.ring = (unsigned) __cvta_generic_to_shared(&sg.ring[0]);
+    ds.bar = (unsigned) __cvta_generic_to_shared(&sg.bar[0]);
+    ds.gmask = ln.gmask;
+    ds.phase = 0;
+    ds.leader = ln.lane == 0;
+    const unsigned sxr = (unsigned) __cvta_generic_to_shared(&sg.sx[0]), syr = (unsigned) __cvta_generic_to_shared(&sg.sy[0]);
+    const int64_t cwx = mab_pack_code_words(bl.h_len_sym_x), cwy = mab_pack_code_words(bl.h_len_sym_y);
 
     for (;;) {
         const int item = item0 + next_item_sub<LPI>(counter, lane32, ln.gmask);
         if (item >= item1) break;
         const TracebackDesc t = bl.tbs[bl.order_bwd[item]];
         const RegionDesc rg = bl.regions[t.region];
-        const DiagDesc *dd = bl.diags + rg.diag_base;
-        const uint8_t *sx = bl.sym_x + rg.sym_x_off, *sy = bl.sym_y + rg.sym_y_off;
         const int lX = rg.lX, lY = rg.lY;
-        DiagDesc cur = dd[t.hi], nxt = dd[t.hi - 1];  // hi >= 1 always
-        int64_t c_above = dd[t.hi + 1].cell_off;      // first cell of the diagonal after `cur`
+        ds.open(bl.diags + rg.diag_base, lX + lY + 2, t.hi + 1, t.lo);
+        int64_t c_above = ds.get(t.hi + 1, false).cell_off;  // first cell of the diagonal after `cur`
+        DiagDesc cur = ds.get(t.hi, (t.hi & (RR_DWIN - 1)) == RR_DWIN - 1);
+        DiagDesc nxt = ds.get(t.hi - 1, ((t.hi - 1) & (RR_DWIN - 1)) == RR_DWIN - 1);  // hi >= 1 always
         Cell<S> a, b = cell_fill<S>(NINF);
         auto store = [&](int d, const DiagDesc &dg, const RegGeom &g, const Cell<S> &c) {
             if (!g.active) return;
@@ -314,16 +483,27 @@ k_backward_rr(const __grid_constant__ DevModel model, Blob bl, int item0, int it
             for (int s = 0; s < S; s++) a.v[s] = g.active ? init[s] : NINF;
             store(t.hi, cur, g, a);
         }
+        const int d_first = t.hi - 1;
         auto step = [&](auto q_tag, int d, const Cell<S> &p1, Cell<S> &p2) {
             constexpr int Q = decltype(q_tag)::value;
             c_above = cur.cell_off;
             cur = nxt;
-            nxt = dd[d - 1];  // d >= 1: dd[0] exists
-            const RegGeom g = reg_geom<LPI>(ln.lane, d, cur.xmyL, (int) (c_above - cur.cell_off));
+            nxt = ds.get(d - 1, ((d - 1) & (RR_DWIN - 1)) == RR_DWIN - 1);  // d >= 1: entry 0 exists
+            const int w = (int) (c_above - cur.cell_off);
+            if (((d_first - d) & (RR_SYM_REFRESH - 1)) == 0) {
+                // the neighbours of the cells of diagonals d .. d - 31 consume X[x], Y[y] with x <= x_hi(d), y <= y_hi(d)
+                // and at most 31 + band width below them
+                const int x_hi = (d + cur.xmyL + 2 * (w - 1)) >> 1, y_hi = (d - cur.xmyL) >> 1;
+                __syncwarp(ln.gmask);
+                unpack_symbols<LPI>(bl.pack_x, cwx, rg.sym_x_off, lX, (x_hi - 100) & ~7, ln.lane, sxr);
+                unpack_symbols<LPI>(bl.pack_y, cwy, rg.sym_y_off, lY, (y_hi - 100) & ~7, ln.lane, syr);
+                __syncwarp(ln.gmask);
+            }
+            const RegGeom g = reg_geom<LPI>(ln.lane, d, cur.xmyL, w);
             int cX = 5, cY = 5;
-            if (g.active) {  // the neighbours consume X[x] and / or Y[y] (0-based); past the end they are out of band
-                cX = g.x < lX ? sx[g.x] : 4;
-                cY = g.y < lY ? sy[g.y] : 4;
+            if (g.active) {  // the neighbours consume X[x] and / or Y[y] (0-based); past the end they unpack as N
+                cX = lds_u8(sxr + (g.x & (RR_SYM_RING - 1)));
+                cY = lds_u8(syr + (g.y & (RR_SYM_RING - 1)));
             }
             const double em = lds_f64(ln.em_addr + (cX * 5 + cY) * (RR_REPL * 8));
             const double ex = lds_f64(ln.ex_addr + cX * (RR_REPL * 8));

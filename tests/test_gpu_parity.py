@@ -275,8 +275,9 @@ def _blob_arrays(raw):
              "max_width", "len_sym_x", "len_sym_y", "off_regions", "off_diags", "off_tracebacks", "off_totals",
              "off_sym_x", "off_sym_y", "off_order_fwd", "off_order_bwd", "off_aln_region", "blob_bytes", "n_edge_cells",
              "n_full_cells", "off_diag_region", "n_class_regions0", "n_class_regions1", "n_class_regions2",
-             "n_class_tbs0", "n_class_tbs1", "n_class_tbs2"]
+             "n_class_tbs0", "n_class_tbs1", "n_class_tbs2", "off_pack_x", "off_pack_y"]
     H = {k: int(h[i]) for i, k in enumerate(names)}
+    words = lambda n: (n + 512 + 15) // 16 + (n + 512 + 31) // 32  # mab_pack_words (csrc/mab_internal.h)
     cut = lambda off, nbytes: raw[off:off + nbytes]
     return H, {
         "regions": cut(H["off_regions"], H["n_regions"] * 64),
@@ -289,6 +290,8 @@ def _blob_arrays(raw):
         "order_bwd": cut(H["off_order_bwd"], H["n_tracebacks"] * 4),
         "aln_region": cut(H["off_aln_region"], (H["n_alignments"] + 1) * 8),
         "diag_region": cut(H["off_diag_region"], (H["n_diagonals"] + 1) * 4),
+        "pack_x": cut(H["off_pack_x"], words(H["len_sym_x"]) * 4),
+        "pack_y": cut(H["off_pack_y"], words(H["len_sym_y"]) * 4),
     }
 
 

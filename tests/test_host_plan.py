@@ -173,3 +173,49 @@ def test_chunker_tiles_the_batch_in_order():
                     assert sizes[-1] <= budget // 2 + int(est.max())
     eng.max_cells = 1000
     assert eng._chunks(mab.AlignmentBatch.from_lists([], [], []), P) == [(0, 0)]
+
+
+def _blob(plan):
+    raw = np.zeros(plan.info.blob_bytes, dtype=np.uint8)
+    plan.write_blob(raw.ctypes.data, raw.nbytes)
+    return raw, raw[:256].view(np.int64)
+
+
+def test_packed_symbols_match_the_symbol_codes():
+    """2-bit codes + N mask (BlobHeader::off_pack_x; symbol_convertStringToSymbols pairwiseAligner.c:281-289 as bits)
+    decode to the byte codes the other kernels read, N and lower-case bases included."""
+    b = mab.AlignmentBatch.from_lists(["ACGTNacgtnRYACGT" * 5, "TTGACCA"], ["ACGTTNNNacgtACGT" * 5, "TTGNCCA"],
+                                      [([0], [80]), ([0], [7])])
+    raw, h = _blob(mab.Plan.from_batch(b, mab.AlignmentParameters()))
+    for off_sym, off_pack, n in ((int(h[15]), int(h[30]), int(h[9])), (int(h[16]), int(h[31]), int(h[10]))):
+        sym = raw[off_sym:off_sym + n]
+        cw, mw = (n + 512 + 15) // 16, (n + 512 + 31) // 32
+        words = raw[off_pack:off_pack + 4 * (cw + mw)].view(np.uint32)
+        pos = np.arange(n) + 256
+        code = (words[pos >> 4] >> (2 * (pos & 15)).astype(np.uint32)) & 3
+        mask = (words[cw + (pos >> 5)] >> (pos & 31).astype(np.uint32)) & 1
+        assert np.array_equal(np.where(mask == 1, 4, code), sym)
+        # nothing outside the sequence is set
+        total = np.unpackbits(words.view(np.uint8)).sum()
+        assert total == np.unpackbits(code.astype(np.uint8)).sum() + mask.sum()
+
+
+def test_band_edges_move_by_at_most_one_base_per_diagonal():
+    """What the register kernels' symbol rings rely on (csrc/wavefront_reg.cuh): along a region the lowest / highest x
+    and y of the band never decrease and grow by at most one per anti-diagonal (band_construct,
+    pairwiseAligner.c:128-179: the rectangles of successive anchor pairs are nested in both coordinates)."""
+    batches = [(mab.synth.make_trna_batch(300, seed=3), mab.AlignmentParameters()),
+               (mab.synth.make_long_batch(3, read_len=3000, genome_len=40_000, seed=4),
+                mab.AlignmentParameters(split_matrix_bigger_than=300)),
+               (mab.synth.make_long_batch(2, read_len=2000, genome_len=40_000, seed=5, p_ins=0.12, p_del=0.12),
+                mab.AlignmentParameters(diagonal_expansion=20, split_matrix_bigger_than=30))]
+    for b, P in batches:
+        plan = mab.Plan.from_batch(b, P)
+        for r in range(plan.info.n_regions):
+            lo, hi = plan.band(r)
+            d = np.arange(len(lo))
+            x_lo, x_hi = (d + lo) // 2, (d + hi) // 2
+            y_lo, y_hi = (d - hi) // 2, (d - lo) // 2
+            for e in (x_lo, x_hi, y_lo, y_hi):
+                step = np.diff(e)
+                assert step.min() >= 0 and step.max() <= 1, (r, step.min(), step.max())
