@@ -4,7 +4,7 @@ EM expectations) behind the cPecanRealign call sites of marginAlign / marginCall
 The directory name is the project name and is not a valid Python identifier; import it as
 ``marginalign_trna_b200`` (a one-file alias package at the repo root) or via __graft_entry__.load_package().
 """
-from . import build, caller, capi, em, hmm, seqio, shard, synth  # noqa: F401
+from . import build, caller, capi, em, hmm, realign_sam, seqio, shard, synth  # noqa: F401
 from .hmm import Hmm  # noqa: F401
 from .pairhmm import (AlignmentParameters, DevicePlan, PairHmmEngine, PairHmmModel, Plan,  # noqa: F401
                       PosteriorPairs, RealignedCigars, jitter_table)
