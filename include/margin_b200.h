@@ -217,6 +217,10 @@ int mab_debug_set_warp_group(int warps);
  * register-resident wavefront kernels; 2: wide bands on the shared-memory-ring kernels).  cls = 1 runs class-0 items as
  * class 1, cls = 2 runs everything as class 2; 0 restores the default.  Results do not depend on it. */
 int mab_debug_set_min_band_class(int cls);
+/* Posterior mode can run backward sweep, total probabilities and posterior match probabilities fused in one kernel for
+ * band classes 0 and 1 (the reference's own loop structure, pairwiseAligner.c:695-733): on = 1.  Default 0: separate
+ * kernels, which measured faster.  Results do not depend on it (bit-identical pairs). */
+int mab_debug_set_fused_posterior(int on);
 /* Kernel launches issued by this library on the calling thread since the last reset (bench.py's gpu_launches). */
 int64_t mab_launch_count(int reset);
 /* Per-kernel timing for the roofline report: when enabled every launch is bracketed by CUDA events on its stream.

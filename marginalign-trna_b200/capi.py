@@ -76,6 +76,7 @@ SIGNATURES = {
     "mab_columns_call": (C.c_int, [vp, C.c_int64, vp, vp, vp, vp, vp]),
     "mab_debug_set_warp_group": (C.c_int, [C.c_int]),
     "mab_debug_set_min_band_class": (C.c_int, [C.c_int]),
+    "mab_debug_set_fused_posterior": (C.c_int, [C.c_int]),
     "mab_launch_count": (C.c_int64, [C.c_int]),
     "mab_kernel_timing": (C.c_int, [C.c_int]),
     "mab_kernel_count": (C.c_int, []),

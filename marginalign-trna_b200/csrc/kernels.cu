@@ -487,13 +487,15 @@ k_backward(const __grid_constant__ DevModel model, Blob bl, int n_tbs, double *_
 template <int S, bool FULL>
 __global__ void k_totals(Blob bl, int n_totals, const double *__restrict__ F, const double *__restrict__ B,
                          const double *__restrict__ FT, const double *__restrict__ BT,
-                         const double *__restrict__ edge, double *__restrict__ totals) {
+                         const double *__restrict__ edge, double *__restrict__ totals, int skip_class_le) {
     const int gt = blockIdx.x * blockDim.x + threadIdx.x;
     const int t = gt >> 2, q = gt & 3;
     if (t >= n_totals) return;
     const unsigned gmask = 0xFu << (threadIdx.x & 28);
     const TotalDesc td = bl.totals[t];
     const RegionDesc &rg = bl.regions[td.region];
+    // regions whose totals the fused backward sweep computes itself (k_backward_post_rr); uniform per 4-lane group
+    if (mab_band_class(mab_region_span(rg.flags)) <= skip_class_le) return;
     const DiagDesc *dd = bl.diags + rg.diag_base;
     const int64_t c0 = dd[td.d].cell_off, c1 = dd[td.d + 1].cell_off;
     // all states of diagonal d: from the full matrices, or from the side arrays in posterior mode
@@ -557,6 +559,7 @@ struct DiagWork {
     int64_t slot;
     uint32_t tot;  // index of the total the reference uses on this diagonal
     int x1, y1;    // region origin inside the alignment
+    int cls;       // band class of the owning region
 };
 
 __device__ __forceinline__ DiagWork diag_work(const Blob &bl, int64_t g) {
@@ -570,6 +573,7 @@ __device__ __forceinline__ DiagWork diag_work(const Blob &bl, int64_t g) {
     k.tot = cur.tot_flags & MAB_DIAG_TOT_MASK;
     k.x1 = rg.x1;
     k.y1 = rg.y1;
+    k.cls = mab_band_class(mab_region_span(rg.flags));
     k.slot = rg.diag_base;
     if (k.d >= 1) {
         const int D = rg.lX + rg.lY;
@@ -588,7 +592,7 @@ __device__ __forceinline__ DiagWork diag_work(const Blob &bl, int64_t g) {
 __global__ void __launch_bounds__(256)
 k_posterior_diag(Blob bl, int64_t n_diagonals, const double *__restrict__ F, const double *__restrict__ B,
                  const double *__restrict__ totals, double threshold, double log_reject, int32_t *__restrict__ pint,
-                 int64_t *__restrict__ counts) {
+                 int64_t *__restrict__ counts, int skip_class_le) {
     const int lane = threadIdx.x & 31;
     const int64_t warp = ((int64_t) blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     const int64_t g0 = warp * 32;
@@ -598,8 +602,13 @@ k_posterior_diag(Blob bl, int64_t n_diagonals, const double *__restrict__ F, con
     if (g0 == n_diagonals) return;        // a warp that holds only the sentinel has no cells to sweep
     const bool mine = g < n_diagonals;
     DiagWork k;
-    k.c0 = 0, k.w = 0, k.d = 0, k.xmyL = 0, k.slot = 0, k.tot = 0, k.x1 = 0, k.y1 = 0;
+    k.c0 = 0, k.w = 0, k.d = 0, k.xmyL = 0, k.slot = 0, k.tot = 0, k.x1 = 0, k.y1 = 0, k.cls = 0;
     if (mine) k = diag_work(bl, g);
+    // diagonals of regions the fused backward sweep has already served (it wrote their p_int and counts): d = 0 marks
+    // a diagonal this kernel leaves alone
+    const bool served = mine && k.cls <= skip_class_le;
+    if (__all_sync(FULL_MASK, served || !mine)) return;
+    if (served) k.d = 0;
     const double my_total = (mine && k.d >= 1) ? totals[k.tot] : 0.0;
     const int64_t base = __shfl_sync(FULL_MASK, k.c0, 0);
     const int64_t g_last = min(g0 + 32, n_diagonals);  // one past the last diagonal of the group
@@ -651,7 +660,7 @@ k_posterior_diag(Blob bl, int64_t n_diagonals, const double *__restrict__ F, con
             }
         }
     }
-    if (mine) counts[k.slot] = count;
+    if (mine && !served) counts[k.slot] = count;
 }
 
 __global__ void k_pair_offsets(Blob bl, int64_t n_aln, int64_t n_regions, int64_t n_diagonals,
@@ -1034,7 +1043,15 @@ WaveLaunch wave_launch(int S, int64_t items, const BlobHeader &h) {
 // test hook (mab_debug_set_min_band_class): 1 runs class-0 items on the warp-per-item kernel, 2 everything on the
 // shared-memory-ring kernels; results must not depend on it
 int g_min_band_class = 0;
+// mab_debug_set_fused_posterior: 1 runs posterior mode through the fused sweep (backward + totals + posteriors in one
+// kernel, k_backward_post_rr) for band classes 0 / 1; 0 (default) through the separate kernels.  Results are
+// bit-identical (tests/test_gpu_parity.py).  Measured on 1 M tRNA reads (profiles/r2_ncu_summary.md): fused sweep
+// 92.3 ms against 52.4 (backward) + 8.8 (k_totals) + 16.1 (k_posterior_diag) = 77.3 ms -- the serial total-probability
+// chains and the exp() of the ~7 % candidate cells cost more issue slots inside the latency-bound sweep (554 against
+// 330 warp instructions per diagonal) than the two streaming kernels they replace, so the separate path stays default.
+int g_fuse_posterior = 0;
 #define RR_LA_DEFAULT 1    // |x - y| logAdd (wavefront_reg.cuh); measured against la_bf and four other coefficient
+#define RR_MINB_POST 6     // fused sweep: 92.3 ms per 1 M tRNA reads at 6 blocks per SM, 95.9 at 5, 99.6 at 4
 #define RR_MINB_DEFAULT 6  // fetches (profiles/r2_ncu_summary.md): 53.5 / 52.0 ms per 1 M tRNA reads at 6 blocks per SM
 
 // register-resident kernels (wavefront_reg.cuh): resident blocks per SM from the occupancy calculator, once per kernel
@@ -1053,8 +1070,14 @@ int rr_grid(K kernel, int64_t items, int items_per_block) {
 // The order arrays list the work items by band class (mab_internal.h): class 2 (wide bands) first -- they run on the
 // shared-memory-ring kernels, G warps per item -- then class 1 (a warp per item) and class 0 (a half-warp per item) on
 // the register-resident kernels.
+// posterior mode: what the fused backward sweep (k_backward_post_rr) needs besides the DP buffers
+struct PostArgs {
+    double threshold, log_reject;
+};
+
 template <int S, bool FULL>
-int run_dp(const DevModel &dm, const mab_plan *plan, const Blob &bl, const Workspace &w, cudaStream_t st) {
+int run_dp(const DevModel &dm, const mab_plan *plan, const Blob &bl, const Workspace &w, cudaStream_t st,
+           const PostArgs *post = nullptr, bool *unfused_items = nullptr) {
     const BlobHeader &h = plan->hdr;
     int nR2 = (int) h.n_class_regions[2], nR1 = (int) h.n_class_regions[1], nR0 = (int) h.n_class_regions[0];
     int nT2 = (int) h.n_class_tbs[2], nT1 = (int) h.n_class_tbs[1], nT0 = (int) h.n_class_tbs[0];
@@ -1128,21 +1151,45 @@ int run_dp(const DevModel &dm, const mab_plan *plan, const Blob &bl, const Works
         k<<<rr_grid(k, nR0, 2 * WPB), RR_THREADS, 0, st>>>(dm, bl, nR2 + nR1, nR2 + nR1 + nR0, w.fwd, w.fwd_tot,
                                                           w.counters + 9);
     }
-    if (nT1 > 0) {
-        LaunchTimer lt(K_BACKWARD, st);
-        auto k = k_backward_rr<S, FULL, 32, LA, MB>;
-        k<<<rr_grid(k, nT1, WPB), RR_THREADS, 0, st>>>(dm, bl, nT2, nT2 + nT1, w.bwd, w.bwd_tot, w.edge, w.counters + 10);
+    // Posterior mode: classes 0 / 1 run the fused sweep (backward + totals + posteriors, wavefront_reg.cuh); only
+    // class-2 items still go through B / BT / edge, k_totals and k_posterior_diag.
+    const bool fused = !FULL && post != nullptr;
+    if (unfused_items) *unfused_items = !fused || nT2 > 0;
+    if constexpr (!FULL) {
+        if (fused) {
+            if (nT1 > 0) {
+                LaunchTimer lt(K_BACKWARD, st);
+                auto k = k_backward_post_rr<S, 32, LA, RR_MINB_POST>;
+                k<<<rr_grid(k, nT1, WPB), RR_THREADS, 0, st>>>(dm, bl, nT2, nT2 + nT1, w.fwd, w.fwd_tot, post->threshold,
+                                                               post->log_reject, w.pint, w.counts, w.counters + 10);
+            }
+            if (nT0 > 0) {
+                LaunchTimer lt(K_BACKWARD, st);
+                auto k = k_backward_post_rr<S, 16, LA, RR_MINB_POST>;
+                k<<<rr_grid(k, nT0, 2 * WPB), RR_THREADS, 0, st>>>(dm, bl, nT2 + nT1, nT2 + nT1 + nT0, w.fwd, w.fwd_tot,
+                                                                   post->threshold, post->log_reject, w.pint, w.counts,
+                                                                   w.counters + 11);
+            }
+        }
     }
-    if (nT0 > 0) {
-        LaunchTimer lt(K_BACKWARD, st);
-        auto k = k_backward_rr<S, FULL, 16, LA, MB>;
-        k<<<rr_grid(k, nT0, 2 * WPB), RR_THREADS, 0, st>>>(dm, bl, nT2 + nT1, nT2 + nT1 + nT0, w.bwd, w.bwd_tot, w.edge,
-                                                          w.counters + 11);
+    if (!fused) {
+        if (nT1 > 0) {
+            LaunchTimer lt(K_BACKWARD, st);
+            auto k = k_backward_rr<S, FULL, 32, LA, MB>;
+            k<<<rr_grid(k, nT1, WPB), RR_THREADS, 0, st>>>(dm, bl, nT2, nT2 + nT1, w.bwd, w.bwd_tot, w.edge, w.counters + 10);
+        }
+        if (nT0 > 0) {
+            LaunchTimer lt(K_BACKWARD, st);
+            auto k = k_backward_rr<S, FULL, 16, LA, MB>;
+            k<<<rr_grid(k, nT0, 2 * WPB), RR_THREADS, 0, st>>>(dm, bl, nT2 + nT1, nT2 + nT1 + nT0, w.bwd, w.bwd_tot, w.edge,
+                                                              w.counters + 11);
+        }
     }
-    if (h.n_totals > 0) {
+    if (h.n_totals > 0 && (!fused || nT2 > 0)) {
         LaunchTimer lt(K_TOTALS, st);
-        k_totals<S, FULL><<<(int) ((4 * h.n_totals + 127) / 128), 128, 0, st>>>(bl, (int) h.n_totals, w.fwd, w.bwd, w.fwd_tot,
-                                                                        w.bwd_tot, w.edge, w.totals);
+        k_totals<S, FULL><<<(int) ((4 * h.n_totals + 127) / 128), 128, 0, st>>>(
+            bl, (int) h.n_totals, w.fwd, w.bwd, w.fwd_tot, w.bwd_tot, w.edge, w.totals,
+            fused && g_min_band_class < 2 ? 1 : -1);
     }
     return check(cudaGetLastError(), "dp launch");
 }
@@ -1152,16 +1199,23 @@ int run_posteriors(const DevModel &dm, const mab_plan *plan, const void *d_blob,
                    int64_t *d_pair_off, int64_t *d_n_pairs, cudaStream_t st) {
     const BlobHeader &h = plan->hdr;
     const Blob bl = blob_view(d_blob, h);
-    int rc = run_dp<S, false>(dm, plan, bl, w, st);
-    if (rc) return rc;
     const int64_t nD = h.n_diagonals;
-    {
+    const double thr = plan->params.threshold;
+    // exp() is skipped where it cannot reach the threshold (log(0) = -inf: never skipped)
+    const PostArgs post{thr, thr > 0.0 ? std::log(thr) - 0.1 : -INFINITY};
+    const bool fuse = g_fuse_posterior != 0;
+    int rc;
+    // pair counts per emission slot: the fused sweep writes the slots of its kept diagonals, k_posterior_diag those of
+    // the others; diagonal 0 of every region and the sentinel stay 0
+    if (fuse && (rc = check(cudaMemsetAsync(w.counts, 0, (size_t) (nD + 1) * sizeof(int64_t), st), "memset counts")))
+        return rc;
+    bool unfused_items = true;
+    if ((rc = run_dp<S, false>(dm, plan, bl, w, st, fuse ? &post : nullptr, &unfused_items))) return rc;
+    if (unfused_items) {
         LaunchTimer lt(K_POSTERIOR, st);
-        const double thr = plan->params.threshold;
-        // exp() is skipped where it cannot reach the threshold (log(0) = -inf: never skipped)
-        const double log_reject = thr > 0.0 ? std::log(thr) - 0.1 : -INFINITY;
-        k_posterior_diag<<<(unsigned) ((nD + 1 + 255) / 256), 256, 0, st>>>(bl, nD, w.fwd, w.bwd, w.totals, thr, log_reject,
-                                                                          w.pint, w.counts);  // a warp per 32 diagonals
+        k_posterior_diag<<<(unsigned) ((nD + 1 + 255) / 256), 256, 0, st>>>(bl, nD, w.fwd, w.bwd, w.totals, post.threshold,
+                                                                          post.log_reject, w.pint, w.counts,
+                                                                          fuse && g_min_band_class < 2 ? 1 : -1);  // a warp per 32 diagonals
     }
     {
         LaunchTimer lt(K_SCAN, st);
@@ -1242,6 +1296,11 @@ extern "C" int mab_debug_set_min_band_class(int cls) {
         return MAB_E_ARG;
     }
     g_min_band_class = cls;
+    return MAB_OK;
+}
+
+extern "C" int mab_debug_set_fused_posterior(int on) {
+    g_fuse_posterior = on != 0;
     return MAB_OK;
 }
 

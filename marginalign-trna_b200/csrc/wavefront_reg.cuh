@@ -526,3 +526,184 @@ k_backward_rr(const __grid_constant__ DevModel model, Blob bl, int item0, int it
         if (d > t.lo) step(std::integral_constant<int, 1>(), d, a, b);
     }
 }
+
+// ------------------------------------------------------------------------------------------------ fused backward (N2)
+// Posterior mode: backward sweep + total probability + posterior match probabilities in ONE pass over a traceback, as
+// the reference's loop does (pairwiseAligner.c:695-733 with the callbacks :566-615).  The backward cells never leave
+// the registers: B, BT and the edge buffer are not written, k_totals and k_posterior_diag are not launched for these
+// items.  Per kept diagonal the lane reads F (match state) of its cell, forms exp(F + B - total) and writes p_int;
+// the per-diagonal pair count goes to counts[slot] for the ordered emission (k_emit_diag).
+//
+// Total probability (every 10th kept diagonal, diagonalCalculationTotalProbability :566-583): the per-cell dot products
+// over the S states are formed by all lanes at once; the two logAdd chains that must run in cell order (logAdd is not
+// associative) -- over the cells of diagonal d, and over the match states of diagonal d+1 that jump over d -- are
+// carried by the even and the odd lanes side by side, every lane pulling the next value of ITS chain by shuffle, so a
+// total costs max(w, w1) + 1 dependent logAdds for the whole warp (both half-warps share the instruction stream: all
+// final tracebacks place their totals on the same steps).
+template <int S, int LPI, int LA, int MINB>
+__global__ void __launch_bounds__(RR_THREADS, MINB)
+k_backward_post_rr(const __grid_constant__ DevModel model, Blob bl, int item0, int item1, const double *__restrict__ F,
+                   const double *__restrict__ FT, double threshold, double log_reject, int32_t *__restrict__ pint,
+                   int64_t *__restrict__ counts, int *counter) {
+    __shared__ RegTables tb;
+    __shared__ __align__(16) CoefTable ct;
+    __shared__ RegStage stage[RR_THREADS / LPI];
+    fill_reg_tables(tb, model, threadIdx.x, blockDim.x);
+    fill_coef_table(ct, threadIdx.x, blockDim.x);
+    stage_init<LPI>(stage);
+    __syncthreads();
+    const RegLane ln = reg_lane<LPI>(tb, ct);
+    const int lane32 = threadIdx.x & 31, lane_base = lane32 & ~(LPI - 1);
+    const double NINF = neg_inf();
+    RegStage &sg = stage[threadIdx.x / LPI];
+    DescStream<LPI, -1> ds;
+    ds.ring = (unsigned) __cvta_generic_to_shared(&sg.ring[0]);
+    ds.bar = (unsigned) __cvta_generic_to_shared(&sg.bar[0]);
+    ds.gmask = ln.gmask;
+    ds.phase = 0;
+    ds.leader = ln.lane == 0;
+    const unsigned sxr = (unsigned) __cvta_generic_to_shared(&sg.sx[0]), syr = (unsigned) __cvta_generic_to_shared(&sg.sy[0]);
+    const int64_t cwx = mab_pack_code_words(bl.h_len_sym_x), cwy = mab_pack_code_words(bl.h_len_sym_y);
+    const bool odd_lane = ln.lane & 1;
+
+    for (;;) {
+        const int item = item0 + next_item_sub<LPI>(counter, lane32, ln.gmask);
+        if (item >= item1) break;
+        const TracebackDesc t = bl.tbs[bl.order_bwd[item]];
+        const RegionDesc rg = bl.regions[t.region];
+        const int lX = rg.lX, lY = rg.lY;
+        // emission slot of diagonal d (see the comment above diag_work in kernels.cu)
+        const int64_t slot0 = rg.diag_base + 1 + (lX + lY - t.from) - t.lo - 1;
+        ds.open(bl.diags + rg.diag_base, lX + lY + 2, t.hi + 1, t.lo);
+        int64_t c_above = ds.get(t.hi + 1, false).cell_off;
+        DiagDesc cur = ds.get(t.hi, (t.hi & (RR_DWIN - 1)) == RR_DWIN - 1);
+        DiagDesc nxt = ds.get(t.hi - 1, ((t.hi - 1) & (RR_DWIN - 1)) == RR_DWIN - 1);
+        Cell<S> a, b = cell_fill<S>(NINF);
+        double total = NINF;
+        // geometry of the previous step (diagonal d + 1): needed by the "jump over d" term of a total on d
+        int64_t up_cell = 0;
+        bool up_active = false;
+        int up_first = 0, up_w = 0;
+
+        // total probability on diagonal d (cells c, first lane lL, width w); through = d < hi
+        auto total_on = [&](const DiagDesc &dg, const RegGeom &g, int w, const Cell<S> &c, const Cell<S> &c_up, bool through) {
+            double cd = NINF, tv = NINF;
+            if (g.active) {
+                const double *ft = FT + ((int64_t) bl.totals[dg.tot_flags & MAB_DIAG_TOT_MASK].full_off + g.j) * S;
+                cd = __dadd_rn(ft[0], c.v[0]);
+#pragma unroll
+                for (int s = 1; s < S; s++) cd = la_rr<LA>(cd, __dadd_rn(ft[s], c.v[s]), ln.cf);
+            }
+            if (through && up_active) tv = __dadd_rn(F[up_cell], c_up.v[M]);
+            const int first = (ln.lane - g.j) & (LPI - 1);  // lane of the diagonal's first cell
+            const int n_it = max(w, through ? up_w : 0);
+            double acc = NINF;
+            for (int j = 0; j < n_it; j++) {
+                const double v1 = shfl_f64(ln.gmask, cd, lane_base | ((first + j) & (LPI - 1)));
+                const double v2 = shfl_f64(ln.gmask, tv, lane_base | ((up_first + j) & (LPI - 1)));
+                const double r = la_rr<LA>(acc, odd_lane ? v2 : v1, ln.cf);
+                if (odd_lane ? (through && j < up_w) : (j < w)) acc = r;
+            }
+            const double t0 = shfl_f64(ln.gmask, acc, lane_base), t1 = shfl_f64(ln.gmask, acc, lane_base | 1);
+            total = through ? la_rr<LA>(t0, t1, ln.cf) : t0;
+        };
+        // posteriors of kept diagonal d >= 1 (diagonalCalculationPosteriorMatchProbs :585-615).  exp() is needed only
+        // where the pair can pass the threshold (~7 % of the cells), but in a warp some lane nearly always has such a
+        // cell, and the library exp is ~40 dependent FP64 operations: a lane therefore parks its candidate (log value,
+        // cell, emission slot) and the group evaluates the parked candidates together only when a lane that already
+        // holds one finds another (every ~4 diagonals), off the recurrence's critical path.  Pair counts per diagonal
+        // are accumulated with integer atomics (order-independent).
+        double pend_s = 0.0;
+        int64_t pend_cell = -1, pend_slot = 0;
+        auto flush = [&]() {
+            if (pend_cell >= 0) {
+                int32_t v = -1;
+                double p = exp(pend_s);
+                if (p >= threshold) {
+                    if (p > 1.0) p = 1.0;
+                    v = (int32_t) floor(__dmul_rn(p, MAB_PROB_1));
+                    atomicAdd((unsigned long long *) (counts + pend_slot), 1ull);
+                }
+                pint[pend_cell] = v;
+                pend_cell = -1;
+            }
+        };
+        auto posterior_on = [&](int d, const DiagDesc &dg, const RegGeom &g, const Cell<S> &c, double f_match) {
+            const int64_t cell = dg.cell_off + g.j;
+            const double s = __dsub_rn(__dadd_rn(f_match, c.v[M]), total);
+            const bool cand = g.active && g.x > 0 && g.y > 0 && s >= log_reject;
+            if (__any_sync(ln.gmask, cand && pend_cell >= 0)) flush();
+            if (cand) {
+                pend_s = s;
+                pend_cell = cell;
+                pend_slot = slot0 + d;
+            } else if (g.active) {
+                pint[cell] = -1;
+            }
+        };
+        {  // diagonal hi: (ragged)endStateProb on every cell, pairwiseAligner.c:680-681
+            const double *init = (t.at_end && (rg.flags & 2)) ? model.ragged_end : model.end;
+            const int w = (int) (c_above - cur.cell_off);
+            const RegGeom g = reg_geom<LPI>(ln.lane, t.hi, cur.xmyL, w);
+#pragma unroll
+            for (int s = 0; s < S; s++) a.v[s] = g.active ? init[s] : NINF;
+            if (t.hi <= t.from) {  // a final traceback keeps its first diagonal, which then carries a total
+                if (cur.tot_flags & MAB_DIAG_IS_TOTAL) total_on(cur, g, w, a, b, false);
+                posterior_on(t.hi, cur, g, a, g.active ? F[cur.cell_off + g.j] : 0.0);
+            }
+            up_cell = cur.cell_off + g.j;
+            up_active = g.active;
+            up_first = (ln.lane - g.j) & (LPI - 1);
+            up_w = w;
+        }
+        const int d_first = t.hi - 1;
+        auto step = [&](auto q_tag, int d, const Cell<S> &p1, Cell<S> &p2) {
+            constexpr int Q = decltype(q_tag)::value;
+            c_above = cur.cell_off;
+            cur = nxt;
+            nxt = ds.get(d - 1, ((d - 1) & (RR_DWIN - 1)) == RR_DWIN - 1);
+            const int w = (int) (c_above - cur.cell_off);
+            if (((d_first - d) & (RR_SYM_REFRESH - 1)) == 0) {
+                const int x_hi = (d + cur.xmyL + 2 * (w - 1)) >> 1, y_hi = (d - cur.xmyL) >> 1;
+                __syncwarp(ln.gmask);
+                unpack_symbols<LPI>(bl.pack_x, cwx, rg.sym_x_off, lX, (x_hi - 100) & ~7, ln.lane, sxr);
+                unpack_symbols<LPI>(bl.pack_y, cwy, rg.sym_y_off, lY, (y_hi - 100) & ~7, ln.lane, syr);
+                __syncwarp(ln.gmask);
+            }
+            const RegGeom g = reg_geom<LPI>(ln.lane, d, cur.xmyL, w);
+            int cX = 5, cY = 5;
+            double f_match = 0.0;
+            if (g.active) {
+                cX = lds_u8(sxr + (g.x & (RR_SYM_RING - 1)));
+                cY = lds_u8(syr + (g.y & (RR_SYM_RING - 1)));
+                if (d <= t.from) f_match = __ldg(F + cur.cell_off + g.j);  // in flight while the cell is computed
+            }
+            const double em = lds_f64(ln.em_addr + (cX * 5 + cY) * (RR_REPL * 8));
+            const double ex = lds_f64(ln.ex_addr + cX * (RR_REPL * 8));
+            const double ey = lds_f64(ln.ey_addr + cY * (RR_REPL * 8));
+            reg_backward_cell<S, Q, LA>(model, ln, p1, p2, em, ex, ey);  // p1 (diagonal d + 1) is left untouched
+            if (d <= t.from) {
+                if (cur.tot_flags & MAB_DIAG_IS_TOTAL) total_on(cur, g, w, p2, p1, true);
+                posterior_on(d, cur, g, p2, f_match);
+            }
+            up_cell = cur.cell_off + g.j;
+            up_active = g.active;
+            up_first = (ln.lane - g.j) & (LPI - 1);
+            up_w = w;
+        };
+        int d = t.hi - 1;
+        if (d > t.lo && !(d & 1)) {
+            step(std::integral_constant<int, 0>(), d, a, b);
+            const Cell<S> tmp = a;
+            a = b;
+            b = tmp;
+            d--;
+        }
+        for (; d - 1 > t.lo; d -= 2) {
+            step(std::integral_constant<int, 1>(), d, a, b);
+            step(std::integral_constant<int, 0>(), d - 1, b, a);
+        }
+        if (d > t.lo) step(std::integral_constant<int, 1>(), d, a, b);
+        flush();
+    }
+}

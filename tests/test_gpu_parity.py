@@ -446,3 +446,27 @@ def test_bigmutations_all_reads_exact_against_oracle(engine):
                                       [(a["ops"], a["lens"]) for a in alns])
     P = mab.AlignmentParameters(split_matrix_bigger_than=100)
     _oracle_check(engine, model, om, b, P, po.make_params(expansion=10, split=100 ** 2), "bigmut", expectations=False)
+
+
+def test_fused_backward_posterior_equals_the_separate_kernels(engine, golden):
+    """N2: posterior mode runs backward sweep, total probabilities and posteriors in one kernel for band classes 0 / 1
+    (pairwiseAligner.c:695-733).  Same pairs, bit for bit, as the separate backward / k_totals / k_posterior_diag
+    kernels, on a batch that mixes all three classes, several tracebacks per region (long reads) and both state counts."""
+    L = mab.capi.load()
+    cases = [(_with_gap_box(_with_gap_box(mab.synth.make_trna_batch(400, seed=51), 12), 300), mab.AlignmentParameters()),
+             (mab.synth.make_long_batch(4, read_len=3000, genome_len=50_000, seed=52),
+              mab.AlignmentParameters(split_matrix_bigger_than=300))]
+    try:
+        for key in ("fixture5asym", "three_asym"):
+            model = gpu_model(golden.model_arrays(key))
+            for b, P in cases:
+                got = []
+                for fused in (1, 0):
+                    mab.capi.check(L.mab_debug_set_fused_posterior(fused))
+                    res = engine.get_aligned_pairs_using_anchors(model, b, P)
+                    got.append((res.offsets.copy(), res.x.copy(), res.y.copy(), res.p.copy()))
+                for k in range(4):
+                    assert np.array_equal(got[0][k], got[1][k]), (key, k)
+                assert len(got[0][1]) > 0
+    finally:
+        L.mab_debug_set_fused_posterior(0)
