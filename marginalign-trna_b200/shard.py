@@ -5,8 +5,9 @@ src/margin/utils.py:127-180; one per alignment chunk per EM iteration, submodule
 "reduction" is Python summing `%f` text files (cPecanEm.py:184-188).  Here every rank (one process per GPU,
 torch.distributed) owns a shard of the alignments:
 
-  * posterior mode has NO collective: alignments are independent work items; results are gathered to the caller's
-    rank in input order (the reference consumes cigars positionally, marginAlignLib.py:334);
+  * posterior mode has NO collective: alignments are independent work items; shards are contiguous slices balanced by
+    estimated cells, results reach the caller's rank in input order (the reference consumes cigars positionally,
+    marginAlignLib.py:334) through shared memory on one node (a padded gather over the backend otherwise);
   * expectation mode has exactly one: an all-reduce(sum) of the S*S + S*16 + 1 doubles per EM iteration.
 
 This module only moves indices and small vectors; the arithmetic is PairHmmEngine's (CUDA, no CPU fallback).
@@ -24,24 +25,32 @@ def estimate_cells(batch, params):
     return (lx + ly + 1).astype(np.int64) * (int(params.diagonal_expansion) + 3)
 
 
-def partition(weights, world):
-    """Deterministic balanced partition of items into `world` shards.
+def partition_bounds(weights, world):
+    """Contiguous balanced partition: world + 1 non-decreasing boundaries; shard r owns items bounds[r]:bounds[r+1].
 
-    Items are sorted by weight (descending, stable) and dealt in boustrophedon order (0..w-1, w-1..0, ...), which keeps
-    the shard sums within one max-weight of each other for sorted input and is O(n log n) vectorised -- 1 M reads
-    partition in well under a second.  Each shard's indices are returned ascending so a shard preserves input order.
-    """
-    weights = np.asarray(weights)
+    Item i goes to the shard that holds the START of its weight interval in the running sum, so every shard's total is
+    within one item weight of total / world, a shard is a slice of the input (no copy of the sequence data) and the
+    results of the shards concatenate back in input order -- which is the order the reference consumes them in
+    (marginAlignLib.py:334)."""
+    weights = np.asarray(weights, dtype=np.float64)
     n = len(weights)
     if world < 1:
         raise ValueError("world must be >= 1")
-    order = np.argsort(-weights, kind="stable")
-    pos = np.arange(n)
-    lap, col = pos // world, pos % world
-    owner_sorted = np.where(lap % 2 == 0, col, world - 1 - col)
-    owner = np.empty(n, dtype=np.int64)
-    owner[order] = owner_sorted
-    return [np.flatnonzero(owner == r) for r in range(world)]
+    if n == 0:
+        return np.zeros(world + 1, dtype=np.int64)
+    start = np.concatenate([[0.0], np.cumsum(weights)[:-1]])
+    total = float(start[-1] + weights[-1])
+    if total <= 0:
+        owner = (np.arange(n) * world) // n
+    else:
+        owner = np.minimum((start * world / total).astype(np.int64), world - 1)
+    return np.searchsorted(owner, np.arange(world + 1), side="left").astype(np.int64)
+
+
+def partition(weights, world):
+    """The shards of partition_bounds as index arrays (ascending, contiguous)."""
+    b = partition_bounds(weights, world)
+    return [np.arange(b[r], b[r + 1], dtype=np.int64) for r in range(world)]
 
 
 def _dist():
@@ -96,12 +105,21 @@ def _gather_varlen(arr, dst, device, group):
 
 def merge_pairs(parts, shards, n_total):
     """Reassembles per-shard PosteriorPairs into one CSR result in input order.  parts[r] = (offsets, x, y, p) of
-    shard r, whose alignments are shards[r] (ascending input indices)."""
+    shard r, whose alignments are shards[r] (ascending input indices; contiguous shards concatenate without a scatter,
+    each shard staying a block of the result)."""
     counts = np.zeros(n_total, dtype=np.int64)
     for (off, _, _, _), idx in zip(parts, shards):
         counts[idx] = np.diff(off)
     offsets = np.zeros(n_total + 1, dtype=np.int64)
     np.cumsum(counts, out=offsets[1:])
+    contiguous = all(len(idx) == 0 or (idx[-1] - idx[0] + 1 == len(idx)) for idx in shards)
+    if contiguous:
+        blocks = [(int(idx[0]), int(idx[-1]) + 1, int(offsets[idx[0]]), px, py, pp)
+                  for (off, px, py, pp), idx in zip(parts, shards) if len(idx)]
+        blocks.sort(key=lambda b: b[0])
+        if not blocks:
+            blocks = [(0, 0, 0, np.zeros(0, np.int32), np.zeros(0, np.int32), np.zeros(0, np.int32))]
+        return PosteriorPairs(offsets, blocks=blocks)
     total = int(offsets[-1])
     x = np.empty(total, dtype=np.int32)
     y = np.empty(total, dtype=np.int32)
@@ -116,6 +134,61 @@ def merge_pairs(parts, shards, n_total):
     return PosteriorPairs(offsets, x, y, p)
 
 
+_SHM_DIR = "/dev/shm"
+_shm_counter = [0]
+
+
+def _gather_shared_memory(arrays, dst, group):
+    """Single-node transport of a rank's result arrays to rank `dst` through a tmpfs file: every other rank writes its
+    arrays into one file under /dev/shm, the paths travel in a tiny gather_object, `dst` maps the files (np.memmap) and
+    returns views; the files are unlinked at once and their pages live as long as the returned arrays.  Returns None
+    when /dev/shm cannot be used (the caller falls back to the collective)."""
+    import os
+    dist = _dist()
+    rank, world = world_info(group)
+    meta, path, ok = None, None, 1
+    if rank != dst:
+        try:
+            _shm_counter[0] += 1
+            path = os.path.join(_SHM_DIR, "mab_%d_%d.bin" % (os.getpid(), _shm_counter[0]))
+            at, layout = 0, []
+            with open(path, "wb") as fh:
+                for a in arrays:
+                    a = np.ascontiguousarray(a)
+                    fh.write(memoryview(a).cast("B"))
+                    layout.append((str(a.dtype), int(a.size), at))
+                    at += int(a.nbytes)
+            meta = (path, layout)
+        except OSError:
+            ok = 0
+    flags = [None] * world
+    dist.all_gather_object(flags, ok, group=group)
+    if not all(flags):
+        if path is not None and os.path.exists(path):
+            os.remove(path)
+        return None
+    metas = [None] * world if rank == dst else None
+    dist.gather_object(meta, metas, dst=dst, group=group)
+    out = ()  # other ranks: done (an empty tuple, not None: None means "shared memory unusable, fall back")
+    if rank == dst:
+        out = []
+        for r in range(world):
+            if r == dst:
+                out.append([np.asarray(a) for a in arrays])
+                continue
+            name, layout = metas[r]
+            out.append([np.memmap(name, dtype=np.dtype(dt), mode="r", offset=at, shape=(n,)) if n else
+                        np.zeros(0, dtype=np.dtype(dt)) for dt, n, at in layout])
+        out = (out, [])
+    dist.barrier(group=group)  # dst has mapped every file: the owners can drop the names
+    if path is not None:
+        try:
+            os.remove(path)
+        except FileNotFoundError:
+            pass
+    return out
+
+
 class ShardedPairHmm:
     """Runs the two hot-path operations over all ranks of the default (or given) process group.
 
@@ -124,8 +197,9 @@ class ShardedPairHmm:
     NCCL, "cpu" under gloo.
     """
 
-    def __init__(self, engine, group=None, comm_device=None):
+    def __init__(self, engine, group=None, comm_device=None, shared_memory=True):
         self.engine = engine
+        self.shared_memory = shared_memory  # single-node result transport through /dev/shm (falls back if unusable)
         self.group = group
         self.rank, self.world = world_info(group)
         self.comm_device = comm_device if comm_device is not None else getattr(engine, "device", "cpu")
@@ -145,19 +219,25 @@ class ShardedPairHmm:
         shards = self.shards(batch, params)
         self.last_shards = shards
         mine = shards[self.rank]
-        sub = batch.subset(mine)
+        sub = batch.slice(mine[0], mine[-1] + 1) if len(mine) else batch.slice(0, 0)  # shards are contiguous: views
         t1 = time.perf_counter()
         res = self.engine.get_aligned_pairs_using_anchors(model, sub, params)
         t2 = time.perf_counter()
-        cols = []
-        for a in (res.offsets, res.x, res.y, res.p):
-            cols.append(_gather_varlen(np.asarray(a), dst, self.comm_device, self.group))
+        arrays = (res.offsets, res.x, res.y, res.p)
+        got = _gather_shared_memory(arrays, dst, self.group) if self.shared_memory else None
+        transport = "shared memory"
+        if got is None:  # no usable /dev/shm (or more than one node): padded gather over the collective backend
+            transport = "collective gather"
+            cols = [_gather_varlen(np.asarray(a), dst, self.comm_device, self.group) for a in arrays]
+            got = ([[cols[k][r] for k in range(4)] for r in range(self.world)], []) if self.rank == dst else None
         t3 = time.perf_counter()
-        self.last_phases = {"partition_s": t1 - t0, "compute_s": t2 - t1, "gather_s": t3 - t2, "merge_s": 0.0}
+        self.last_phases = {"partition_s": t1 - t0, "compute_s": t2 - t1, "gather_s": t3 - t2, "merge_s": 0.0,
+                            "transport": transport}
         if self.rank != dst:
             return None
-        parts = [(cols[0][r], cols[1][r], cols[2][r], cols[3][r]) for r in range(self.world)]
-        out = merge_pairs(parts, shards, batch.n)
+        parts, keep = got
+        out = merge_pairs([tuple(p) for p in parts], shards, batch.n)
+        out._keep = keep  # shared-memory segments behind the blocks of the other ranks
         self.last_phases["merge_s"] = time.perf_counter() - t3
         return out
 
@@ -170,7 +250,8 @@ class ShardedPairHmm:
         shards = self.shards(batch, params)
         self.last_shards = shards
         mine = shards[self.rank]
-        T, E, lik = self.engine.get_expectations_using_anchors(model, batch.subset(mine), params, pseudo_count=0.0)
+        sub = batch.slice(mine[0], mine[-1] + 1) if len(mine) else batch.slice(0, 0)
+        T, E, lik = self.engine.get_expectations_using_anchors(model, sub, params, pseudo_count=0.0)
         vec = allreduce_expectations(np.concatenate([T, E, [lik]]), self.comm_device, self.group)
         nT, nE = len(T), len(E)
         return vec[:nT] + pseudo_count, vec[nT:nT + nE] + pseudo_count, float(vec[-1])

@@ -60,11 +60,13 @@ def test_partition_is_balanced_deterministic_and_complete():
         assert np.array_equal(np.sort(allidx), np.arange(len(w)))
         for p in parts:
             assert np.all(np.diff(p) > 0)  # ascending: a shard preserves input order
+            assert len(p) == 0 or p[-1] - p[0] + 1 == len(p)  # ... and is a slice of it
         sums = np.array([w[p].sum() for p in parts])
-        assert sums.max() - sums.min() <= w.max()
+        assert np.abs(sums - w.sum() / world).max() <= w.max()  # each shard within one item of the ideal share
         again = shard.partition(w, world)
         assert all(np.array_equal(a, b) for a, b in zip(parts, again))
-    assert [len(p) for p in shard.partition(np.array([5, 1]), 4)] == [1, 1, 0, 0]
+    assert [len(p) for p in shard.partition(np.array([5, 1]), 4)] == [1, 0, 0, 1]
+    assert np.array_equal(shard.partition_bounds(np.array([3, 3, 3, 3]), 2), [0, 2, 4])
     assert [len(p) for p in shard.partition(np.zeros(0), 2)] == [0, 0]
 
 
