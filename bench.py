@@ -324,19 +324,6 @@ def load_peaks():
     return peaks, src, fp64
 
 
-def pin_rank_to_cores(local_rank, world):
-    """Each rank (and the helper threads of its engine) on its own slice of the host cores: the chunk pipeline packs
-    and plans on host threads, and 8 ranks sharing every core of one socket was what bent the round-1 e2e curve."""
-    try:
-        cores = sorted(os.sched_getaffinity(0))
-        per = max(1, len(cores) // max(1, world))
-        mine = cores[local_rank * per:(local_rank + 1) * per] or cores
-        os.sched_setaffinity(0, mine)
-        return len(mine)
-    except (AttributeError, OSError):
-        return None
-
-
 def run_ours(args, rank, world, local_rank):
     import torch
     import marginalign_trna_b200 as mab
@@ -347,7 +334,7 @@ def run_ours(args, rank, world, local_rank):
         raise RuntimeError("bench.py needs a CUDA device (no CPU fallback on this path)")
     torch.cuda.set_device(local_rank)
     dev = torch.device("cuda", local_rank)
-    cores_mine = pin_rank_to_cores(local_rank, world) if world > 1 else None
+    cores_mine = mab.shard.bind_rank_to_local_cores(local_rank, local_rank, world) if world > 1 else None
     dist = None
     if world > 1:
         import torch.distributed as dist

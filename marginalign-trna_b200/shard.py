@@ -58,6 +58,61 @@ def _dist():
     return dist
 
 
+def _parse_cpulist(text):
+    cpus = set()
+    for part in text.strip().split(","):
+        if not part:
+            continue
+        a, _, b = part.partition("-")
+        cpus.update(range(int(a), int(b or a) + 1))
+    return cpus
+
+
+def bind_rank_to_local_cores(device_index, local_rank, local_world):
+    """Pins the calling process (one rank per GPU) to its share of the host cores next to its GPU: the cores of the
+    GPU's NUMA node (sysfs local_cpulist of its PCI device) split among the ranks whose GPUs sit on that node, or --
+    without that information -- an even slice of the allowed cores.  Must run before the engine allocates pinned host
+    memory, so that first-touch places the staging and result buffers on the GPU's own node.  Returns a description
+    (for the bench line); never fails."""
+    import os
+    try:
+        allowed = sorted(os.sched_getaffinity(0))
+    except (AttributeError, OSError):
+        return None
+    info = {"allowed": len(allowed), "numa": None}
+    mine = None
+    try:
+        import torch
+        groups = {}  # local cpu list -> ranks (device indices) that share it
+        for dev in range(local_world):
+            bus = torch.cuda.get_device_properties(dev).pci_bus_id if hasattr(
+                torch.cuda.get_device_properties(dev), "pci_bus_id") else None
+            if bus is None:
+                raise OSError("no pci bus id")
+            path = "/sys/bus/pci/devices/%04x:%02x:%02x.0/local_cpulist" % (
+                torch.cuda.get_device_properties(dev).pci_domain_id, bus, torch.cuda.get_device_properties(dev).pci_device_id)
+            with open(path) as fh:
+                cpus = tuple(sorted(_parse_cpulist(fh.read()) & set(allowed)))
+            groups.setdefault(cpus, []).append(dev)
+        for cpus, devs in groups.items():
+            if device_index in devs and cpus:
+                per = max(1, len(cpus) // len(devs))
+                k = devs.index(device_index)
+                mine = list(cpus[k * per:(k + 1) * per]) or list(cpus)
+                info["numa"] = "%d local cores shared by %d GPUs" % (len(cpus), len(devs))
+    except (OSError, AttributeError, RuntimeError, ValueError):
+        mine = None
+    if not mine:
+        per = max(1, len(allowed) // max(1, local_world))
+        mine = allowed[local_rank * per:(local_rank + 1) * per] or allowed
+    try:
+        os.sched_setaffinity(0, mine)
+    except OSError:
+        return info
+    info["cores"] = len(mine)
+    return info
+
+
 def world_info(group=None):
     dist = _dist()
     if not (dist.is_available() and dist.is_initialized()):
