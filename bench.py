@@ -60,6 +60,7 @@ def parse_args():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true", help="skip the end-to-end leg (profiling runs)")
     ap.add_argument("--no-em-leg", action="store_true", help="skip the seconds-per-EM-iteration leg")
+    ap.add_argument("--no-realign-leg", action="store_true", help="skip the realign-mode end-to-end leg")
     ap.add_argument("--no-strong-leg", action="store_true", help="skip the strong-scaling leg (ShardedPairHmm)")
     ap.add_argument("--em-reads", type=int, default=300000, help="alignments per GPU in the EM leg")
     ap.add_argument("--em-iterations", type=int, default=2)
@@ -503,6 +504,25 @@ def run_ours(args, rank, world, local_rank):
                            "realign tail on the GPU, D2H of the cigars" if realign else
                            "D2H of the expectation vector" if em else "D2H of the pairs into pinned host blocks")}
 
+    # ---- realign mode end to end (what marginAlign does with every read: posteriors + AMAP reweight + MEA chain + cigar,
+    # all on the GPU; only cigars come back, ~0.1 GB per 1 M reads instead of 2.2 GB of pairs)
+    realign_leg = None
+    if not args.no_realign_leg and args.workload == "trna" and not em and not realign:
+        torch.cuda.empty_cache()
+        for _ in range(2):
+            eng.realign(model, batch, params)
+        barrier()
+        t0 = time.perf_counter()
+        for _ in range(e2e_steps):
+            eng.realign(model, batch, params)
+        torch.cuda.synchronize()
+        dt = max_over_ranks((time.perf_counter() - t0) / e2e_steps)
+        st = dict(eng.last_stats)
+        realign_leg = {"value": total_cells / dt / 1e9, "unit": "GCUPS", "reads_per_s": n_reads * world / dt,
+                       "ms_per_step": dt * 1e3, "steps": e2e_steps, "h2d_bytes_per_step": int(st["h2d_bytes"]),
+                       "d2h_bytes_per_step": int(st["d2h_bytes"]),
+                       "note": "PairHmmEngine.realign through the public API, host buffers in, cigars out"}
+
     # ---- strong scaling through the product's sharder: ONE batch (rank 0's), split by ShardedPairHmm.shards()
     strong = None
     if not args.no_strong_leg and args.workload == "trna" and not em and not realign:
@@ -606,7 +626,8 @@ def run_ours(args, rank, world, local_rank):
                    "l2": "inputs larger than L2: %.1f GB of DP state per step" % (cells * (80 if em else 28) / 1e9),
                    "parallelism": "reads sharded, dp%d" % world, "host_cores_per_rank": cores_mine},
         "reads_per_s": n_reads * world / (ms_step * 1e-3),
-        "clocks": clocks, "e2e": e2e, "em": em_leg, "strong": strong, "gpu_launches": launches,
+        "clocks": clocks, "e2e": e2e, "e2e_realign": realign_leg, "em": em_leg, "strong": strong,
+        "gpu_launches": launches,
         "kernel_ms_per_step": {k: v[0] / args.steps for k, v in kernel_ms.items()},
         "roofline": roof, "cpu_baseline": cpu,
     }

@@ -1,3 +1,6 @@
 mkdir -p gpurun_out
 N=$1
-timeout 900 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29511 bench.py --gpus $N --steps 3 --warmup 3 > gpurun_out/r2l_bench_n$N.json 2> gpurun_out/r2l_bench_n$N.err; echo "bench rc=$?"; tail -3 gpurun_out/r2l_bench_n$N.err | cut -c1-300; python tools/bench_summary.py < gpurun_out/r2l_bench_n$N.json; nproc; df -h /dev/shm | tail -1
+run() { name=$1; shift; timeout 900 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29511 bench.py --gpus $N "$@" > gpurun_out/r2n_bench_n${N}_$name.json 2> gpurun_out/r2n_bench_n${N}_$name.err; echo "$name rc=$?"; python tools/bench_summary.py < gpurun_out/r2n_bench_n${N}_$name.json; }
+run post --steps 3 --warmup 3 --no-em-leg --no-strong-leg
+run realign --steps 3 --warmup 3 --mode realign --no-em-leg --no-strong-leg
+nvidia-smi topo -m > gpurun_out/r2n_topo.txt 2>&1; lscpu | grep -i "numa\|socket\|model name" > gpurun_out/r2n_lscpu.txt
