@@ -1052,7 +1052,9 @@ int g_min_band_class = 0;
 int g_fuse_posterior = 0;
 #define RR_LA_DEFAULT 1    // |x - y| logAdd (wavefront_reg.cuh); measured against la_bf and four other coefficient
 #define RR_MINB_POST 6     // fused sweep: 92.3 ms per 1 M tRNA reads at 6 blocks per SM, 95.9 at 5, 99.6 at 4
-#define RR_MINB_DEFAULT 6  // fetches (profiles/r2_ncu_summary.md): 53.5 / 52.0 ms per 1 M tRNA reads at 6 blocks per SM
+#ifndef RR_MINB_DEFAULT
+#define RR_MINB_DEFAULT 5  // fetches (profiles/r2_ncu_summary.md); 4 ... 7 resident blocks per SM are within 2 % of each other
+#endif
 
 // register-resident kernels (wavefront_reg.cuh): resident blocks per SM from the occupancy calculator, once per kernel
 template <typename K>
