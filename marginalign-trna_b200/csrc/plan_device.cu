@@ -365,8 +365,10 @@ extern "C" int64_t mab_plan_device_arena_hint(const mab_params *p, int64_t n, in
     (void) p;
     const int64_t nR = n + n / 8 + 64, nD = len_x + len_y + 2 * nR;
     const int64_t nT = nR + nD / 900 + 64, nTot = nD / 10 + nT + 64;
-    return 4096 + 8 * (n + 2) * 2 + (len_x + len_y + 1024) + nR * (64 + 64 + 8 * 2 + 40 * 2 + 4 * 6) + (nD + 1) * 16 + (len_x + len_y) / 2 + 4096 +
-           nT * (32 + 4 * 6) + nTot * 16 + (int64_t) 64 * 1024 * 1024 / 8 + (nR + nT) * 8;
+    return 64 * 256 /* alignment slack of the sub-allocations */ + 4096 + 8 * (n + 2) * 2 + (len_x + len_y + 1024) +
+           (mab_pack_words(len_x) + mab_pack_words(len_y)) * 4 + nR * (64 + 64 + 8 * 2 + 40 * 2 + 4 * 6) +
+           (nD + 1) * (16 + 4) /* DiagDesc + diag_region */ + nT * (32 + 4 * 6) + nTot * 16 +
+           (int64_t) 64 * 1024 * 1024 / 8 + (nR + nT) * 8;
 }
 
 extern "C" int mab_plan_build_device(const mab_params *p, int64_t n, const uint8_t *d_seq_x, const int64_t *d_off_x,
