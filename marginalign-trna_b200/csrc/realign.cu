@@ -100,7 +100,8 @@ __global__ void __launch_bounds__(256) k_rl_weights(RlArgs a) {
         const int64_t ox = a.off_x[al], oy = a.off_y[al], p0 = a.pair_off[al];
         const int lX = (int) (a.off_x[al + 1] - ox), lY = (int) (a.off_y[al + 1] - oy);
         const int np = (int) (a.pair_off[al + 1] - p0);
-        if (a.pair_off[al + 1] > a.n_pairs) continue;  // clipped by the caller's capacity: see k_rl_chain
+        if (a.pair_off[al + 1] > a.n_pairs || 2 * (int64_t) np > a.n_rand) continue;  // clipped by the caller's capacity, or
+                                                                    // more pairs than the jitter stream holds: see k_rl_chain
         long long *ix = a.ix + ox, *iy = a.iy + oy;
         const int32_t *px = a.x + p0, *py = a.y + p0, *pp = a.p + p0;
         if (a.gap_gamma > 0.0) {  // reweightAlignedPairs2 returns the list untouched otherwise (:1252)
@@ -232,7 +233,10 @@ __global__ void __launch_bounds__(128) k_rl_chain(RlArgs a) {
     if (al >= a.n) return;
     const int64_t ox = a.off_x[al], oy = a.off_y[al], p0 = a.pair_off[al];
     const int lX = (int) (a.off_x[al + 1] - ox), lY = (int) (a.off_y[al + 1] - oy);
-    if (a.pair_off[al + 1] > a.n_pairs) {  // the pairs of this alignment were clipped: the caller re-runs the batch
+    // the pairs of this alignment were clipped by the capacity, or it has more pairs than half the jitter stream (the
+    // draw index must never wrap: every reference process draws 2 np fresh values): no operations, chain length -1 --
+    // the caller sees an empty cigar for a non-empty alignment and re-runs with a larger buffer / table
+    if (a.pair_off[al + 1] > a.n_pairs || 2 * (a.pair_off[al + 1] - p0) > a.n_rand) {
         a.cnt[2 * al] = 0;
         a.cnt[2 * al + 1] = -1;
         return;

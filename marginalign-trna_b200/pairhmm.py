@@ -778,13 +778,17 @@ def _realign_launch(engine, model, dplan, sub, expansion, gap_gamma, match_gamma
                                             np.ascontiguousarray(off_y, dtype=np.int64)])).pin_memory()
         d_offs = h_offs.to(dev, non_blocking=True)
         ox_ptr, oy_ptr = d_offs[0].data_ptr(), d_offs[1].data_ptr()
-    # jitter stream: two draws per pair; an alignment has at most one pair per band cell
-    est = int(((off_x[1:] - off_x[:-1]) + (off_y[1:] - off_y[:-1]) + 1).max() * (expansion + 4)) if n else 0
+    # jitter stream: two draws per pair.  An alignment has at most one pair per band cell, i.e. at most (diagonals x the
+    # widest diagonal of the batch) pairs: a bound, not an estimate (the kernels refuse to wrap the stream, and
+    # _engine_realign raises if an alignment was refused because the 2^25-draw cap was hit)
+    est = int(((off_x[1:] - off_x[:-1]) + (off_y[1:] - off_y[:-1]) + 1).max() * max(int(dplan.plan.info.max_width), 1)) if n else 0
     table = jitter_table(min(2 * est + 2, 1 << 25))
     key = (str(dev), len(table))
     if engine._jitter_dev is None or engine._jitter_dev[0] != key:
         engine._jitter_dev = (key, torch.from_numpy(table).to(dev))
     d_rand = engine._jitter_dev[1]
+    st["n_rand"] = len(table)
+    st["span"] = np.asarray((off_x[1:] - off_x[:-1]) + (off_y[1:] - off_y[:-1]))
     cap = st["cap"]
     ws_bytes = int(L.mab_realign_workspace_bytes(n, cap, len_x, len_y))
     d_ws = torch.empty(ws_bytes + 256, dtype=torch.uint8, device=dev)
@@ -889,6 +893,11 @@ def _engine_realign(self, model, batch, params=None, gap_gamma=0.5, match_gamma=
         for host, ev, st in copies:
             ev.synchronize()
             arrs = [h.numpy() for h in host]
+            # a non-empty alignment without a single cigar operation was refused by the tail kernels (k_rl_chain): it
+            # has more posterior pairs than the jitter stream holds, and wrapping the stream would change the cigar
+            if ((np.diff(arrs[0]) == 0) & (st["span"] > 0)).any():
+                raise RuntimeError("realign: an alignment has more posterior pairs than the jitter stream holds "
+                                   "(%d draws); split the batch or lower diagonalExpansion" % st["n_rand"])
             parts.append(arrs + [None] * (6 - len(arrs)))
             stats["pairs"] += st["total"]
             stats["d2h_bytes"] += sum(a.nbytes for a in arrs)
