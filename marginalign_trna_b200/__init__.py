@@ -1,7 +1,12 @@
-"""Import alias: the real package lives in ../marginalign-trna_b200 (a name Python cannot import directly)."""
-import os as _os
+"""marginalign_trna_b200: B200-native anchor-banded pair-HMM forward-backward (posterior match probabilities and
+EM expectations) behind the cPecanRealign call sites of marginAlign / marginCaller / cPecanEm.
 
-_real = _os.path.join(_os.path.dirname(_os.path.dirname(_os.path.abspath(__file__))), "marginalign-trna_b200")
-__path__ = [_real]
-with open(_os.path.join(_real, "__init__.py")) as _fh:
-    exec(compile(_fh.read(), _os.path.join(_real, "__init__.py"), "exec"), globals())
+(The project is named marginalign-trna_b200; the package directory carries the importable spelling.)
+"""
+from . import build, caller, capi, em, hmm, realign_sam, seqio, shard, synth  # noqa: F401
+from .hmm import Hmm  # noqa: F401
+from .pairhmm import (AlignmentParameters, DevicePlan, PairHmmEngine, PairHmmModel, Plan,  # noqa: F401
+                      PosteriorPairs, RealignedCigars, jitter_table)
+from .synth import AlignmentBatch  # noqa: F401
+
+__version__ = "0.1.0"

@@ -248,7 +248,7 @@ def _torch():
 def require_cuda():
     torch = _torch()
     if not torch.cuda.is_available() or capi.load().mab_device_count() == 0:
-        raise RuntimeError("marginalign-trna_b200: no CUDA device; the pair-HMM path has no CPU fallback")
+        raise RuntimeError("marginalign_trna_b200: no CUDA device; the pair-HMM path has no CPU fallback")
     return torch
 
 
