@@ -390,7 +390,7 @@ class PairHmmEngine:
     posterior mode, 80 B in expectation mode).  plan_on = "device" (default): raw inputs are uploaded and the plan is
     built on the GPU; "host": the C++ host planner builds the blob and it is copied over PCIe."""
 
-    def __init__(self, device=None, max_cells=None, plan_threads=0, plan_on="device"):
+    def __init__(self, device=None, max_cells=None, plan_threads=0, plan_on="device", plan_ahead=None):
         torch = require_cuda()
         self.torch = torch
         self.device = torch.device(device if device is not None else "cuda:%d" % torch.cuda.current_device())
@@ -399,6 +399,8 @@ class PairHmmEngine:
         if plan_on not in ("device", "host"):
             raise ValueError("plan_on must be 'device' or 'host'")
         self.plan_on = plan_on
+        if plan_ahead is not None:  # chunks planned concurrently ahead of the one computing (default PLAN_AHEAD)
+            self.PLAN_AHEAD = max(1, int(plan_ahead))
         self.last_stats = {}
         self._t = {"wait_plan_s": 0.0, "plan_s": 0.0, "pack_s": 0.0, "compute_s": 0.0, "host_alloc_s": 0.0, "drain_s": 0.0}
         self._stagings = (_Staging(), _Staging())
