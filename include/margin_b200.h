@@ -155,6 +155,11 @@ int mab_posteriors_emit(const mab_plan *plan, const void *d_blob, void *d_ws, in
         int32_t *d_y, int32_t *d_p, int64_t capacity, void *stream);
 int mab_expectations(const mab_model *m, const mab_plan *plan, const void *d_blob, void *d_ws, int64_t ws_bytes,
         double *d_out, void *stream);
+/* mab_posteriors_emit with 16-bit coordinates: 8 instead of 12 bytes per pair leave the GPU.  Only valid when every
+ * sub-sequence of the batch is shorter than 32768 bases (the caller checks: coordinates are relative to the
+ * sub-sequences); the pairs and their order are the same. */
+int mab_posteriors_emit_i16(const mab_plan *plan, const void *d_blob, void *d_ws, int64_t ws_bytes, int16_t *d_x,
+        int16_t *d_y, int32_t *d_p, int64_t capacity, void *stream);
 /* ---- realign tail --------------------------------------------------------------------------------
  * Replaces what cPecanRealign does with the posterior pairs of an alignment before it prints the new cigar
  * (cPecanRealign.c:590-631): reweightAlignedPairs2 (pairwiseAligner.c:1251-1261; AMAP gap reweighting),

@@ -64,6 +64,7 @@ SIGNATURES = {
     "mab_plan_device_blob": (vp, [vp]),
     "mab_posteriors_compute": (C.c_int, [vp, vp, vp, vp, C.c_int64, vp, vp, vp]),
     "mab_posteriors_emit": (C.c_int, [vp, vp, vp, C.c_int64, vp, vp, vp, C.c_int64, vp]),
+    "mab_posteriors_emit_i16": (C.c_int, [vp, vp, vp, C.c_int64, vp, vp, vp, C.c_int64, vp]),
     "mab_expectations": (C.c_int, [vp, vp, vp, vp, C.c_int64, vp, vp]),
     "mab_debug_copy_matrices": (C.c_int, [vp, vp, dp, dp, dp, vp]),
     "mab_realign_workspace_bytes": (C.c_int64, [C.c_int64, C.c_int64, C.c_int64, C.c_int64]),

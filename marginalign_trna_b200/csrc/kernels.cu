@@ -673,9 +673,10 @@ __global__ void k_pair_offsets(Blob bl, int64_t n_aln, int64_t n_regions, int64_
     if (a == 0) n_pairs[0] = pos[n_diagonals];
 }
 
+template <typename XY>  // int32_t, or int16_t when every sub-sequence of the batch is shorter than 32768 (8 B per pair)
 __global__ void __launch_bounds__(256)
 k_emit_diag(Blob bl, int64_t n_diagonals, const int32_t *__restrict__ pint, const int64_t *__restrict__ pos,
-            int32_t *__restrict__ out_x, int32_t *__restrict__ out_y, int32_t *__restrict__ out_p, int64_t capacity) {
+            XY *__restrict__ out_x, XY *__restrict__ out_y, int32_t *__restrict__ out_p, int64_t capacity) {
     const int64_t g = (int64_t) blockIdx.x * blockDim.x + threadIdx.x;
     if (g >= n_diagonals) return;
     const DiagWork k = diag_work(bl, g);
@@ -687,8 +688,8 @@ k_emit_diag(Blob bl, int64_t n_diagonals, const int32_t *__restrict__ pint, cons
         if (v >= 0) {
             if (at < capacity) {
                 const int xmy = k.xmyL + 2 * j;
-                out_x[at] = k.x1 + ((k.d + xmy) >> 1) - 1;
-                out_y[at] = k.y1 + ((k.d - xmy) >> 1) - 1;
+                out_x[at] = (XY) (k.x1 + ((k.d + xmy) >> 1) - 1);
+                out_y[at] = (XY) (k.y1 + ((k.d - xmy) >> 1) - 1);
                 out_p[at] = v;
             }
             at++;
@@ -1366,8 +1367,10 @@ extern "C" int mab_posteriors_compute(const mab_model *m, const mab_plan *plan, 
                      : run_posteriors<3>(dm, plan, d_blob, w, d_pair_off, d_n_pairs, st);
 }
 
-extern "C" int mab_posteriors_emit(const mab_plan *plan, const void *d_blob, void *d_ws, int64_t ws_bytes, int32_t *d_x,
-                                   int32_t *d_y, int32_t *d_p, int64_t capacity, void *stream) {
+namespace {
+template <typename XY>
+int posteriors_emit(const mab_plan *plan, const void *d_blob, void *d_ws, int64_t ws_bytes, XY *d_x, XY *d_y, int32_t *d_p,
+                    int64_t capacity, void *stream) {
     if (!plan || !d_blob || !d_ws || (capacity > 0 && (!d_x || !d_y || !d_p))) {
         mab_set_error("mab_posteriors_emit: null argument");
         return MAB_E_ARG;
@@ -1382,10 +1385,21 @@ extern "C" int mab_posteriors_emit(const mab_plan *plan, const void *d_blob, voi
     const Blob bl = blob_view(d_blob, h);
     {
         LaunchTimer lt(K_EMIT, st);
-        k_emit_diag<<<(unsigned) ((h.n_diagonals + 255) / 256), 256, 0, st>>>(bl, h.n_diagonals, w.pint, w.counts, d_x, d_y,
-                                                                            d_p, capacity);
+        k_emit_diag<XY><<<(unsigned) ((h.n_diagonals + 255) / 256), 256, 0, st>>>(bl, h.n_diagonals, w.pint, w.counts, d_x,
+                                                                                d_y, d_p, capacity);
     }
     return check(cudaGetLastError(), "emit launch");
+}
+}  // namespace
+
+extern "C" int mab_posteriors_emit(const mab_plan *plan, const void *d_blob, void *d_ws, int64_t ws_bytes, int32_t *d_x,
+                                   int32_t *d_y, int32_t *d_p, int64_t capacity, void *stream) {
+    return posteriors_emit<int32_t>(plan, d_blob, d_ws, ws_bytes, d_x, d_y, d_p, capacity, stream);
+}
+
+extern "C" int mab_posteriors_emit_i16(const mab_plan *plan, const void *d_blob, void *d_ws, int64_t ws_bytes,
+                                       int16_t *d_x, int16_t *d_y, int32_t *d_p, int64_t capacity, void *stream) {
+    return posteriors_emit<int16_t>(plan, d_blob, d_ws, ws_bytes, d_x, d_y, d_p, capacity, stream);
 }
 
 extern "C" int mab_expectations(const mab_model *m, const mab_plan *plan, const void *d_blob, void *d_ws,

@@ -200,7 +200,8 @@ class PosteriorPairs:
     the reference's getAlignedPairsUsingAnchors returns them; p_int = floor(min(p,1) * 1e7).
 
     The engine returns one block per chunk (pinned host memory filled by D2H copies); .x / .y / .p concatenate the
-    blocks on first use, .pairs(i) reads the owning block directly."""
+    blocks on first use, .pairs(i) reads the owning block directly.  x and y are int16 arrays when every sub-sequence of
+    the batch is shorter than 32768 bases (PairHmmEngine(compact_pairs=True), the default), else int32; p is int32."""
 
     def __init__(self, offsets, x=None, y=None, p=None, blocks=None):
         self.offsets = np.asarray(offsets, dtype=np.int64)
@@ -390,7 +391,8 @@ class PairHmmEngine:
     posterior mode, 80 B in expectation mode).  plan_on = "device" (default): raw inputs are uploaded and the plan is
     built on the GPU; "host": the C++ host planner builds the blob and it is copied over PCIe."""
 
-    def __init__(self, device=None, max_cells=None, plan_threads=0, plan_on="device", plan_ahead=None):
+    def __init__(self, device=None, max_cells=None, plan_threads=0, plan_on="device", plan_ahead=None,
+                 compact_pairs=True):
         torch = require_cuda()
         self.torch = torch
         self.device = torch.device(device if device is not None else "cuda:%d" % torch.cuda.current_device())
@@ -399,6 +401,9 @@ class PairHmmEngine:
         if plan_on not in ("device", "host"):
             raise ValueError("plan_on must be 'device' or 'host'")
         self.plan_on = plan_on
+        # get_aligned_pairs_using_anchors returns x / y as int16 arrays when every sub-sequence is shorter than 32768
+        # bases (same values; a third less data leaves the GPU); False keeps int32 always
+        self.compact_pairs = bool(compact_pairs)
         if plan_ahead is not None:  # chunks planned concurrently ahead of the one computing (default PLAN_AHEAD)
             self.PLAN_AHEAD = max(1, int(plan_ahead))
         self.last_stats = {}
@@ -566,6 +571,11 @@ class PairHmmEngine:
             pending.append((a0, na, host, ev, dev))
             self._t["host_alloc_s"] += time.perf_counter() - t1
 
+        # coordinates are relative to the sub-sequences: 16 bits are enough unless one of them reaches 32768 bases, and
+        # the pairs are what this call moves (8 instead of 12 bytes each over PCIe and into host memory)
+        longest = int(max(np.diff(batch.off_x).max(initial=0), np.diff(batch.off_y).max(initial=0))) if batch.n else 0
+        narrow = longest < 32768 and self.compact_pairs
+        xy_dtype, emit = (torch.int16, L.mab_posteriors_emit_i16) if narrow else (torch.int32, L.mab_posteriors_emit)
         first, prev = 0, None
         with torch.cuda.device(self.device):
             for k in self._t:
@@ -583,12 +593,11 @@ class PairHmmEngine:
                     start_copy(*prev)
                 t1 = time.perf_counter()
                 total = int(d_np.item())  # the sync: the output size is data dependent
-                d_x = torch.empty(total, dtype=torch.int32, device=self.device)
-                d_y = torch.empty(total, dtype=torch.int32, device=self.device)
+                d_x = torch.empty(total, dtype=xy_dtype, device=self.device)
+                d_y = torch.empty(total, dtype=xy_dtype, device=self.device)
                 d_p = torch.empty(total, dtype=torch.int32, device=self.device)
-                capi.check(L.mab_posteriors_emit(dplan.plan._h, dplan.blob_ptr, dplan.ws_ptr, dplan.ws_bytes,
-                                                 d_x.data_ptr(), d_y.data_ptr(), d_p.data_ptr(), total,
-                                                 self._stream_ptr()))
+                capi.check(emit(dplan.plan._h, dplan.blob_ptr, dplan.ws_ptr, dplan.ws_bytes,
+                                d_x.data_ptr(), d_y.data_ptr(), d_p.data_ptr(), total, self._stream_ptr()))
                 done = torch.cuda.Event()
                 done.record(torch.cuda.current_stream(self.device))
                 self._t["compute_s"] += time.perf_counter() - t1

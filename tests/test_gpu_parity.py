@@ -470,3 +470,23 @@ def test_fused_backward_posterior_equals_the_separate_kernels(engine, golden):
                 assert len(got[0][1]) > 0
     finally:
         L.mab_debug_set_fused_posterior(0)
+
+
+def test_compact_pair_coordinates_are_the_same_pairs(golden):
+    """16-bit coordinates (mab_posteriors_emit_i16, the default when every sub-sequence is shorter than 32768 bases)
+    carry the same pairs as the 32-bit ones; a batch with a longer sequence falls back to 32 bits by itself."""
+    model = gpu_model(golden.model_arrays("fixture5asym"))
+    wide, compact = mab.PairHmmEngine(compact_pairs=False), mab.PairHmmEngine()
+    b = mab.synth.make_trna_batch(500, seed=61)
+    r32, r16 = wide.get_aligned_pairs_using_anchors(model, b), compact.get_aligned_pairs_using_anchors(model, b)
+    assert r32.x.dtype == np.int32 and r16.x.dtype == np.int16 and r16.p.dtype == np.int32
+    for a in ("offsets", "x", "y", "p"):
+        assert np.array_equal(getattr(r32, a), getattr(r16, a)), a
+    assert np.array_equal(r16.pairs(7), r32.pairs(7))
+    long_b = mab.synth.make_long_batch(1, read_len=33_000, genome_len=100_000, seed=62)
+    P = mab.AlignmentParameters(split_matrix_bigger_than=300)
+    l16 = compact.get_aligned_pairs_using_anchors(model, long_b, P)
+    assert l16.x.dtype == np.int32 and int(l16.x.max()) >= 32768
+    l32 = wide.get_aligned_pairs_using_anchors(model, long_b, P)
+    for a in ("offsets", "x", "y", "p"):
+        assert np.array_equal(getattr(l32, a), getattr(l16, a)), a
