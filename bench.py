@@ -64,6 +64,7 @@ def parse_args():
     ap.add_argument("--no-strong-leg", action="store_true", help="skip the strong-scaling leg (ShardedPairHmm)")
     ap.add_argument("--em-reads", type=int, default=300000, help="alignments per GPU in the EM leg")
     ap.add_argument("--em-iterations", type=int, default=2)
+    ap.add_argument("--int32-pairs", action="store_true", help="e2e leg: 32-bit pair coordinates even where 16 bits do")
     ap.add_argument("--plan-ahead", type=int, default=0, help="chunks planned ahead of the one computing (0: engine default)")
     ap.add_argument("--max-cells", type=int, default=0,
                     help="DP cells resident per chunk (0: the engine sizes chunks from the band width and free HBM)")
@@ -346,7 +347,8 @@ def run_ours(args, rank, world, local_rank):
     hmm = mab.Hmm.loadHmm(os.path.join(ROOT, "tests", "golden", "input_model.hmm"))
     model = mab.PairHmmModel.from_hmm(hmm) if args.states == 5 else mab.PairHmmModel.default(2)
     S = model.state_number
-    eng = mab.PairHmmEngine(device=dev, max_cells=args.max_cells or None, plan_ahead=args.plan_ahead or None)
+    eng = mab.PairHmmEngine(device=dev, max_cells=args.max_cells or None, plan_ahead=args.plan_ahead or None,
+                            compact_pairs=not args.int32_pairs)
     em = args.mode == "em"
     realign = args.mode == "realign"
     stream = torch.cuda.current_stream(dev)
