@@ -271,29 +271,75 @@ __device__ __forceinline__ Cell<3> backward_cell3_bf(const Cell<3> &nMi, const C
     c.v[SY] = LC(LG(__dadd_rn(nMi.v[M], eM[2]), __dadd_rn(nUp.v[SY], eU[1])), __dadd_rn(nLo.v[SX], eL[2]));
     return c;
 }
+__device__ __forceinline__ Cell<5> forward_cell5_bf(const Cell<5> &lo, const Cell<5> &mi, const Cell<5> &up,
+                                                    const double *eL, const double *eM, const double *eU,
+                                                    const CoefAddr &cf) {
+    Cell<5> c;
+    c.v[SX] = LG(__dadd_rn(lo.v[M], eL[0]), __dadd_rn(lo.v[SX], eL[1]));
+    c.v[LX] = LG(__dadd_rn(lo.v[M], eL[2]), __dadd_rn(lo.v[LX], eL[3]));
+    double m = LC(__dadd_rn(mi.v[M], eM[0]), __dadd_rn(mi.v[SX], eM[1]));
+    m = LC(m, __dadd_rn(mi.v[SY], eM[2]));
+    m = LC(m, __dadd_rn(mi.v[LX], eM[3]));
+    c.v[M] = LC(m, __dadd_rn(mi.v[LY], eM[4]));
+    c.v[SY] = LG(__dadd_rn(up.v[M], eU[0]), __dadd_rn(up.v[SY], eU[1]));
+    c.v[LY] = LG(__dadd_rn(up.v[M], eU[2]), __dadd_rn(up.v[LY], eU[3]));
+    return c;
+}
+__device__ __forceinline__ Cell<5> backward_cell5_bf(const Cell<5> &nMi, const Cell<5> &nUp, const Cell<5> &nLo,
+                                                     const double *eM, const double *eU, const double *eL,
+                                                     const CoefAddr &cf) {
+    Cell<5> c;
+    double m = LC(__dadd_rn(nMi.v[M], eM[0]), __dadd_rn(nUp.v[SY], eU[0]));
+    m = LC(m, __dadd_rn(nUp.v[LY], eU[2]));
+    m = LC(m, __dadd_rn(nLo.v[SX], eL[0]));
+    c.v[M] = LC(m, __dadd_rn(nLo.v[LX], eL[2]));
+    c.v[SX] = LG(__dadd_rn(nMi.v[M], eM[1]), __dadd_rn(nLo.v[SX], eL[1]));
+    c.v[SY] = LG(__dadd_rn(nMi.v[M], eM[2]), __dadd_rn(nUp.v[SY], eU[1]));
+    c.v[LX] = LG(__dadd_rn(nMi.v[M], eM[3]), __dadd_rn(nLo.v[LX], eL[3]));
+    c.v[LY] = LG(__dadd_rn(nMi.v[M], eM[4]), __dadd_rn(nUp.v[LY], eU[3]));
+    return c;
+}
 #undef LG
 #undef LC
 template <int S>
 __device__ __forceinline__ Cell<S> forward_cell_sel(const Cell<S> &lo, const Cell<S> &mi, const Cell<S> &up,
                                                     const double *eL, const double *eM, const double *eU,
                                                     const CoefAddr &cf) {
-    static_assert(S == 3, "5-state bands run on wavefront5.cuh / wavefront_reg.cuh");
-    return forward_cell3_bf(lo, mi, up, eL, eM, eU, cf);
+    if constexpr (S == 3) return forward_cell3_bf(lo, mi, up, eL, eM, eU, cf);
+    else return forward_cell5_bf(lo, mi, up, eL, eM, eU, cf);  // only the over-wide fallback (global-memory ring)
 }
 template <int S>
 __device__ __forceinline__ Cell<S> backward_cell_sel(const Cell<S> &nMi, const Cell<S> &nUp, const Cell<S> &nLo,
                                                      const double *eM, const double *eU, const double *eL,
                                                      const CoefAddr &cf) {
-    static_assert(S == 3, "5-state bands run on wavefront5.cuh / wavefront_reg.cuh");
-    return backward_cell3_bf(nMi, nUp, nLo, eM, eU, eL, cf);
+    if constexpr (S == 3) return backward_cell3_bf(nMi, nUp, nLo, eM, eU, eL, cf);
+    else return backward_cell5_bf(nMi, nUp, nLo, eM, eU, eL, cf);
 }
 
 #include "wavefront_reg.cuh"
 
-template <int S, bool FULL, int LPI>
+// Ring accesses of the two kernels below.  GR = false: the ring is shared memory.  GR = true: the ring is a slice of a
+// global scratch buffer (bands wider than 227 KB of shared memory can hold, up to the widest gap box the split rule
+// allows); a warp's lanes exchange cells through it, so the accesses go to L2 (ld.cg / st.cg) and the __syncwarp
+// between diagonals orders them.
+template <int S, bool GR>
+__device__ __forceinline__ Cell<S> ring_load(const double *p) {
+    return GR ? cell_load_cg<S>(p) : cell_load<S>(p);
+}
+template <int S, bool GR>
+__device__ __forceinline__ void ring_store(double *p, const Cell<S> &c) {
+    if (GR) {
+#pragma unroll
+        for (int s = 0; s < S; s++) __stcg(p + s, c.v[s]);
+    } else {
+        cell_store<S>(p, c);
+    }
+}
+
+template <int S, bool FULL, int LPI, bool GR = false>
 __global__ void __launch_bounds__(THREADS_PER_BLOCK)
 k_forward(const __grid_constant__ DevModel model, Blob bl, int n_regions, double *__restrict__ F,
-          double *__restrict__ FT, int *counter, int ring_w) {
+          double *__restrict__ FT, int *counter, int ring_w, double *g_ring = nullptr) {
     extern __shared__ __align__(16) unsigned char dyn_smem_raw[];
     __shared__ DevModel sm;
     __shared__ __align__(16) CoefTable ct;
@@ -306,7 +352,8 @@ k_forward(const __grid_constant__ DevModel model, Blob bl, int n_regions, double
     const CoefAddr cf = (unsigned) __cvta_generic_to_shared(&ct.coef[0][0][lane32 & (W5_COPIES - 1)]);
     const int slot_id = (threadIdx.x >> 5) * (32 / LPI) + (lane32 / LPI);
     const unsigned gmask = LPI == 32 ? FULL_MASK : (0xffffu << (lane32 & 16));
-    double *ring = reinterpret_cast<double *>(dyn_smem_raw) + (size_t) slot_id * 3 * ring_w * S;
+    double *ring = GR ? g_ring + ((size_t) blockIdx.x * (THREADS_PER_BLOCK / LPI) + slot_id) * 3 * ring_w * S
+                      : reinterpret_cast<double *>(dyn_smem_raw) + (size_t) slot_id * 3 * ring_w * S;
     const double NINF = neg_inf();
 
     for (;;) {
@@ -327,7 +374,7 @@ k_forward(const __grid_constant__ DevModel model, Blob bl, int n_regions, double
                 for (int s = 0; s < S; s++) c.v[s] = init[s];
                 if (FULL) cell_store<S>(F + (c_prev1 + j) * S, c);
                 else F[c_prev1 + j] = c.v[M];
-                cell_store<S>(ring + (size_t) j * S, c);
+                ring_store<S, GR>(ring + (size_t) j * S, c);
             }
         }
         __syncwarp(gmask);
@@ -349,9 +396,9 @@ k_forward(const __grid_constant__ DevModel model, Blob bl, int n_regions, double
                 const int x = (d + xmy) >> 1, y = (d - xmy) >> 1;
                 const int cX = x > 0 ? sx[x - 1] : 4, cY = y > 0 ? sy[y - 1] : 4;
                 const int iLo = j + oLo, iUp = iLo + 1, iMi = j + oMi;
-                const Cell<S> lo = (iLo >= 0 && iLo < w1) ? cell_load<S>(slot1 + (size_t) iLo * S) : cell_fill<S>(NINF);
-                const Cell<S> up = (iUp >= 0 && iUp < w1) ? cell_load<S>(slot1 + (size_t) iUp * S) : cell_fill<S>(NINF);
-                const Cell<S> mi = (d >= 2 && iMi >= 0 && iMi < w2) ? cell_load<S>(slot2 + (size_t) iMi * S)
+                const Cell<S> lo = (iLo >= 0 && iLo < w1) ? ring_load<S, GR>(slot1 + (size_t) iLo * S) : cell_fill<S>(NINF);
+                const Cell<S> up = (iUp >= 0 && iUp < w1) ? ring_load<S, GR>(slot1 + (size_t) iUp * S) : cell_fill<S>(NINF);
+                const Cell<S> mi = (d >= 2 && iMi >= 0 && iMi < w2) ? ring_load<S, GR>(slot2 + (size_t) iMi * S)
                                                                      : cell_fill<S>(NINF);
                 const Cell<S> c = forward_cell_sel<S>(lo, mi, up, sm.etp_lower[cX], sm.etp_middle[cX * 5 + cY],
                                                       sm.etp_upper[cY], cf);
@@ -360,7 +407,7 @@ k_forward(const __grid_constant__ DevModel model, Blob bl, int n_regions, double
                     F[c_cur + j] = c.v[M];
                     if (ft != nullptr) cell_store<S>(ft + (int64_t) j * S, c);
                 }
-                cell_store<S>(slot + (size_t) j * S, c);
+                ring_store<S, GR>(slot + (size_t) j * S, c);
             }
             __syncwarp(gmask);
             c_cur = c_next;
@@ -374,10 +421,10 @@ k_forward(const __grid_constant__ DevModel model, Blob bl, int n_regions, double
 
 // ------------------------------------------------------------------------------------------------ backward
 
-template <int S, bool FULL, int LPI>
+template <int S, bool FULL, int LPI, bool GR = false>
 __global__ void __launch_bounds__(THREADS_PER_BLOCK)
 k_backward(const __grid_constant__ DevModel model, Blob bl, int n_tbs, double *__restrict__ B,
-           double *__restrict__ BT, double *__restrict__ edge, int *counter, int ring_w) {
+           double *__restrict__ BT, double *__restrict__ edge, int *counter, int ring_w, double *g_ring = nullptr) {
     extern __shared__ __align__(16) unsigned char dyn_smem_raw[];
     __shared__ DevModel sm;
     __shared__ __align__(16) CoefTable ct;
@@ -392,7 +439,8 @@ k_backward(const __grid_constant__ DevModel model, Blob bl, int n_tbs, double *_
     const unsigned gmask = LPI == 32 ? FULL_MASK : (0xffffu << (lane32 & 16));
     // The ring is private to the warp: the overlap diagonals (from, hi] that the reference discards must not reach
     // B, where they would collide with the next traceback's cells.
-    double *ring = reinterpret_cast<double *>(dyn_smem_raw) + (size_t) slot_id * 3 * ring_w * S;
+    double *ring = GR ? g_ring + ((size_t) blockIdx.x * (THREADS_PER_BLOCK / LPI) + slot_id) * 3 * ring_w * S
+                      : reinterpret_cast<double *>(dyn_smem_raw) + (size_t) slot_id * 3 * ring_w * S;
     const double NINF = neg_inf();
 
     for (;;) {
@@ -417,7 +465,7 @@ k_backward(const __grid_constant__ DevModel model, Blob bl, int n_tbs, double *_
                 Cell<S> c;
 #pragma unroll
                 for (int s = 0; s < S; s++) c.v[s] = init[s];
-                cell_store<S>(slot + (size_t) j * S, c);
+                ring_store<S, GR>(slot + (size_t) j * S, c);
                 if (keep) {
                     if (FULL) cell_store<S>(B + (c1 + j) * S, c);
                     else {
@@ -449,13 +497,13 @@ k_backward(const __grid_constant__ DevModel model, Blob bl, int n_tbs, double *_
                 // the neighbours consume X[x] and/or Y[y] (0-based); past the end they are out of band anyway
                 const int cX = x < rg.lX ? sx[x] : 4, cY = y < rg.lY ? sy[y] : 4;
                 const int iUp = j + oUp, iLo = iUp + 1, iMi = j + oMi;
-                const Cell<S> nUp = (iUp >= 0 && iUp < w1) ? cell_load<S>(slot1 + (size_t) iUp * S) : cell_fill<S>(NINF);
-                const Cell<S> nLo = (iLo >= 0 && iLo < w1) ? cell_load<S>(slot1 + (size_t) iLo * S) : cell_fill<S>(NINF);
-                const Cell<S> nMi = (have2 && iMi >= 0 && iMi < w2) ? cell_load<S>(slot2 + (size_t) iMi * S)
+                const Cell<S> nUp = (iUp >= 0 && iUp < w1) ? ring_load<S, GR>(slot1 + (size_t) iUp * S) : cell_fill<S>(NINF);
+                const Cell<S> nLo = (iLo >= 0 && iLo < w1) ? ring_load<S, GR>(slot1 + (size_t) iLo * S) : cell_fill<S>(NINF);
+                const Cell<S> nMi = (have2 && iMi >= 0 && iMi < w2) ? ring_load<S, GR>(slot2 + (size_t) iMi * S)
                                                                      : cell_fill<S>(NINF);
                 const Cell<S> c = backward_cell_sel<S>(nMi, nUp, nLo, sm.etp_middle[cX * 5 + cY], sm.etp_upper[cY],
                                                        sm.etp_lower[cX], cf);
-                cell_store<S>(slot + (size_t) j * S, c);
+                ring_store<S, GR>(slot + (size_t) j * S, c);
                 if (keep) {
                     if (FULL) cell_store<S>(B + (c0 + j) * S, c);
                     else {
@@ -1099,13 +1147,28 @@ int run_dp(const DevModel &dm, const mab_plan *plan, const Blob &bl, const Works
         const bool wave5 = S == 5;
         const WaveLaunch lf = wave5 ? wave_launch(S, nR2, h) : wave_launch_for(S, 1, h, false),
                          lb = wave5 ? wave_launch(S, nT2, h) : wave_launch_for(S, 1, h, false);
-        if (lf.warps < 1 || lb.warps < 1) {
-            mab_set_error("band too wide for the shared-memory ring (max width %lld cells); lower diagonalExpansion or "
-                          "splitMatrixBiggerThanThis", (long long) h.max_width);
-            return MAB_E_ARG;
-        }
         const int ring_w = (int) h.max_width;
-        if constexpr (S == 5) {
+        if (lf.warps < 1 || lb.warps < 1) {
+            // A diagonal wider than a shared-memory ring can hold (~1850 cells for 5 states): the reference handles any
+            // gap box up to splitMatrixBiggerThanThis (3000 x 3000 at marginAlign's realign call site).  The class-2
+            // items of such a batch run on the one-lane ring kernels with the ring in a global scratch buffer (L2):
+            // slow, correct, and only the batches that contain such a box pay.
+            const int gf = grid_for(nR2, 2), gb = grid_for(nT2, 2);
+            const size_t bytes = (size_t) 3 * ring_w * S * sizeof(double) * WARPS_PER_BLOCK * std::max(gf, gb);
+            double *g_ring = nullptr;
+            if ((rc = check(cudaMallocAsync((void **) &g_ring, bytes, st), "over-wide ring scratch"))) return rc;
+            {
+                LaunchTimer lt(K_FORWARD, st);
+                k_forward<S, FULL, 32, true><<<gf, THREADS_PER_BLOCK, 0, st>>>(dm, bl, nR2, w.fwd, w.fwd_tot,
+                                                                                w.counters + 0, ring_w, g_ring);
+            }
+            {
+                LaunchTimer lt(K_BACKWARD, st);
+                k_backward<S, FULL, 32, true><<<gb, THREADS_PER_BLOCK, 0, st>>>(dm, bl, nT2, w.bwd, w.bwd_tot, w.edge,
+                                                                                 w.counters + 1, ring_w, g_ring);
+            }
+            if ((rc = check(cudaFreeAsync(g_ring, st), "over-wide ring scratch"))) return rc;
+        } else if constexpr (S == 5) {
             auto kf = k_forward5<FULL, COEF_SMEM, 1>;
             auto kb = k_backward5<FULL, COEF_SMEM, 1>;
             if (lf.G == 2) kf = k_forward5<FULL, COEF_SMEM, 2>;

@@ -490,3 +490,16 @@ def test_compact_pair_coordinates_are_the_same_pairs(golden):
     l32 = wide.get_aligned_pairs_using_anchors(model, long_b, P)
     for a in ("offsets", "x", "y", "p"):
         assert np.array_equal(getattr(l32, a), getattr(l16, a)), a
+
+
+def test_over_wide_gap_box_runs_on_the_global_ring(engine, golden):
+    """A 2200 x 2200 unanchored gap box (marginAlign's realign split limit allows up to 3000 x 3000): its diagonals
+    are wider than any shared-memory ring (~1850 cells for five states), which failed the whole batch in round 1.  The
+    class-2 items of such a batch run with the ring in global memory; pairs and expectations match the oracle, and the
+    narrow alignments in the same batch are untouched."""
+    b = _with_gap_box(mab.synth.make_trna_batch(20, seed=71), 2200)
+    spec = golden.model_arrays("fixture5asym")
+    model, om = gpu_model(spec), oracle_model(po, spec)
+    P = mab.AlignmentParameters()
+    assert mab.Plan.from_batch(b, P).info.max_width > 1900
+    _oracle_check(engine, model, om, b, P, po.make_params(expansion=10, split=3000 ** 2), "over-wide")
