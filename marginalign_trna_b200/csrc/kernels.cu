@@ -1195,12 +1195,12 @@ int run_dp(const DevModel &dm, const mab_plan *plan, const Blob &bl, const Works
             {
                 LaunchTimer lt(K_FORWARD, st);
                 kf<<<grid_for(nR2, lf.blocks_per_sm, lf.warps), lf.warps * 32, lf.ring_bytes, st>>>(
-                    dm, bl, nR2, w.fwd, w.fwd_tot, w.counters + 0, ring_w);
+                    dm, bl, nR2, w.fwd, w.fwd_tot, w.counters + 0, ring_w, nullptr);
             }
             {
                 LaunchTimer lt(K_BACKWARD, st);
                 kb<<<grid_for(nT2, lb.blocks_per_sm, lb.warps), lb.warps * 32, lb.ring_bytes, st>>>(
-                    dm, bl, nT2, w.bwd, w.bwd_tot, w.edge, w.counters + 1, ring_w);
+                    dm, bl, nT2, w.bwd, w.bwd_tot, w.edge, w.counters + 1, ring_w, nullptr);
             }
         }
     }
