@@ -3,7 +3,7 @@ EM expectations) behind the cPecanRealign call sites of marginAlign / marginCall
 
 (The project is named marginalign-trna_b200; the package directory carries the importable spelling.)
 """
-from . import build, caller, capi, em, hmm, realign_sam, seqio, shard, synth  # noqa: F401
+from . import build, caller, capi, chain_sam, em, hmm, realign_sam, seqio, shard, synth  # noqa: F401
 from .hmm import Hmm  # noqa: F401
 from .pairhmm import (AlignmentParameters, DevicePlan, PairHmmEngine, PairHmmModel, Plan,  # noqa: F401
                       PosteriorPairs, RealignedCigars, jitter_table)

@@ -7,6 +7,7 @@ Re-statement for Python 3 of what marginAlign does between reading the (chained)
                                                                              GPU call here, no temp files)
   realignSamFile3TargetFn            src/margin/marginAlignLib.py:320-370   hard / soft clips re-attached, length
                                                                              assertions, SAM rebuilt positionally
+  chainSamFile (optional first step)  src/margin/marginAlignLib.py:159-199   chain_sam.py
 No pysam: records are parsed by seqio.sam_read.  Unaligned records are dropped, as samIterator does (utils.py:108-114).
 """
 from typing import Dict, List, Sequence
@@ -101,11 +102,16 @@ def realign_records(engine, model, records, references, gap_gamma=0.5, match_gam
     return out
 
 
-def realign_sam(sam_in, reference_fasta, sam_out, model, engine, gap_gamma=0.5, match_gamma=0.0):
-    """realignSamFileTargetFn without chaining / EM (marginAlignLib.py:265-296 with --noChain and a given model):
-    sam_in -> sam_out with every aligned record's cigar replaced by its pair-HMM realignment."""
+def realign_sam(sam_in, reference_fasta, sam_out, model, engine, gap_gamma=0.5, match_gamma=0.0, read_fastq=None):
+    """realignSamFileTargetFn with a given model (marginAlignLib.py:265-296, no EM): sam_in -> sam_out with every
+    aligned record's cigar replaced by its pair-HMM realignment.  With `read_fastq` the local alignments are first
+    chained into one alignment per read (chainSamFile, chain_sam.py); without it the SAM is taken as it is
+    (--noChain)."""
     header, records = seqio.sam_read(sam_in)
     references = seqio.fasta_dict(reference_fasta)
+    if read_fastq is not None:
+        from . import chain_sam
+        records = chain_sam.chain_records(records, list(seqio.fastq_read(read_fastq)), references)
     out = realign_records(engine, model, records, references, gap_gamma, match_gamma)
     seqio.sam_write(sam_out, header, out)
     return len(out)
