@@ -118,6 +118,58 @@ def main():
         env["modifyHmmEmissionsByExpectedVariationRate"](h3, 0.1)
         out["postprocess"].append({"modelType": model_type, "before": before, "flat": flat, "flat_gc50": gc50,
                                    "gc35": gc35, "variation_0.1": [float(v) for v in h3.emissions]})
+    # ---- marginCaller collation + SNV loop (marginCallerLib.py:59-69 and :189-209): the loop bodies are cut out of the
+    # two job functions (whose surroundings are jobTree / pysam plumbing) and run on a posterior file written the way
+    # cPecanRealign's writePosteriorProbs does ("%d\t%d\t%f", cPecanRealign.c:346-351) from posteriors of the reference C
+    # library (oracle/_ref) for three short fixture reads, one of them with an N and a lower-case base planted
+    import sys
+    import tempfile
+    import textwrap
+    sys.path.insert(0, os.path.dirname(os.path.dirname(HERE)))
+    from oracle import pyoracle as po
+    from oracle import pyref
+    lib_src = open(os.path.join(REF, "src/margin/marginCallerLib.py")).read().split("\n")
+    i0 = next(k for k, l in enumerate(lib_src) if "#Now collate the reference position expectations" in l)
+    i1 = next(k for k, l in enumerate(lib_src) if "#Pickle the posterior probs" in l)
+    collate_src = textwrap.dedent("\n".join(lib_src[i0:i1]))
+    j0 = next(k for k, l in enumerate(lib_src) if "#Now do the SNV calculations" in l)
+    j1 = next(k for k, l in enumerate(lib_src) if "# Write to VCF" in l)
+    snv_src = textwrap.dedent("\n".join(lib_src[j0:j1]))
+    case = json.load(open(os.path.join(HERE, "caller_case.json")))
+    alns = json.load(open(os.path.join(HERE, "bigmutations_alignments.json")))
+    model = pyref.RefModel.load(model_path)
+    picked, reads_in, pairs_in = [13, 19, 27], [], []
+
+    class Opt:
+        noMargin = False
+        threshold = case["threshold"]
+
+    expectations = {}
+    for n, k in enumerate(picked):
+        a = alns[k]
+        y = a["y"]
+        if n == 0:
+            y = y[:40] + "N" + y[41:60] + y[60:80].lower() + y[80:]
+        anc = po.anchors_from_cigar(a["ops"], a["lens"], a["x"], y)
+        pairs = pyref.aligned_pairs(model, a["x"], y, anc, expansion=10, split=100 * 100)
+        with tempfile.NamedTemporaryFile("w", suffix=".txt", delete=False) as fh:
+            for p_int, x, yy in pairs.tolist():
+                fh.write("%d\t%d\t%f\n" % (case["where"][k][1] + x, yy, float(p_int) / 10000000))
+            path = fh.name
+        env2 = dict(env)
+        env2.update(tempPosteriorProbsFile=path, referenceSequenceName=case["where"][k][0], querySequence=y,
+                    options=Opt, expectationsOfBasesAtEachPosition=expectations)
+        exec(collate_src, env2)
+        os.remove(path)
+        reads_in.append({"aln": k, "y": y})
+        pairs_in.append(pairs.tolist())
+    env3 = dict(env)
+    env3.update(expectationsOfBasesAtEachPosition=expectations, refSequences=case["references"], options=Opt,
+                variantCalls=[], errorSubstitutionMatrix=err, evolutionarySubstitutionMatrix=null)
+    exec(snv_src, env3)
+    out["collate"] = {"reads": reads_in, "pairs": pairs_in,
+                      "expectations": [[k[0], k[1]] + [v[b] for b in "ACGT"] for k, v in expectations.items()],
+                      "calls": [list(c) for c in env3["variantCalls"]], "threshold": case["threshold"]}
     with open(os.path.join(HERE, "py_reference_vectors.json"), "w") as fh:
         json.dump(out, fh)
     print({k: len(v) for k, v in out.items()})

@@ -106,3 +106,21 @@ def test_caller_oracle_is_pinned_to_the_reference_functions(vec):
         evo = co.null_matrix() if rec["evo"] == "null" else err
         post = co.calc_base_posterior_probs(dict(zip("ACGT", rec["obs"])), rec["ref"], evo, err)
         assert [post[b] for b in "ACGT"] == rec["post"], rec
+
+
+def test_caller_collation_and_snv_loop_are_pinned(vec):
+    """The loop bodies of posteriorProbabilityCalculationTargetFn (marginCallerLib.py:59-69: `%f` round trip, float sums,
+    N / lower-case read bases) and variantCallSamFileTargetFn (:189-209), cut out of the reference and run on posteriors
+    of the reference C library: oracle/caller_oracle.py gives the same expectations and the same calls, to the bit."""
+    with open(os.path.join(GOLDEN, "caller_case.json")) as fh:
+        case = json.load(fh)
+    c = vec["collate"]
+    where = [case["where"][r["aln"]] for r in c["reads"]]
+    exp = co.collate(c["pairs"], [r["y"] for r in c["reads"]], [w[0] for w in where], [w[1] for w in where])
+    want = {(e[0], e[1]): e[2:] for e in c["expectations"]}
+    assert set(exp) == set(want) and len(want) > 1000
+    for k, v in want.items():
+        assert [exp[k][b] for b in "ACGT"] == v, k
+    h = mab.Hmm.loadHmm(os.path.join(GOLDEN, "input_model.hmm"))
+    calls, _post = co.variant_calls(exp, case["references"], co.substitution_matrix(h.emissions), c["threshold"])
+    assert sorted(map(tuple, calls)) == sorted(tuple(x) for x in c["calls"]) and len(calls) > 0
