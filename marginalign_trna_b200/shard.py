@@ -296,6 +296,46 @@ class ShardedPairHmm:
         self.last_phases["merge_s"] = time.perf_counter() - t3
         return out
 
+    def realign(self, model, batch, params=None, gap_gamma=0.5, match_gamma=0.0, dst=0):
+        """PairHmmEngine.realign over all ranks: every rank realigns its contiguous shard on its GPU (posteriors, AMAP
+        reweight, MEA chain, cigar), only the cigars travel to rank `dst` -- a few bytes per read instead of the pairs --
+        and are concatenated in input order, the order marginAlignLib.py:334 consumes.  Others return None."""
+        from .pairhmm import RealignedCigars
+        params = params or AlignmentParameters()
+        if self.world == 1:
+            return self.engine.realign(model, batch, params, gap_gamma=gap_gamma, match_gamma=match_gamma)
+        import time
+        t0 = time.perf_counter()
+        shards = self.shards(batch, params)
+        self.last_shards = shards
+        mine = shards[self.rank]
+        sub = batch.slice(mine[0], mine[-1] + 1) if len(mine) else batch.slice(0, 0)
+        t1 = time.perf_counter()
+        res = self.engine.realign(model, sub, params, gap_gamma=gap_gamma, match_gamma=match_gamma)
+        t2 = time.perf_counter()
+        arrays = (np.asarray(res.off_ops, dtype=np.int64), np.asarray(res.ops, dtype=np.uint8),
+                  np.asarray(res.lens, dtype=np.int32))
+        got = _gather_shared_memory(arrays, dst, self.group) if self.shared_memory else None
+        transport = "shared memory"
+        if got is None:
+            transport = "collective gather"
+            cols = [_gather_varlen(a, dst, self.comm_device, self.group) for a in arrays]
+            got = ([[cols[k][r] for k in range(3)] for r in range(self.world)], []) if self.rank == dst else None
+        t3 = time.perf_counter()
+        self.last_phases = {"partition_s": t1 - t0, "compute_s": t2 - t1, "gather_s": t3 - t2, "merge_s": 0.0,
+                            "transport": transport}
+        if self.rank != dst:
+            return None
+        parts, _keep = got
+        off, base = [np.zeros(1, dtype=np.int64)], 0
+        for p in parts:  # shards are contiguous and in rank order: concatenation restores the input order
+            off.append(np.asarray(p[0][1:]) + base)
+            base += int(p[0][-1]) if len(p[0]) else 0
+        out = RealignedCigars(np.concatenate(off), np.concatenate([np.asarray(p[1]) for p in parts]),
+                              np.concatenate([np.asarray(p[2]) for p in parts]))
+        self.last_phases["merge_s"] = time.perf_counter() - t3
+        return out
+
     def get_expectations_using_anchors(self, model, batch, params=None, pseudo_count=1e-12):
         """All ranks receive the same summed (transitions, emissions, likelihood).  The pseudo-count is added once,
         as hmm_constructEmpty(1e-12) does for one cPecanRealign process (cPecanRealign.c:531)."""

@@ -28,8 +28,10 @@ def _worker(rank, world, port, out_path):
         assert sh.world == world
         res = sh.get_aligned_pairs_using_anchors(model, b)
         T, E, lik = sh.get_expectations_using_anchors(model, b)
+        cig = sh.realign(model, b)
         if rank == 0:
-            np.savez(out_path, offsets=res.offsets, x=res.x, y=res.y, p=res.p, exp=np.concatenate([T, E, [lik]]))
+            np.savez(out_path, offsets=res.offsets, x=res.x, y=res.y, p=res.p, exp=np.concatenate([T, E, [lik]]),
+                     c_off=cig.off_ops, c_ops=cig.ops, c_lens=cig.lens)
         else:
             assert res is None
             np.save(out_path + ".rank%d.npy" % rank, np.concatenate([T, E, [lik]]))
@@ -54,6 +56,9 @@ def test_two_ranks_equal_one_engine(tmp_path):
     one = eng.get_aligned_pairs_using_anchors(model, b)
     for k in ("offsets", "x", "y", "p"):
         assert np.array_equal(got[k], getattr(one, k)), k
+    cig = eng.realign(model, b)
+    assert np.array_equal(got["c_off"], cig.off_ops) and np.array_equal(got["c_ops"], cig.ops)
+    assert np.array_equal(got["c_lens"], cig.lens)
     T, E, lik = eng.get_expectations_using_anchors(model, b)
     want = np.concatenate([T, E, [lik]])
     np.testing.assert_allclose(got["exp"], want, rtol=1e-11, atol=0)

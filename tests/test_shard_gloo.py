@@ -41,6 +41,17 @@ class OracleEngine:
         cat = lambda l: (np.concatenate(l) if l else np.zeros(0)).astype(np.int32)
         return PosteriorPairs(np.array(offs, dtype=np.int64), cat(xs), cat(ys), cat(ps))
 
+    def realign(self, model, batch, params, gap_gamma=0.5, match_gamma=0.0):
+        po, off, ops, lens = self.po, [0], [], []
+        for i in range(batch.n):
+            anc = po.anchors_from_cigar(*batch.cigar(i), batch.x(i), batch.y(i))
+            rows, _chain = po.realign(self.om, batch.x(i), batch.y(i), anc, self._oparams(params), gap_gamma, match_gamma)
+            ops += rows[:, 0].tolist()
+            lens += rows[:, 1].tolist()
+            off.append(len(ops))
+        return mab.RealignedCigars(np.array(off, dtype=np.int64), np.array(ops, dtype=np.uint8),
+                                   np.array(lens, dtype=np.int32))
+
     def get_expectations_using_anchors(self, model, batch, params, pseudo_count=1e-12):
         po = self.po
         T, E, lik = np.full(25, pseudo_count), np.full(80, pseudo_count), 0.0
@@ -109,6 +120,11 @@ def _worker(rank, world, port, out_dir):
         res = sh.get_aligned_pairs_using_anchors(None, b, P, dst=0)
         T, E, lik = sh.get_expectations_using_anchors(None, b, P)
         np.savez(os.path.join(out_dir, "exp_%d.npz" % rank), T=T, E=E, lik=lik)
+        cig = sh.realign(None, b, P)
+        if rank == 0:
+            np.savez(os.path.join(out_dir, "cigars.npz"), off=cig.off_ops, ops=cig.ops, lens=cig.lens)
+        else:
+            assert cig is None
         if rank == 0:
             np.savez(os.path.join(out_dir, "pairs.npz"), offsets=res.offsets, x=res.x, y=res.y, p=res.p)
         else:
@@ -149,6 +165,9 @@ def test_world_size_2_gloo_matches_single_process(tmp_path):
     got = np.load(tmp_path / "pairs.npz")
     for a in ("offsets", "x", "y", "p"):
         assert np.array_equal(got[a], getattr(whole, a)), a
+    want_c, got_c = eng.realign(None, b, P), np.load(tmp_path / "cigars.npz")
+    assert np.array_equal(got_c["off"], want_c.off_ops) and np.array_equal(got_c["ops"], want_c.ops)
+    assert np.array_equal(got_c["lens"], want_c.lens) and len(want_c.ops) > 10
     T, E, lik = eng.get_expectations_using_anchors(None, b, P)
     for r in range(2):
         e = np.load(tmp_path / ("exp_%d.npz" % r))
