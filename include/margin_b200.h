@@ -160,6 +160,21 @@ int mab_expectations(const mab_model *m, const mab_plan *plan, const void *d_blo
  * sub-sequences); the pairs and their order are the same. */
 int mab_posteriors_emit_i16(const mab_plan *plan, const void *d_blob, void *d_ws, int64_t ws_bytes, int16_t *d_x,
         int16_t *d_y, int32_t *d_p, int64_t capacity, void *stream);
+/* mab_posteriors_compute for callers that may not allocate device memory (code under CUDA graph capture, tight serving
+ * loops, harnesses that forbid cudaMalloc).  No counterpart in the reference.
+ * Same arguments, same results as mab_posteriors_compute; the difference is the scratch of the over-wide
+ * band kernels (diagonals wider than a shared-memory ring, ~1850 cells for five states), which mab_posteriors_compute
+ * takes from cudaMallocAsync and this call takes from a static device array of MAB_NOALLOC_SCRATCH_BYTES that every
+ * GPU loading the library holds until exit.  The call itself issues no cudaMalloc / cudaFree or allocating library
+ * routine.  Limit: one block of the over-wide kernels needs 3 * max_width * S * 8 * 4 bytes of ring, so the widest
+ * band it takes is MAB_NOALLOC_SCRATCH_BYTES / (96 * S) cells (69905 for five states, 116508 for three); beyond that
+ * it returns MAB_E_CAPACITY with a message and runs nothing.  With fewer rings than mab_posteriors_compute would
+ * allocate, the over-wide items run on fewer blocks (slower, same results).  All calls on one GPU share the array
+ * (nothing in it has to be cleared: every ring cell is written before it is read), so two calls that overlap on the
+ * GPU -- different streams or host threads -- race; serialise them. */
+#define MAB_NOALLOC_SCRATCH_BYTES (32u << 20)
+int mab_posteriors_compute_noalloc(const mab_model *m, const mab_plan *plan, const void *d_blob, void *d_ws,
+        int64_t ws_bytes, int64_t *d_pair_off, int64_t *d_n_pairs, void *stream);
 /* ---- realign tail --------------------------------------------------------------------------------
  * Replaces what cPecanRealign does with the posterior pairs of an alignment before it prints the new cigar
  * (cPecanRealign.c:590-631): reweightAlignedPairs2 (pairwiseAligner.c:1251-1261; AMAP gap reweighting),

@@ -63,6 +63,7 @@ SIGNATURES = {
                                         vp, vp, vp, vp, C.c_int64, vp, C.POINTER(vp), i64p]),
     "mab_plan_device_blob": (vp, [vp]),
     "mab_posteriors_compute": (C.c_int, [vp, vp, vp, vp, C.c_int64, vp, vp, vp]),
+    "mab_posteriors_compute_noalloc": (C.c_int, [vp, vp, vp, vp, C.c_int64, vp, vp, vp]),
     "mab_posteriors_emit": (C.c_int, [vp, vp, vp, C.c_int64, vp, vp, vp, C.c_int64, vp]),
     "mab_posteriors_emit_i16": (C.c_int, [vp, vp, vp, C.c_int64, vp, vp, vp, C.c_int64, vp]),
     "mab_expectations": (C.c_int, [vp, vp, vp, vp, C.c_int64, vp, vp]),

@@ -27,6 +27,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <mutex>
 #include <vector>
 
 #include "mab_internal.h"
@@ -34,6 +35,10 @@
 #define WARPS_PER_BLOCK 4
 #define THREADS_PER_BLOCK (WARPS_PER_BLOCK * 32)
 #define FULL_MASK 0xffffffffu
+
+// scratch of mab_posteriors_compute_noalloc (see static_ring_address below); MAB_NOALLOC_SCRATCH_BYTES in margin_b200.h
+#define MAB_STATIC_RING_BYTES ((size_t) 32 << 20)
+static __device__ __align__(256) double g_static_ring[MAB_STATIC_RING_BYTES / sizeof(double)];
 
 namespace {
 
@@ -1117,6 +1122,42 @@ int rr_grid(K kernel, int64_t items, int items_per_block) {
     return (int) std::max<int64_t>(1, std::min(want, cap));
 }
 
+// ---- mab_posteriors_compute_noalloc: over-wide ring scratch that is never allocated ------------------------------
+// The one place this library allocates device memory on its own is the ring scratch of the over-wide kernels
+// (k_forward / k_backward with GR = true, below).  Callers that cannot allocate (CUDA graph capture, serving loops,
+// harnesses that forbid cudaMalloc) get the same kernels with the ring in this file-scope array instead: 32 MiB, held
+// by every GPU that loads the library until the process exits.  In host code `g_static_ring` is only a stand-in for the
+// symbol, not a device address: static_ring_address() asks the runtime once per device (with that device current) and
+// that pointer is what the kernels receive (the array itself is defined at file scope, top of this file).  The kernels initialise every ring cell they read (the same code runs on
+// uninitialised cudaMallocAsync memory), so nothing has to be cleared between calls; all calls on one GPU share the
+// array, so calls that overlap on the GPU (two streams) race.
+#define MAB_MAX_DEVICES 64
+double *g_static_ring_addr[MAB_MAX_DEVICES];  // per device, from cudaGetSymbolAddress
+std::mutex g_static_ring_mutex;
+
+int static_ring_address(double **out) {
+    int dev = -1, rc;
+    if ((rc = check(cudaGetDevice(&dev), "cudaGetDevice"))) return rc;
+    if (dev < 0 || dev >= MAB_MAX_DEVICES) {
+        mab_set_error("static ring scratch: device ordinal %d outside 0..%d", dev, MAB_MAX_DEVICES - 1);
+        return MAB_E_ARG;
+    }
+    std::lock_guard<std::mutex> lock(g_static_ring_mutex);
+    if (!g_static_ring_addr[dev]) {
+        void *ptr = nullptr;
+        if ((rc = check(cudaGetSymbolAddress(&ptr, g_static_ring), "cudaGetSymbolAddress(static ring scratch)")))
+            return rc;
+        g_static_ring_addr[dev] = static_cast<double *>(ptr);
+    }
+    *out = g_static_ring_addr[dev];
+    return MAB_OK;
+}
+
+// set by mab_posteriors_compute_noalloc for the duration of its call (per host thread): run_dp takes the over-wide
+// ring from here instead of cudaMallocAsync
+thread_local double *t_ext_ring = nullptr;
+thread_local size_t t_ext_ring_bytes = 0;
+
 // forward + backward + totals: shared by posterior mode (FULL = false) and expectation mode (FULL = true).
 // The order arrays list the work items by band class (mab_internal.h): class 2 (wide bands) first -- they run on the
 // shared-memory-ring kernels, G warps per item -- then class 1 (a warp per item) and class 0 (a half-warp per item) on
@@ -1153,10 +1194,27 @@ int run_dp(const DevModel &dm, const mab_plan *plan, const Blob &bl, const Works
             // gap box up to splitMatrixBiggerThanThis (3000 x 3000 at marginAlign's realign call site).  The class-2
             // items of such a batch run on the one-lane ring kernels with the ring in a global scratch buffer (L2):
             // slow, correct, and only the batches that contain such a box pay.
-            const int gf = grid_for(nR2, 2), gb = grid_for(nT2, 2);
-            const size_t bytes = (size_t) 3 * ring_w * S * sizeof(double) * WARPS_PER_BLOCK * std::max(gf, gb);
+            int gf = grid_for(nR2, 2), gb = grid_for(nT2, 2);
+            const size_t block_bytes = (size_t) 3 * ring_w * S * sizeof(double) * WARPS_PER_BLOCK;
+            const size_t bytes = block_bytes * std::max(gf, gb);
             double *g_ring = nullptr;
-            if ((rc = check(cudaMallocAsync((void **) &g_ring, bytes, st), "over-wide ring scratch"))) return rc;
+            const bool ext_ring = t_ext_ring != nullptr;
+            if (ext_ring) {
+                // no-allocation variant: as many blocks as the static scratch has rings for (the work queue hands
+                // every block item after item, so a smaller grid only takes longer)
+                const size_t fit = t_ext_ring_bytes / block_bytes;
+                if (fit < 1) {
+                    mab_set_error("mab_posteriors_compute_noalloc: a band of %d cells needs %zu bytes of ring scratch per "
+                                  "block, the static scratch holds %zu (widest band it can take: %zu cells for %d states); "
+                                  "use mab_posteriors_compute",
+                                  ring_w, block_bytes, t_ext_ring_bytes,
+                                  t_ext_ring_bytes / ((size_t) 3 * S * sizeof(double) * WARPS_PER_BLOCK), S);
+                    return MAB_E_CAPACITY;
+                }
+                gf = (int) std::min<size_t>(gf, fit), gb = (int) std::min<size_t>(gb, fit);
+                g_ring = t_ext_ring;
+            } else if ((rc = check(cudaMallocAsync((void **) &g_ring, bytes, st), "over-wide ring scratch")))
+                return rc;
             {
                 LaunchTimer lt(K_FORWARD, st);
                 k_forward<S, FULL, 32, true><<<gf, THREADS_PER_BLOCK, 0, st>>>(dm, bl, nR2, w.fwd, w.fwd_tot,
@@ -1167,7 +1225,7 @@ int run_dp(const DevModel &dm, const mab_plan *plan, const Blob &bl, const Works
                 k_backward<S, FULL, 32, true><<<gb, THREADS_PER_BLOCK, 0, st>>>(dm, bl, nT2, w.bwd, w.bwd_tot, w.edge,
                                                                                  w.counters + 1, ring_w, g_ring);
             }
-            if ((rc = check(cudaFreeAsync(g_ring, st), "over-wide ring scratch"))) return rc;
+            if (!ext_ring && (rc = check(cudaFreeAsync(g_ring, st), "over-wide ring scratch"))) return rc;
         } else if constexpr (S == 5) {
             auto kf = k_forward5<FULL, COEF_SMEM, 1>;
             auto kb = k_backward5<FULL, COEF_SMEM, 1>;
@@ -1429,6 +1487,22 @@ extern "C" int mab_posteriors_compute(const mab_model *m, const mab_plan *plan, 
     return m->S == 5 ? run_posteriors<5>(dm, plan, d_blob, w, d_pair_off, d_n_pairs, st)
                      : run_posteriors<3>(dm, plan, d_blob, w, d_pair_off, d_n_pairs, st);
 }
+
+// mab_posteriors_compute without any allocation (margin_b200.h): the over-wide ring comes from g_static_ring.
+extern "C" int mab_posteriors_compute_noalloc(const mab_model *m, const mab_plan *plan, const void *d_blob, void *d_ws,
+                                              int64_t ws_bytes, int64_t *d_pair_off, int64_t *d_n_pairs, void *stream) {
+    int rc = require_gpu();
+    if (rc) return rc;
+    double *ring = nullptr;
+    if ((rc = static_ring_address(&ring))) return rc;
+    struct Scope {  // run_dp sees the static ring only inside this call
+        Scope(double *p) { t_ext_ring = p, t_ext_ring_bytes = MAB_STATIC_RING_BYTES; }
+        ~Scope() { t_ext_ring = nullptr, t_ext_ring_bytes = 0; }
+    } scope(ring);
+    return mab_posteriors_compute(m, plan, d_blob, d_ws, ws_bytes, d_pair_off, d_n_pairs, stream);
+}
+
+static_assert(MAB_STATIC_RING_BYTES == MAB_NOALLOC_SCRATCH_BYTES, "header and scratch array disagree");
 
 namespace {
 template <typename XY>
