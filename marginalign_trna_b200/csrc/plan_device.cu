@@ -11,7 +11,8 @@
 //   k_bands           one thread per region: band_construct -> DiagDesc (region-local cell offsets), then the traceback
 //                     schedule in count mode -> cells / tracebacks / totals / edge cells / full cells per region
 //   scan              those five counts (one struct scan)
-//   k_schedule        one thread per region: rebase cell offsets, write TracebackDesc / TotalDesc / diagonal flags
+//   k_schedule        one thread per region: TracebackDesc / TotalDesc (the serial part of the schedule)
+//   k_diag_fill       one thread per diagonal: cell offsets region-local -> global, per-diagonal total flags
 //   sort x2           regions and tracebacks longest first (stable radix sort: same order as the host's stable_sort)
 //   k_symbols         bases -> symbol codes
 // Two tiny D2H reads (counts) size the later arrays.  The result is byte-identical to the host planner's blob except
@@ -120,9 +121,10 @@ __device__ __forceinline__ void store_region(const DevInput &in, int64_t a, int6
 // are stored from inside the walk.
 template <bool WRITE>
 __global__ void k_regions(DevInput in, mab_params p, int64_t *region_count /* [n+1] or aln_region in WRITE */,
-                          Status *status, RegionDesc *regions, RegionTmp *tmp, int64_t *diag_count) {
-    const int64_t a_raw = (int64_t) blockIdx.x * blockDim.x + threadIdx.x;
-    const bool live = a_raw < in.n;
+                          Status *status, RegionDesc *regions, RegionTmp *tmp, int64_t *diag_count, int spread) {
+    const int64_t gt = (int64_t) blockIdx.x * blockDim.x + threadIdx.x;
+    const int64_t a_raw = gt >> spread;
+    const bool live = a_raw < in.n && (gt & ((1 << spread) - 1)) == 0;
     const int64_t a = live ? a_raw : 0;  // idle lanes shadow alignment 0 so the whole warp stays in the stepping loop
     if (in.n == 0) return;
     const AlnInput ai = aln_input(in, a);
@@ -191,9 +193,10 @@ struct CountSink {
 
 __global__ void k_bands(DevInput in, mab_params p, int64_t n_regions, RegionDesc *regions, const RegionTmp *tmp,
                         const int64_t *diag_base, DiagDesc *diags, int32_t *diag_region, RegionCounts *counts,
-                        Status *status) {
-    const int64_t r = (int64_t) blockIdx.x * blockDim.x + threadIdx.x;
-    if (r >= n_regions) return;
+                        Status *status, int spread) {
+    const int64_t gt = (int64_t) blockIdx.x * blockDim.x + threadIdx.x;
+    const int64_t r = gt >> spread;
+    if (r >= n_regions || (gt & ((1 << spread) - 1)) != 0) return;
     const RegionDesc rg = regions[r];
     const RegionTmp t = tmp[r];
     const AlnInput ai = aln_input(in, rg.aln);
@@ -242,12 +245,8 @@ struct WriteSink {
         n_full += w;
         totals[n_tot++] = td;
     }
-    __device__ __forceinline__ void diag_flags(int64_t q, int64_t tot_in_region, bool is_total, bool no_middle) {
-        uint32_t tf = (uint32_t) (tot_base + tot_in_region);
-        if (is_total) tf |= MAB_DIAG_IS_TOTAL;
-        if (no_middle) tf |= MAB_DIAG_NO_MIDDLE;
-        dd[q].tot_flags = tf;
-    }
+    // the per-diagonal flags are written by k_diag_fill, one thread per diagonal, from the tracebacks stored here
+    __device__ __forceinline__ void diag_flags(int64_t, int64_t, bool, bool) {}
     __device__ __forceinline__ void traceback(int64_t lo, int64_t hi, int64_t from, bool at_end, int64_t n, int64_t edge_cells) {
         TracebackDesc tb;
         tb.region = region;
@@ -266,8 +265,10 @@ struct WriteSink {
 __global__ void k_schedule(mab_params p, int64_t n_regions, RegionDesc *regions, const int64_t *diag_base,
                            const RegionCounts *base /* exclusive scan, [n_regions + 1] */, DiagDesc *diags,
                            TracebackDesc *tbs, TotalDesc *totals, int32_t *region_key, int32_t *tb_key,
-                           int64_t n_diagonals, Status *status) {
-    const int64_t r = (int64_t) blockIdx.x * blockDim.x + threadIdx.x;
+                           int64_t n_diagonals, Status *status, int spread) {
+    const int64_t gt = (int64_t) blockIdx.x * blockDim.x + threadIdx.x;
+    if ((gt & ((1 << spread) - 1)) != 0) return;
+    const int64_t r = gt >> spread;
     if (r == 0) {  // sentinel diagonal carrying the total cell count
         DiagDesc s;
         s.cell_off = base[n_regions].cells;
@@ -282,7 +283,6 @@ __global__ void k_schedule(mab_params p, int64_t n_regions, RegionDesc *regions,
     const int64_t D = (int64_t) rg.lX + rg.lY, n_cells = nb.cells - b.cells;
     WriteSink sink{dd, tbs + b.tbs, totals + b.tots, (int32_t) r, b.tots, b.edge, b.full};
     plan_core::schedule_walk(p, D, WidthFromDiags{dd, D, n_cells}, sink);
-    for (int64_t d = 0; d <= D; d++) dd[d].cell_off += b.cells;  // region-local -> global
     // sort keys: band class first (class 2 leads the order arrays), then length
     const int cls = mab_band_class(mab_region_span(rg.flags));
     const int32_t key_cap = (1 << 28) - 1;
@@ -297,6 +297,37 @@ __global__ void k_schedule(mab_params p, int64_t n_regions, RegionDesc *regions,
     rg.n_tot = (int32_t) sink.n_tot;
     regions[r] = rg;
     region_key[r] = (cls << 28) | (int32_t) min(D, (int64_t) key_cap);
+}
+
+// One thread per diagonal, after k_schedule: region-local cell offsets -> global, and the flags schedule_walk's
+// diag_flags would have written (plan_core.h): diagonal q in (lo, from] of a traceback is the k = from - q-th posterior
+// diagonal of that traceback; every tenth one carries a total.  Coalesced, where the per-region loops it replaces read
+// and wrote every DiagDesc of a region from one thread (2 GB of sector traffic per 113 k tRNA regions).
+__global__ void k_diag_fill(int64_t n_diagonals, const int32_t *__restrict__ diag_region, const int64_t *__restrict__ diag_base,
+                            const RegionCounts *__restrict__ base, const RegionDesc *__restrict__ regions,
+                            const TracebackDesc *__restrict__ tbs, DiagDesc *diags) {
+    const int64_t g = (int64_t) blockIdx.x * blockDim.x + threadIdx.x;
+    if (g >= n_diagonals) return;
+    const int32_t r = diag_region[g];
+    const int32_t q = (int32_t) (g - diag_base[r]);
+    DiagDesc d = diags[g];
+    d.cell_off += base[r].cells;
+    if (q >= 1) {
+        const int32_t tb0 = regions[r].tb_base, n_tb = regions[r].n_tb;
+        int32_t lo_i = 0, hi_i = n_tb - 1;  // first traceback with from >= q (their (lo, from] ranges tile 1 .. D)
+        while (lo_i < hi_i) {
+            const int32_t mid = (lo_i + hi_i) >> 1;
+            if (tbs[tb0 + mid].from >= q) hi_i = mid;
+            else lo_i = mid + 1;
+        }
+        const TracebackDesc tb = tbs[tb0 + lo_i];
+        const int32_t k = tb.from - q;
+        uint32_t tf = (uint32_t) (tb.tot_base + k / 10);
+        if (k % 10 == 0) tf |= MAB_DIAG_IS_TOTAL;
+        if (q - 2 < tb.lo) tf |= MAB_DIAG_NO_MIDDLE;
+        d.tot_flags = tf;
+    }
+    diags[g] = d;
 }
 
 __global__ void k_symbols(const uint8_t *seq, int64_t n, uint8_t *sym /* 16 guard bytes on both sides */) {
@@ -357,6 +388,16 @@ int cuda_fail(cudaError_t e, const char *what) {
 }
 
 inline int grid(int64_t n, int block) { return (int) std::max<int64_t>(1, (n + block - 1) / block); }
+
+// The walks are one thread per alignment / region.  A batch of few, long alignments (600 reads of 10 kb per chunk) would
+// leave that to a handful of warps whose lanes, each in its own stretch of a different read, take turns: 12 ms per walk
+// on 3 thread blocks.  Such batches are spread out, one item per 2^spread threads (only the first one works), so every
+// item gets a warp -- and with it an instruction stream -- of its own; dense batches (tRNA) keep 32 items per warp.
+inline int spread_for(int64_t n) {
+    int s = 5;
+    while (s > 0 && (n << s) > 300000) s--;
+    return s;
+}
 
 }  // namespace
 
@@ -421,7 +462,10 @@ extern "C" int mab_plan_build_device(const mab_params *p, int64_t n, const uint8
     int64_t *d_aln_region = ar.ptr<int64_t>(h.off_aln_region);
     if ((rc = cuda_fail(cudaMemsetAsync(d_status, 0, 256, st), "memset"))) return rc;
     if ((rc = cuda_fail(cudaMemsetAsync(d_aln_region + n, 0, 8, st), "memset"))) return rc;
-    if (n > 0) k_regions<false><<<grid(n, 128), 128, 0, st>>>(in, *p, d_aln_region, d_status, nullptr, nullptr, nullptr);
+    const int spread_a = spread_for(n);
+    if (n > 0)
+        k_regions<false><<<grid(n << spread_a, 128), 128, 0, st>>>(in, *p, d_aln_region, d_status, nullptr, nullptr, nullptr,
+                                                                 spread_a);
     {  // also for empty inputs: the guard bytes must be set
         k_symbols<<<grid(std::max<int64_t>(len_x, 16), 256), 256, 0, st>>>(d_seq_x, len_x, ar.ptr<uint8_t>(h.off_sym_x));
         k_symbols<<<grid(std::max<int64_t>(len_y, 16), 256), 256, 0, st>>>(d_seq_y, len_y, ar.ptr<uint8_t>(h.off_sym_y));
@@ -493,17 +537,22 @@ extern "C" int mab_plan_build_device(const mab_params *p, int64_t n, const uint8
     if (nR > 0) {
         if ((rc = cuda_fail(cudaMemsetAsync(d_diag_base + nR, 0, 8, st), "memset"))) return rc;
         if ((rc = cuda_fail(cudaMemsetAsync(d_counts + nR, 0, sizeof(RegionCounts), st), "memset"))) return rc;
-        k_regions<true><<<grid(n, 128), 128, 0, st>>>(in, *p, d_aln_region, d_status, d_regions, d_tmp, d_diag_base);
+        const int spread_r = spread_for(nR);
+        k_regions<true><<<grid(n << spread_a, 128), 128, 0, st>>>(in, *p, d_aln_region, d_status, d_regions, d_tmp, d_diag_base,
+                                                                 spread_a);
         cub::DeviceScan::ExclusiveSum(d_cub, scan_tmp2, d_diag_base, d_diag_base, nR + 1, st);
-        k_bands<<<grid(nR, 128), 128, 0, st>>>(in, *p, nR, d_regions, d_tmp, d_diag_base, d_diags,
-                                               ar.ptr<int32_t>(h.off_diag_region), d_counts, d_status);
+        k_bands<<<grid(nR << spread_r, 128), 128, 0, st>>>(in, *p, nR, d_regions, d_tmp, d_diag_base, d_diags,
+                                                           ar.ptr<int32_t>(h.off_diag_region), d_counts, d_status, spread_r);
         cub::DeviceScan::ExclusiveScan(d_cub, scan_tmp3, d_counts, d_bases, SumCounts(), RegionCounts{0, 0, 0, 0, 0}, nR + 1,
                                        st);
         int32_t *rkey = ar.ptr<int32_t>(at_rkey), *rkey2 = ar.ptr<int32_t>(at_rkey2), *riota = ar.ptr<int32_t>(at_riota);
         int32_t *tkey = ar.ptr<int32_t>(at_tkey), *tkey2 = ar.ptr<int32_t>(at_tkey2), *tiota = ar.ptr<int32_t>(at_tiota);
-        k_schedule<<<grid(nR, 128), 128, 0, st>>>(*p, nR, d_regions, d_diag_base, d_bases, d_diags,
-                                                  ar.ptr<TracebackDesc>(h.off_tracebacks),
-                                                  ar.ptr<TotalDesc>(h.off_totals), rkey, tkey, nD, d_status);
+        k_schedule<<<grid(nR << spread_r, 128), 128, 0, st>>>(*p, nR, d_regions, d_diag_base, d_bases, d_diags,
+                                                              ar.ptr<TracebackDesc>(h.off_tracebacks),
+                                                              ar.ptr<TotalDesc>(h.off_totals), rkey, tkey, nD, d_status,
+                                                              spread_r);
+        k_diag_fill<<<grid(nD, 256), 256, 0, st>>>(nD, ar.ptr<int32_t>(h.off_diag_region), d_diag_base, d_bases, d_regions,
+                                                   ar.ptr<TracebackDesc>(h.off_tracebacks), d_diags);
         if ((rc = cuda_fail(cudaMemcpyAsync(&totals, d_bases + nR, sizeof(totals), cudaMemcpyDeviceToHost, st), "copy")))
             return rc;
         if ((rc = cuda_fail(cudaMemcpyAsync(&hs, d_status, sizeof(hs), cudaMemcpyDeviceToHost, st), "copy"))) return rc;

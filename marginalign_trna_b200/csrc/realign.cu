@@ -228,9 +228,13 @@ struct Frontier {
     }
 };
 
-__global__ void __launch_bounds__(128) k_rl_chain(RlArgs a) {
-    const int64_t al = (int64_t) blockIdx.x * blockDim.x + threadIdx.x;
-    if (al >= a.n) return;
+// One thread per alignment; `spread` > 0 gives every alignment 2^spread threads of which the first one works, so that
+// the few long alignments of a long-read batch each get an instruction stream of their own instead of taking turns
+// inside a handful of diverged warps (rl_spread below).
+__global__ void __launch_bounds__(128) k_rl_chain(RlArgs a, int spread) {
+    const int64_t gt = (int64_t) blockIdx.x * blockDim.x + threadIdx.x;
+    const int64_t al = gt >> spread;
+    if (al >= a.n || (gt & ((1 << spread) - 1)) != 0) return;
     const int64_t ox = a.off_x[al], oy = a.off_y[al], p0 = a.pair_off[al];
     const int lX = (int) (a.off_x[al + 1] - ox), lY = (int) (a.off_y[al + 1] - oy);
     // the pairs of this alignment were clipped by the capacity, or it has more pairs than half the jitter stream (the
@@ -318,6 +322,12 @@ __global__ void __launch_bounds__(128) k_rl_chain(RlArgs a) {
     a.cnt[2 * al + 1] = m;
 }
 
+inline int rl_spread(int64_t n) {  // same rule as the planner's spread_for (plan_device.cu)
+    int s = 5;
+    while (s > 0 && (n << s) > 300000) s--;
+    return s;
+}
+
 // exclusive scans of the per-alignment op counts and chain lengths (one block)
 __global__ void __launch_bounds__(1024) k_rl_scan(const int32_t *cnt, int64_t n, int64_t *op_off, int64_t *chain_off) {
     __shared__ long long warp_sums[2][32];
@@ -373,9 +383,10 @@ __global__ void __launch_bounds__(1024) k_rl_scan(const int32_t *cnt, int64_t n,
 
 __global__ void __launch_bounds__(128)
 k_rl_emit(RlArgs a, const int64_t *op_off, const int64_t *chain_off, uint8_t *ops, int32_t *lens, int32_t *chain_x,
-          int32_t *chain_y) {
-    const int64_t al = (int64_t) blockIdx.x * blockDim.x + threadIdx.x;
-    if (al >= a.n) return;
+          int32_t *chain_y, int spread) {
+    const int64_t gt = (int64_t) blockIdx.x * blockDim.x + threadIdx.x;
+    const int64_t al = gt >> spread;
+    if (al >= a.n || (gt & ((1 << spread) - 1)) != 0) return;
     const int64_t oy = a.off_y[al];
     const int lX = (int) (a.off_x[al + 1] - a.off_x[al]), lY = (int) (a.off_y[al + 1] - oy);
     const int2 *chain = reinterpret_cast<const int2 *>(a.front + oy + 2 * al);
@@ -500,7 +511,8 @@ extern "C" int mab_realign_chain(int64_t n, const int64_t *d_off_x, const int64_
         k_rl_weights<<<(unsigned) blocks_w, 256, 0, st>>>(a);
         mab_launch_timer_end(t);
         t = mab_launch_timer_begin(MAB_K_RL_CHAIN, st);
-        k_rl_chain<<<(unsigned) ((n + 127) / 128), 128, 0, st>>>(a);
+        const int spread = rl_spread(n);
+        k_rl_chain<<<(unsigned) (((n << spread) + 127) / 128), 128, 0, st>>>(a, spread);
         mab_launch_timer_end(t);
     }
     void *t = mab_launch_timer_begin(MAB_K_RL_SCAN, st);
@@ -522,8 +534,9 @@ extern "C" int mab_realign_emit(int64_t n, const int64_t *d_off_x, const int64_t
         return MAB_E_ARG;
     }
     void *t = mab_launch_timer_begin(MAB_K_RL_EMIT, stream);
-    k_rl_emit<<<(unsigned) ((n + 127) / 128), 128, 0, (cudaStream_t) stream>>>(a, d_op_off, d_chain_off, d_ops, d_lens,
-                                                                            d_chain_x, d_chain_y);
+    const int spread = rl_spread(n);
+    k_rl_emit<<<(unsigned) (((n << spread) + 127) / 128), 128, 0, (cudaStream_t) stream>>>(a, d_op_off, d_chain_off, d_ops,
+                                                                                          d_lens, d_chain_x, d_chain_y, spread);
     mab_launch_timer_end(t);
     return rl_check(cudaGetLastError(), "realign emit launch");
 }
