@@ -5,7 +5,7 @@ EM expectations) behind the cPecanRealign call sites of marginAlign / marginCall
 """
 from . import build, caller, capi, chain_sam, em, hmm, realign_sam, seqio, shard, synth  # noqa: F401
 from .hmm import Hmm  # noqa: F401
-from .pairhmm import (AlignmentParameters, DevicePlan, PairHmmEngine, PairHmmModel, Plan,  # noqa: F401
+from .pairhmm import (AlignmentParameters, DevicePlan, PairHmmEngine, PairHmmModel, Plan, PlanCache,  # noqa: F401
                       PosteriorPairs, RealignedCigars, jitter_table)
 from .synth import AlignmentBatch  # noqa: F401
 

@@ -9,6 +9,7 @@ rank.  What stays: model initialisation order, sampling of alignments by aligned
 keep-old-emissions rules, running likelihoods, model file written every iteration (the reference's checkpoint),
 random-restart trials with best-likelihood selection.
 """
+import inspect
 import random
 from dataclasses import dataclass, field
 from typing import List, Optional
@@ -16,7 +17,7 @@ from typing import List, Optional
 import numpy as np
 
 from .hmm import Hmm
-from .pairhmm import AlignmentParameters, PairHmmModel
+from .pairhmm import AlignmentParameters, PairHmmModel, PlanCache
 
 
 @dataclass
@@ -110,9 +111,13 @@ def expectation_maximisation(runner, batch, output_model, options, rng=random):
     work = batch if len(idx) == batch.n else batch.subset(idx)
     params = options.params()
     running = []
+    # the band plans do not depend on the model: runners that can keep them in HBM plan `work` once (pairhmm.PlanCache)
+    extra = {}
+    if "plan_cache" in inspect.signature(runner.get_expectations_using_anchors).parameters:
+        extra["plan_cache"] = PlanCache()
     for iteration in range(options.iterations):
         model = PairHmmModel.from_hmm(hmm)
-        T, E, lik = runner.get_expectations_using_anchors(model, work, params)
+        T, E, lik = runner.get_expectations_using_anchors(model, work, params, **extra)
         new = Hmm(hmm.modelType)
         new.addExpectations(T, E, lik)
         hmm = maximisation(new, hmm, options)

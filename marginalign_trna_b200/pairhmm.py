@@ -287,6 +287,9 @@ class DevicePlan:
             self.d_ws = _torch().empty(self.ws_bytes + 256, dtype=_torch().uint8, device=self.device)
             self.ws_ptr = (self.d_ws.data_ptr() + 255) & ~255
 
+    def drop_workspace(self):
+        self.d_ws, self.ws_ptr = None, None
+
     def adopt(self, stream):
         """Hands a plan built on another stream (already synchronised) over to `stream`: the caching allocator must
         not recycle the blob or the inputs while kernels of `stream` still read them."""
@@ -386,6 +389,40 @@ class _null:
         return False
 
 
+class PlanCache:
+    """Device plans of one batch kept in HBM between calls.  The band geometry of an alignment (anchors, split regions,
+    bands, checkpoint schedule: cPecanRealign recomputes all of it in every EM iteration, cPecanEm.py:139-165 ->
+    cPecanRealign.c:567) does not depend on the HMM, so the EM loop plans its alignments once and every later
+    iteration starts at the forward sweep: no packing, no upload, no planner kernels.  Pass the same object to
+    get_expectations_using_anchors for every call on the same (batch, parameters); a cache that was filled for another
+    batch, other banding parameters or the other mode is refilled.  Holds the plan blobs only (~5.5 kB per tRNA read;
+    workspaces are scratch and allocated per call); `max_bytes` bounds what it keeps (default: a quarter of the HBM
+    free when it is filled) -- a batch whose plans do not fit is simply planned again every call."""
+
+    def __init__(self, max_bytes=None):
+        self.max_bytes = max_bytes
+        self.batch, self.key, self.plans = None, None, None
+        self.hits = 0
+
+    @staticmethod
+    def _key(params, expectations):
+        return tuple(getattr(params, f) for f in sorted(vars(params)) if not f.startswith("_")) + (bool(expectations),)
+
+    def lookup(self, batch, params, expectations):
+        """The kept plans if they were made for this very batch object (the cache holds a reference to it, so the
+        identity test cannot be fooled by a recycled id), these parameters and this mode."""
+        if self.plans is not None and self.batch is batch and self.key == self._key(params, expectations):
+            self.hits += 1
+            return self.plans
+        return None
+
+    def store(self, batch, params, expectations, plans):
+        self.batch, self.key, self.plans = batch, self._key(params, expectations), plans
+
+    def clear(self):
+        self.batch, self.key, self.plans = None, None, None
+
+
 class PairHmmEngine:
     """Runs batches on one GPU.  `max_cells` bounds the number of DP cells resident at once (28 B of HBM each in
     posterior mode, 80 B in expectation mode).  plan_on = "device" (default): raw inputs are uploaded and the plan is
@@ -475,8 +512,37 @@ class PairHmmEngine:
     def _stream_ptr(self):
         return C.c_void_p(self.torch.cuda.current_stream(self.device).cuda_stream)
 
-    def _device_plans(self, batch, params, expectations):
-        """Yields one DevicePlan per chunk.  Host planning of chunk k+1 overlaps the GPU work on chunk k."""
+    def _device_plans(self, batch, params, expectations, cache=None):
+        """Yields one DevicePlan per chunk.  Host planning of chunk k+1 overlaps the GPU work on chunk k.  With a
+        PlanCache the plans of a batch are kept and re-used by the next call (see PlanCache)."""
+        if cache is None:
+            yield from self._build_device_plans(batch, params, expectations)
+            return
+        kept = cache.lookup(batch, params, expectations)
+        if kept is not None:
+            for dplan in kept:
+                dplan.alloc_workspace()
+                yield dplan
+                dplan.drop_workspace()  # scratch only: freed in stream order, the next chunk's takes its place
+            return
+        cache.clear()
+        budget = cache.max_bytes
+        if budget is None:
+            budget = self.torch.cuda.mem_get_info(self.device)[0] // 4
+        keep, used = [], 0
+        for dplan in self._build_device_plans(batch, params, expectations):
+            yield dplan
+            if keep is not None:
+                used += int(dplan.d_blob.numel())
+                if used > budget:
+                    keep = None  # does not fit: this batch is planned again next time
+                else:
+                    dplan.drop_workspace()
+                    keep.append(dplan)
+        if keep is not None:
+            cache.store(batch, params, expectations, keep)
+
+    def _build_device_plans(self, batch, params, expectations):
         chunks = self._chunks(batch, params, expectations)
         torch = self.torch
         if self.plan_on == "device":
@@ -682,11 +748,13 @@ class PairHmmEngine:
         capi.check(capi.load().mab_expectations(model._h, dplan.plan._h, dplan.blob_ptr, dplan.ws_ptr,
                                                 dplan.ws_bytes, d_out.data_ptr(), self._stream_ptr()))
 
-    def get_expectations_using_anchors(self, model, batch, params=None, pseudo_count=1e-12, as_hmm=False):
+    def get_expectations_using_anchors(self, model, batch, params=None, pseudo_count=1e-12, as_hmm=False,
+                                       plan_cache=None):
         """EM expectations summed over the batch: (transitions[S*S], emissions[S*16], likelihood).
 
         Starts from hmm_constructEmpty(1e-12) like cPecanRealign.c:531 (pseudo-count on transitions and emissions,
-        likelihood 0)."""
+        likelihood 0).  plan_cache: a PlanCache that keeps the batch's device plans for the next call (the EM loop
+        passes one: only the model changes between iterations)."""
         params = params or AlignmentParameters()
         torch = self.torch
         S = model.state_number
@@ -696,7 +764,7 @@ class PairHmmEngine:
         with torch.cuda.device(self.device):
             d_out = torch.from_numpy(init).to(self.device)
             done = []  # one event per chunk: at most two chunks' workspaces are alive, and the host never waits for
-            for dplan in self._device_plans(batch, params, True):  # the chunk it has just queued
+            for dplan in self._device_plans(batch, params, True, plan_cache):  # the chunk it has just queued
                 info = dplan.plan.info
                 if len(done) >= 2:
                     done[-2].synchronize()

@@ -12,6 +12,8 @@ torch.distributed) owns a shard of the alignments:
 
 This module only moves indices and small vectors; the arithmetic is PairHmmEngine's (CUDA, no CPU fallback).
 """
+import inspect
+
 import numpy as np
 
 from .pairhmm import AlignmentParameters, PosteriorPairs
@@ -336,17 +338,29 @@ class ShardedPairHmm:
         self.last_phases["merge_s"] = time.perf_counter() - t3
         return out
 
-    def get_expectations_using_anchors(self, model, batch, params=None, pseudo_count=1e-12):
+    def get_expectations_using_anchors(self, model, batch, params=None, pseudo_count=1e-12, plan_cache=None):
         """All ranks receive the same summed (transitions, emissions, likelihood).  The pseudo-count is added once,
-        as hmm_constructEmpty(1e-12) does for one cPecanRealign process (cPecanRealign.c:531)."""
+        as hmm_constructEmpty(1e-12) does for one cPecanRealign process (cPecanRealign.c:531).  plan_cache: a
+        pairhmm.PlanCache; every rank keeps the device plans of its own shard between calls."""
         params = params or AlignmentParameters()
+        extra = {}
+        if plan_cache is not None and "plan_cache" in inspect.signature(
+                self.engine.get_expectations_using_anchors).parameters:
+            extra["plan_cache"] = plan_cache
         if self.world == 1:
-            return self.engine.get_expectations_using_anchors(model, batch, params, pseudo_count=pseudo_count)
-        shards = self.shards(batch, params)
-        self.last_shards = shards
-        mine = shards[self.rank]
-        sub = batch.slice(mine[0], mine[-1] + 1) if len(mine) else batch.slice(0, 0)
-        T, E, lik = self.engine.get_expectations_using_anchors(model, sub, params, pseudo_count=0.0)
+            return self.engine.get_expectations_using_anchors(model, batch, params, pseudo_count=pseudo_count, **extra)
+        sub = None
+        if plan_cache is not None:  # the shard object must be the same one for the cache to recognise it
+            if getattr(plan_cache, "_shard_of", None) is batch:
+                sub = plan_cache._shard
+        if sub is None:
+            shards = self.shards(batch, params)
+            self.last_shards = shards
+            mine = shards[self.rank]
+            sub = batch.slice(mine[0], mine[-1] + 1) if len(mine) else batch.slice(0, 0)
+            if plan_cache is not None:
+                plan_cache._shard_of, plan_cache._shard = batch, sub
+        T, E, lik = self.engine.get_expectations_using_anchors(model, sub, params, pseudo_count=0.0, **extra)
         vec = allreduce_expectations(np.concatenate([T, E, [lik]]), self.comm_device, self.group)
         nT, nE = len(T), len(E)
         return vec[:nT] + pseudo_count, vec[nT:nT + nE] + pseudo_count, float(vec[-1])

@@ -100,3 +100,33 @@ def test_config2_on_the_two_alignments_of_input_sam(tmp_path, golden):
 def engine_cells(b):
     plan = mab.Plan.from_batch(b, mab.AlignmentParameters(split_matrix_bigger_than=300))
     return plan.info.n_cells
+
+
+def test_plan_cache_reuses_the_device_plans_between_iterations(golden):
+    """The EM loop plans its batch once (pairhmm.PlanCache: the band geometry does not depend on the model,
+    cPecanRealign.c:567 recomputes it every iteration).  Several chunks, two models, three calls: cached calls give what
+    uncached calls give (the same kernels on the same plan; sums differ only by the order of the atomic additions),
+    another batch or other banding parameters refill the cache."""
+    eng = mab.PairHmmEngine(max_cells=150_000)
+    b = mab.synth.make_trna_batch(400, seed=91)
+    P = mab.AlignmentParameters()
+    assert len(eng._chunks(b, P, True)) >= 3
+    models = [mab.PairHmmModel.from_arrays(*golden.model_arrays("fixture5asym")), mab.PairHmmModel.default(0)]
+    cache = mab.PlanCache()
+    for it, m in enumerate([models[0], models[1], models[0]]):
+        got = np.concatenate([np.ravel(v) for v in eng.get_expectations_using_anchors(m, b, P, plan_cache=cache)])
+        want = np.concatenate([np.ravel(v) for v in eng.get_expectations_using_anchors(m, b, P)])
+        np.testing.assert_allclose(got, want, rtol=1e-11, atol=0)
+        assert cache.hits == it and len(cache.plans) >= 3
+    b2 = mab.synth.make_trna_batch(400, seed=92)
+    eng.get_expectations_using_anchors(models[0], b2, P, plan_cache=cache)
+    assert cache.hits == 2 and cache.batch is b2
+    P2 = mab.AlignmentParameters(diagonal_expansion=12)
+    got = np.concatenate([np.ravel(v) for v in eng.get_expectations_using_anchors(models[0], b2, P2, plan_cache=cache)])
+    want = np.concatenate([np.ravel(v) for v in eng.get_expectations_using_anchors(models[0], b2, P2)])
+    np.testing.assert_allclose(got, want, rtol=1e-11, atol=0)
+    assert cache.hits == 2
+    tiny = mab.PlanCache(max_bytes=1)  # nothing fits: every call plans again, results unchanged
+    for _ in range(2):
+        got = np.concatenate([np.ravel(v) for v in eng.get_expectations_using_anchors(models[0], b, P, plan_cache=tiny)])
+    assert tiny.hits == 0 and tiny.plans is None
