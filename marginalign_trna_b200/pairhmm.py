@@ -381,6 +381,10 @@ class _Staging:
         return self.buf[:nbytes]
 
 
+def torch_props(torch, device):
+    return torch.cuda.get_device_properties(device)
+
+
 class _null:
     def __enter__(self):
         return self
@@ -463,8 +467,18 @@ class PairHmmEngine:
         160 B)."""
         free, _total = self.torch.cuda.mem_get_info(self.device)
         mem_cap = min(int(0.55 * free / (170 if expectations else 40)), 2_000_000_000)  # 32-bit side offsets
-        group = min(8, max(1, -(-(params.diagonal_expansion + 2) // 16)))
-        want_alignments = 6144 // group
+        # regions resident at once in the forward kernel: the register kernels hold 5 blocks of 128 threads per SM, a
+        # half-warp per region while the band span fits 16 lanes (expansion <= 13), a warp up to expansion 29
+        # (mab_band_class); a chunk slightly larger than that would run the sweep twice, the second time for a handful
+        # of regions.  (The forward sweep of 10 kb reads stays bound by its 20 000 sequential diagonals, ~1.2 us each:
+        # 8000 reads at expansion 10 take 70 ms forward against 36 ms backward whatever the chunking.)
+        sms = torch_props(self.torch, self.device).multi_processor_count
+        if params.diagonal_expansion <= 13:
+            want_alignments = sms * 5 * 8
+        elif params.diagonal_expansion <= 29:
+            want_alignments = sms * 5 * 4
+        else:
+            want_alignments = 6144 // min(8, max(1, -(-(params.diagonal_expansion + 2) // 16)))
         target = int(mean_est * want_alignments)
         return max(min(max(self.BASE_CELLS, target), mem_cap), 1), want_alignments
 
