@@ -290,13 +290,23 @@ class DevicePlan:
     def drop_workspace(self):
         self.d_ws, self.ws_ptr = None, None
 
-    def adopt(self, stream):
+    def use_workspace(self, buf):
+        """Scratch owned by somebody else (PairHmmEngine keeps one grow-only buffer for all its chunks)."""
+        assert buf.numel() >= self.ws_bytes + 256
+        self.d_ws = buf
+        self.ws_ptr = (buf.data_ptr() + 255) & ~255
+
+    def adopt(self, stream, workspace=None):
         """Hands a plan built on another stream (already synchronised) over to `stream`: the caching allocator must
-        not recycle the blob or the inputs while kernels of `stream` still read them."""
+        not recycle the blob or the inputs while kernels of `stream` still read them.  workspace: a function
+        bytes -> buffer that provides the scratch (default: an allocation of its own)."""
         for t in (self.d_blob,) + tuple(x for x in (self._inputs or ()) if hasattr(x, "record_stream")):
             if t is not None and t.is_cuda:
                 t.record_stream(stream)
-        self.alloc_workspace()
+        if workspace is not None:
+            self.use_workspace(workspace(self.ws_bytes + 256))
+        else:
+            self.alloc_workspace()
 
     @staticmethod
     def pack_inputs(batch, staging=None):
@@ -449,10 +459,25 @@ class PairHmmEngine:
             self.PLAN_AHEAD = max(1, int(plan_ahead))
         self.last_stats = {}
         self._t = {"wait_plan_s": 0.0, "plan_s": 0.0, "pack_s": 0.0, "compute_s": 0.0, "host_alloc_s": 0.0, "drain_s": 0.0}
+        self._ws_buf = None
         self._stagings = (_Staging(), _Staging())
         self._copy_stream = torch.cuda.Stream(device=self.device)
         self._plan_streams = [torch.cuda.Stream(device=self.device)]
         self._t_lock = threading.Lock()
+
+    def _workspace(self, nbytes):
+        """The DP scratch of the chunk being computed: ONE grow-only buffer per engine.  Chunks run one after the other
+        on the caller's stream, so they can share it; allocating it per chunk let the caching allocator carve smaller
+        tensors (pair outputs, plan arenas) out of a freed 46 GB block and then open another 46 GB segment for the next
+        chunk -- 20 000 reads of 10 kb at expansion 100 ran out of memory with 139 GB reserved and 1.4 GB in use.
+        release_workspace() gives it back."""
+        if self._ws_buf is None or self._ws_buf.numel() < nbytes:
+            self._ws_buf = None  # never hold two: the old block is recycled in stream order
+            self._ws_buf = self.torch.empty(int(nbytes), dtype=self.torch.uint8, device=self.device)
+        return self._ws_buf
+
+    def release_workspace(self):
+        self._ws_buf = None
 
     # ---------------------------------------------------------------- chunking
     CHUNK_RAMP = (4,)         # the first chunk is a quarter of the others, see _chunks
@@ -535,7 +560,7 @@ class PairHmmEngine:
         kept = cache.lookup(batch, params, expectations)
         if kept is not None:
             for dplan in kept:
-                dplan.alloc_workspace()
+                dplan.use_workspace(self._workspace(dplan.ws_bytes + 256))
                 yield dplan
                 dplan.drop_workspace()  # scratch only: freed in stream order, the next chunk's takes its place
             return
@@ -595,7 +620,7 @@ class PairHmmEngine:
                     self._t["wait_plan_s"] += time.perf_counter() - t0
                     if ci + ahead < len(chunks):
                         futs.append(pool.submit(make, ci + ahead))
-                    dplan.adopt(torch.cuda.current_stream(self.device))
+                    dplan.adopt(torch.cuda.current_stream(self.device), self._workspace)
                     yield dplan
             return
         with ThreadPoolExecutor(1) as pool:
