@@ -538,13 +538,19 @@ def run_ours(args, rank, world, local_rank):
             run_e2e()  # warm-up: the device and page-locked allocator pools reach their steady state in 2-3 calls
         torch.cuda.synchronize()
         barrier()
+        ms0 = torch.cuda.memory_stats(dev)
         t0 = time.perf_counter()
         for _ in range(e2e_steps):
             run_e2e()
         torch.cuda.synchronize()
         dt = max_over_ranks((time.perf_counter() - t0) / e2e_steps)
+        ms1 = torch.cuda.memory_stats(dev)
         st = dict(eng.last_stats)
         e2e = {"value": total_cells / dt / 1e9, "unit": "GCUPS", "h2d_bytes_per_step": int(st["h2d_bytes"]),
+               # device allocator traffic inside the timed calls (cudaMalloc / cudaFree synchronise the device)
+               "allocator": {k: int(ms1.get(k, 0) - ms0.get(k, 0)) for k in
+                             ("num_device_alloc", "num_device_free", "num_alloc_retries")},
+               "chunks": int(st.get("chunks", 0)),
                "d2h_bytes_per_step": int(st["d2h_bytes"]), "ms_per_step": dt * 1e3, "steps": e2e_steps,
                "reads_per_s": n_reads * world / dt, "host_wall_s": st.get("host_wall"),
                "note": "packing of bases+cigars into pinned memory, H2D, planning on the GPU, DP kernels, %s, per step "

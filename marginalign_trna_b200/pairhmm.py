@@ -460,6 +460,7 @@ class PairHmmEngine:
         self.last_stats = {}
         self._t = {"wait_plan_s": 0.0, "plan_s": 0.0, "pack_s": 0.0, "compute_s": 0.0, "host_alloc_s": 0.0, "drain_s": 0.0}
         self._ws_buf = None
+        self._pool, self._slot_free = {}, [None, None]
         self._stagings = (_Staging(), _Staging())
         self._copy_stream = torch.cuda.Stream(device=self.device)
         self._plan_streams = [torch.cuda.Stream(device=self.device)]
@@ -478,6 +479,20 @@ class PairHmmEngine:
 
     def release_workspace(self):
         self._ws_buf = None
+        self._pool.clear()
+        self._slot_free = [None, None]
+
+    def _pooled(self, slot, name, numel, dtype):
+        """A view of `numel` elements of a grow-only device buffer owned by the engine (one per pipeline slot and
+        name).  The realign path sizes its per-chunk arrays by bounds (pairs: a quarter of the band cells, tail scratch
+        36 B per pair): allocated per chunk, 14 chunks of 10 kb reads cycled ~18 GB each through the caching allocator
+        (different sizes every time, cudaMalloc / cudaFree with device syncs) and e2e ran at 4.7 instead of 12 GCUPS."""
+        key = (slot, name)
+        buf = self._pool.get(key)
+        if buf is None or buf.numel() < numel or buf.dtype != dtype:
+            self._pool[key] = None
+            buf = self._pool[key] = self.torch.empty(int(numel * 1.1) + 64, dtype=dtype, device=self.device)
+        return buf[:numel]
 
     # ---------------------------------------------------------------- chunking
     CHUNK_RAMP = (4,)         # the first chunk is a quarter of the others, see _chunks
@@ -490,7 +505,14 @@ class PairHmmEngine:
         wave_launch in csrc/kernels.cu): a few hundred 10 kb reads per chunk would leave the forward kernel
         latency-bound.  Bounded by free HBM (posterior mode ~28 B of workspace per cell + outputs, expectation mode
         160 B)."""
+        # HBM this call can use: what the driver reports free, what the caching allocator holds without using it, and
+        # the engine's own grow-only buffers, which the chunks of this call will re-use.  (Counting only the first
+        # made the second call on 20 000 reads of 10 kb cut the batch into 236 chunks of 85 reads: the buffers of
+        # the first call looked like somebody else's memory.)
         free, _total = self.torch.cuda.mem_get_info(self.device)
+        free += self.torch.cuda.memory_reserved(self.device) - self.torch.cuda.memory_allocated(self.device)
+        free += self._ws_buf.numel() if self._ws_buf is not None else 0
+        free += sum(b.numel() * b.element_size() for b in self._pool.values() if b is not None)
         mem_cap = min(int(0.55 * free / (170 if expectations else 40)), 2_000_000_000)  # 32-bit side offsets
         # regions resident at once in the forward kernel: the register kernels hold 5 blocks of 128 threads per SM, a
         # half-warp per region while the band span fits 16 lanes (expansion <= 13), a warp up to expansion 29
@@ -673,7 +695,7 @@ class PairHmmEngine:
                     t.record_stream(self._copy_stream)
                 ev = torch.cuda.Event()
                 ev.record(self._copy_stream)
-            pending.append((a0, na, host, ev, dev))
+            pending.append((a0, na, host, ev, None))  # record_stream above keeps the device arrays until the copies ran
             self._t["host_alloc_s"] += time.perf_counter() - t1
 
         # coordinates are relative to the sub-sequences: 16 bits are enough unless one of them reaches 32768 bases, and
@@ -733,7 +755,7 @@ class PairHmmEngine:
 
     PAIRS_PER_CELL_CAP = 0.25  # output capacity of the sync-free path (measured: 0.07 pairs per cell at threshold 0.01)
 
-    def posteriors_async(self, model, dplan):
+    def posteriors_async(self, model, dplan, slot=None):
         """posteriors_device without the host sync: outputs are sized by a bound (PAIRS_PER_CELL_CAP x cells; the emit
         kernel clips at the capacity), the pair count follows asynchronously into pinned memory.  Returns a state
         dict; `posteriors_settle` must be called before the pairs are trusted."""
@@ -741,12 +763,18 @@ class PairHmmEngine:
         info = dplan.plan.info
         n = info.n_alignments
         cap = int(info.n_cells * self.PAIRS_PER_CELL_CAP) + 1024
-        st = dict(dplan=dplan, n=n, cap=cap,
-                  d_off=torch.empty(n + 1, dtype=torch.int64, device=self.device),
+        if slot is None:
+            new = lambda name, numel, dtype: torch.empty(numel, dtype=dtype, device=self.device)
+        else:  # the engine's buffers of this pipeline slot: the copies of the chunk that used them last must be done
+            new = lambda name, numel, dtype: self._pooled(slot, name, numel, dtype)
+            if self._slot_free[slot] is not None:
+                torch.cuda.current_stream(self.device).wait_event(self._slot_free[slot])
+        st = dict(dplan=dplan, n=n, cap=cap, slot=slot, new=new,
+                  d_off=new("d_off", n + 1, torch.int64),
                   d_np=torch.empty(1, dtype=torch.int64, device=self.device),
-                  d_x=torch.empty(cap, dtype=torch.int32, device=self.device),
-                  d_y=torch.empty(cap, dtype=torch.int32, device=self.device),
-                  d_p=torch.empty(cap, dtype=torch.int32, device=self.device),
+                  d_x=new("d_x", cap, torch.int32),
+                  d_y=new("d_y", cap, torch.int32),
+                  d_p=new("d_p", cap, torch.int32),
                   h_np=torch.empty(1, dtype=torch.int64, pin_memory=True))
         sp = self._stream_ptr()
         capi.check(L.mab_posteriors_compute(model._h, dplan.plan._h, dplan.blob_ptr, dplan.ws_ptr, dplan.ws_bytes,
@@ -879,13 +907,13 @@ def jitter_table(n_draws):
     return have
 
 
-def _realign_launch(engine, model, dplan, sub, expansion, gap_gamma, match_gamma, want_chain):
+def _realign_launch(engine, model, dplan, sub, expansion, gap_gamma, match_gamma, want_chain, slot=None):
     """Queues everything one chunk needs -- posteriors, realign chain, cigar emission -- without a host sync: the
     outputs are sized by bounds (at most 2 (lX + lY) + 1 operations and min(lX, lY) chain pairs per alignment)."""
     torch, L = engine.torch, capi.load()
     dev = engine.device
-    st = engine.posteriors_async(model, dplan)
-    n = st["n"]
+    st = engine.posteriors_async(model, dplan, slot)
+    n, new = st["n"], st["new"]
     off_x, off_y = sub.off_x, sub.off_y
     if getattr(dplan, "input_offsets", None) is not None:  # planned on the device: the offsets are already in HBM
         ox_ptr, oy_ptr, len_x, len_y = dplan.input_offsets
@@ -901,25 +929,25 @@ def _realign_launch(engine, model, dplan, sub, expansion, gap_gamma, match_gamma
     # _engine_realign raises if an alignment was refused because the 2^25-draw cap was hit)
     est = int(((off_x[1:] - off_x[:-1]) + (off_y[1:] - off_y[:-1]) + 1).max() * max(int(dplan.plan.info.max_width), 1)) if n else 0
     table = jitter_table(min(2 * est + 2, 1 << 25))
-    key = (str(dev), len(table))
-    if engine._jitter_dev is None or engine._jitter_dev[0] != key:
-        engine._jitter_dev = (key, torch.from_numpy(table).to(dev))
+    # grow-only on the device: a longer prefix of the same stream gives the same draws
+    if engine._jitter_dev is None or engine._jitter_dev[0] != str(dev) or engine._jitter_dev[1].numel() < len(table):
+        engine._jitter_dev = (str(dev), torch.from_numpy(table).to(dev))
     d_rand = engine._jitter_dev[1]
-    st["n_rand"] = len(table)
+    st["n_rand"] = int(d_rand.numel())
     st["span"] = np.asarray((off_x[1:] - off_x[:-1]) + (off_y[1:] - off_y[:-1]))
     cap = st["cap"]
     ws_bytes = int(L.mab_realign_workspace_bytes(n, cap, len_x, len_y))
-    d_ws = torch.empty(ws_bytes + 256, dtype=torch.uint8, device=dev)
+    d_ws = new("rl_ws", ws_bytes + 256, torch.uint8)
     ws_ptr = (d_ws.data_ptr() + 255) & ~255
     cap_ops = 2 * (len_x + len_y) + n + 1
     cap_chain = min(len_x, len_y) + 1
     st.update(len_x=len_x, len_y=len_y, d_offs=d_offs, h_offs=h_offs, ox_ptr=ox_ptr, oy_ptr=oy_ptr, d_ws=d_ws, ws_ptr=ws_ptr, ws_bytes=ws_bytes,
-              d_op_off=torch.empty(n + 1, dtype=torch.int64, device=dev),
-              d_ch_off=torch.empty(n + 1, dtype=torch.int64, device=dev),
-              d_ops=torch.empty(cap_ops, dtype=torch.uint8, device=dev),
-              d_lens=torch.empty(cap_ops, dtype=torch.int32, device=dev),
-              d_cx=torch.empty(cap_chain, dtype=torch.int32, device=dev) if want_chain else None,
-              d_cy=torch.empty(cap_chain, dtype=torch.int32, device=dev) if want_chain else None,
+              d_op_off=new("d_op_off", n + 1, torch.int64),
+              d_ch_off=new("d_ch_off", n + 1, torch.int64),
+              d_ops=new("d_ops", cap_ops, torch.uint8),
+              d_lens=new("d_lens", cap_ops, torch.int32),
+              d_cx=new("d_cx", cap_chain, torch.int32) if want_chain else None,
+              d_cy=new("d_cy", cap_chain, torch.int32) if want_chain else None,
               h_tot=torch.empty(2, dtype=torch.int64, pin_memory=True), d_rand=d_rand,
               gammas=(gap_gamma, match_gamma), want_chain=want_chain)
     _realign_kernels(engine, st)
@@ -952,7 +980,7 @@ def _realign_finish(engine, st):
     engine.posteriors_settle(st)
     if st["cap"] != before:  # the pair bound was too small (never seen at threshold 0.01): redo the tail, exact sizes
         ws_bytes = int(L.mab_realign_workspace_bytes(st["n"], st["cap"], st["len_x"], st["len_y"]))
-        st["d_ws"] = torch.empty(ws_bytes + 256, dtype=torch.uint8, device=engine.device)
+        st["d_ws"] = st["new"]("rl_ws", ws_bytes + 256, torch.uint8)
         st["ws_ptr"], st["ws_bytes"] = (st["d_ws"].data_ptr() + 255) & ~255, ws_bytes
         _realign_kernels(engine, st)
     st["done"].synchronize()
@@ -967,7 +995,14 @@ def _realign_finish(engine, st):
             t.record_stream(engine._copy_stream)
         ev = torch.cuda.Event()
         ev.record(engine._copy_stream)
-    st["dplan"] = None
+    # the chunk's device buffers (pair arrays sized by a bound, tail scratch: ~50 B per band cell) are done with once the
+    # copies above are queued; the caller keeps `st` until the end of the batch, so only what it reads later stays
+    # (20 000 reads of 10 kb ran out of HBM with 14 chunks' buffers alive)
+    if st.get("slot") is not None:
+        engine._slot_free[st["slot"]] = ev  # the slot's buffers may be written again once these copies have run
+    keep = {k: st[k] for k in ("span", "n_rand", "total")}
+    st.clear()
+    st.update(keep)
     return host, ev, st
 
 
@@ -989,7 +1024,7 @@ def _engine_realign(self, model, batch, params=None, gap_gamma=0.5, match_gamma=
             n = info.n_alignments
             t0 = time.perf_counter()
             st = _realign_launch(self, model, dplan, batch.slice(first, first + n), params.diagonal_expansion, gap_gamma,
-                                 match_gamma, want_chain)
+                                 match_gamma, want_chain, slot=stats["chunks"] & 1)
             t1 = time.perf_counter()
             self._t["host_alloc_s"] += t1 - t0  # queueing a chunk: buffers + launches, no sync
             if prev is not None:
