@@ -83,6 +83,31 @@ def test_long_reads_and_chunking(models):
         assert_same(r1, i, ops, chain, i)
 
 
+def test_repeated_calls_reuse_the_engine_buffers(models):
+    """The engine keeps its DP workspace and the bound-sized arrays of the realign path between chunks and calls
+    (pairhmm.py: _workspace, _pooled): chunks of different sizes and repeated calls on one engine -- several chunks, so
+    that both pipeline slots are written again while copies of an earlier chunk may still be queued -- give the same
+    cigars as a fresh engine, and the chunking of a call does not depend on what earlier calls left allocated."""
+    big = mab.synth.make_trna_batch(6000, seed=35)
+    small = mab.synth.make_trna_batch(700, seed=36)
+    eng = mab.PairHmmEngine(max_cells=2_000_000)
+    want_big = mab.PairHmmEngine(max_cells=2_000_000).realign(models[0], big, want_chain=True)
+    want_small = mab.PairHmmEngine(max_cells=2_000_000).realign(models[0], small, want_chain=True)
+    auto = mab.PairHmmEngine()
+    chunks = []
+    for b, want in ((small, want_small), (big, want_big), (small, want_small), (big, want_big)):
+        got = eng.realign(models[0], b, want_chain=True)
+        assert eng.last_stats["chunks"] >= (3 if b is big else 1)
+        for a in ("off_ops", "ops", "lens", "chain_off", "chain_x", "chain_y"):
+            assert np.array_equal(getattr(got, a), getattr(want, a)), a
+        auto.realign(models[0], b)
+        chunks.append(auto.last_stats["chunks"])
+    assert chunks[0] == chunks[2] and chunks[1] == chunks[3]
+    pairs = [eng.get_aligned_pairs_using_anchors(models[0], small) for _ in range(2)]
+    for a in ("offsets", "x", "y", "p"):
+        assert np.array_equal(getattr(pairs[0], a), getattr(pairs[1], a)), a
+
+
 def test_full_size_properties(engine, models):
     """100 k reads: every cigar spans its two sequences, match runs equal the chain, chains strictly increase."""
     b = mab.synth.make_trna_batch(100_000, seed=35)
