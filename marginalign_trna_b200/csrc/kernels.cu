@@ -763,6 +763,7 @@ k_emit_diag(Blob bl, int64_t n_diagonals, const int32_t *__restrict__ pint, cons
 #define EXP_WARPS 4
 #define EXP_COLS 8     // bin columns per warp: lanes with the same (lane % EXP_COLS) take turns
 #define EXP_SEGMENT 4096  // cells per work item of k_expect
+#define EXP_PREFETCH 64   // cells ahead of the current one whose F / B lines are prefetched (two chunks; 128: no better)
 
 template <int S>
 struct TransTable;
@@ -893,6 +894,14 @@ k_expect(const __grid_constant__ DevModel model, Blob bl, int64_t n_cells, int64
             const bool active = c < c_end;
             const int d = g0 + k_adv;
             g0 += n_starts + (next_starts_new ? 1 : 0);  // diagonal of the first cell of the next chunk
+            // The backward cells are touched once, front to back, and the forward cells a chunk reads lie one and two
+            // diagonals behind them: both streams are sequential, so the lines of the chunk after the next one are
+            // requested now and arrive under this chunk's 13 exp chains (the kernel waited on these loads: 3.9
+            // long-scoreboard stalls per issue before, 2.5 after; profiles/r2_ncu_summary.md sections 6 and 9).
+            if (c + EXP_PREFETCH < c_end) {
+                asm volatile("prefetch.global.L1 [%0];" ::"l"(B + (c + EXP_PREFETCH) * S));
+                asm volatile("prefetch.global.L1 [%0];" ::"l"(F + (c + EXP_PREFETCH) * S));
+            }
             double e_to[S];
 #pragma unroll
             for (int s = 0; s < S; s++) e_to[s] = 0.0;
