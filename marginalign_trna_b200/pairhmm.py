@@ -419,19 +419,20 @@ class PlanCache:
         self.hits = 0
 
     @staticmethod
-    def _key(params, expectations):
-        return tuple(getattr(params, f) for f in sorted(vars(params)) if not f.startswith("_")) + (bool(expectations),)
+    def _key(params, expectations, device):
+        return tuple(getattr(params, f) for f in sorted(vars(params)) if not f.startswith("_")) + (
+            bool(expectations), str(device))
 
-    def lookup(self, batch, params, expectations):
+    def lookup(self, batch, params, expectations, device):
         """The kept plans if they were made for this very batch object (the cache holds a reference to it, so the
-        identity test cannot be fooled by a recycled id), these parameters and this mode."""
-        if self.plans is not None and self.batch is batch and self.key == self._key(params, expectations):
+        identity test cannot be fooled by a recycled id), these parameters, this mode and this GPU."""
+        if self.plans is not None and self.batch is batch and self.key == self._key(params, expectations, device):
             self.hits += 1
             return self.plans
         return None
 
-    def store(self, batch, params, expectations, plans):
-        self.batch, self.key, self.plans = batch, self._key(params, expectations), plans
+    def store(self, batch, params, expectations, device, plans):
+        self.batch, self.key, self.plans = batch, self._key(params, expectations, device), plans
 
     def clear(self):
         self.batch, self.key, self.plans = None, None, None
@@ -579,7 +580,7 @@ class PairHmmEngine:
         if cache is None:
             yield from self._build_device_plans(batch, params, expectations)
             return
-        kept = cache.lookup(batch, params, expectations)
+        kept = cache.lookup(batch, params, expectations, self.device)
         if kept is not None:
             for dplan in kept:
                 dplan.use_workspace(self._workspace(dplan.ws_bytes + 256))
@@ -601,7 +602,7 @@ class PairHmmEngine:
                     dplan.drop_workspace()
                     keep.append(dplan)
         if keep is not None:
-            cache.store(batch, params, expectations, keep)
+            cache.store(batch, params, expectations, self.device, keep)
 
     def _build_device_plans(self, batch, params, expectations):
         chunks = self._chunks(batch, params, expectations)
