@@ -498,7 +498,10 @@ class PairHmmEngine:
     # ---------------------------------------------------------------- chunking
     CHUNK_RAMP = (4,)         # the first chunk is a quarter of the others, see _chunks
     PLAN_AHEAD = 2            # chunks planned ahead of the one computing
-    BASE_CELLS = 400_000_000  # chunk size that pipelines well for short reads (tRNA: ~140 k alignments per chunk)
+    # chunk size for short reads (tRNA: ~285 k alignments, 22 GB of workspace).  Measured on 1 M tRNA reads (r2bi / r2bj):
+    # 2.5e8 -> e2e 15.5 GCUPS, 4e8 -> 16.4, 8e8 -> 17.0, 1.2e9 -> 16.7, 1.6e9 -> 16.6 (larger chunks: fewer planner
+    # round trips and kernel tails; smaller ones: more of the first upload and the last download overlapped)
+    BASE_CELLS = 800_000_000
 
     def _auto_max_cells(self, mean_est, params, expectations):
         """Chunk size when the caller gave none.  The forward sweep of one region is sequential over its diagonals, so
