@@ -65,6 +65,8 @@ def parse_args():
     ap.add_argument("--em-reads", type=int, default=300000, help="alignments per GPU in the EM leg")
     ap.add_argument("--em-iterations", type=int, default=2)
     ap.add_argument("--int32-pairs", action="store_true", help="e2e leg: 32-bit pair coordinates even where 16 bits do")
+    ap.add_argument("--chunk-ramp", default="",
+                    help="divisors of the chunk size for the first chunks of a call, e.g. 8,2 (default: the engine's)")
     ap.add_argument("--no-pipelined-leg", action="store_true",
                     help="skip the resident loop with planning overlapped on a second stream")
     ap.add_argument("--plan-ahead", type=int, default=0, help="chunks planned ahead of the one computing (0: engine default)")
@@ -350,7 +352,8 @@ def run_ours(args, rank, world, local_rank):
     model = mab.PairHmmModel.from_hmm(hmm) if args.states == 5 else mab.PairHmmModel.default(2)
     S = model.state_number
     eng = mab.PairHmmEngine(device=dev, max_cells=args.max_cells or None, plan_ahead=args.plan_ahead or None,
-                            compact_pairs=not args.int32_pairs)
+                            compact_pairs=not args.int32_pairs,
+                            chunk_ramp=[int(v) for v in args.chunk_ramp.split(",")] if args.chunk_ramp else None)
     em = args.mode == "em"
     realign = args.mode == "realign"
     stream = torch.cuda.current_stream(dev)

@@ -444,7 +444,7 @@ class PairHmmEngine:
     built on the GPU; "host": the C++ host planner builds the blob and it is copied over PCIe."""
 
     def __init__(self, device=None, max_cells=None, plan_threads=0, plan_on="device", plan_ahead=None,
-                 compact_pairs=True):
+                 compact_pairs=True, chunk_ramp=None):
         torch = require_cuda()
         self.torch = torch
         self.device = torch.device(device if device is not None else "cuda:%d" % torch.cuda.current_device())
@@ -456,6 +456,8 @@ class PairHmmEngine:
         # get_aligned_pairs_using_anchors returns x / y as int16 arrays when every sub-sequence is shorter than 32768
         # bases (same values; a third less data leaves the GPU); False keeps int32 always
         self.compact_pairs = bool(compact_pairs)
+        if chunk_ramp is not None:  # divisors of the chunk size for the first chunks (default CHUNK_RAMP)
+            self.CHUNK_RAMP = tuple(int(d) for d in chunk_ramp)
         if plan_ahead is not None:  # chunks planned concurrently ahead of the one computing (default PLAN_AHEAD)
             self.PLAN_AHEAD = max(1, int(plan_ahead))
         self.last_stats = {}
