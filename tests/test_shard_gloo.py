@@ -52,8 +52,10 @@ class OracleEngine:
         return mab.RealignedCigars(np.array(off, dtype=np.int64), np.array(ops, dtype=np.uint8),
                                    np.array(lens, dtype=np.int32))
 
-    def get_expectations_using_anchors(self, model, batch, params, pseudo_count=1e-12):
+    def get_expectations_using_anchors(self, model, batch, params, pseudo_count=1e-12, plan_cache=None):
         po = self.po
+        if plan_cache is not None:  # what a PairHmmEngine would key its kept device plans on
+            self.cache_calls = getattr(self, "cache_calls", []) + [(batch, plan_cache)]
         T, E, lik = np.full(25, pseudo_count), np.full(80, pseudo_count), 0.0
         for i in range(batch.n):
             anc = po.anchors_from_cigar(*batch.cigar(i), batch.x(i), batch.y(i))
@@ -134,6 +136,11 @@ def _worker(rank, world, port, out_dir):
         hmm = mab.em.expectation_maximisation_trials(_NoModelRunner(sh), b, None, opts)
         np.savez(os.path.join(out_dir, "em_%d.npz" % rank), T=hmm.transitions, E=hmm.emissions,
                  L=np.array(hmm.runningLikelihoods))
+        # the EM loop hands one PlanCache to every iteration, and the sharder gives the engine the SAME shard object
+        # each time -- that identity is what lets a PairHmmEngine re-use the device plans of its shard
+        calls = eng.cache_calls
+        assert len(calls) == 2 and calls[0][0] is calls[1][0] and calls[0][1] is calls[1][1]
+        assert isinstance(calls[0][1], mab.PlanCache)
     finally:
         dist.destroy_process_group()
 
@@ -145,12 +152,12 @@ class _NoModelRunner:
     def __init__(self, sharded):
         self.sh = sharded
 
-    def get_expectations_using_anchors(self, model, batch, params):
+    def get_expectations_using_anchors(self, model, batch, params, plan_cache=None):
         T = np.zeros((13, 4))
         eng = self.sh.engine
         # rebuild the oracle model from the CURRENT hmm held by the PairHmmModel's source arrays
         eng.om = eng.po.model_from_hmm(model.type, model.src_transitions, model.src_emissions)
-        return self.sh.get_expectations_using_anchors(model, batch, params)
+        return self.sh.get_expectations_using_anchors(model, batch, params, plan_cache=plan_cache)
 
 
 @pytest.mark.timeout(300)
