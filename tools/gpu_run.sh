@@ -8,7 +8,7 @@ nvidia-smi --query-gpu=name,clocks.max.sm,memory.total --format=csv > gpurun_out
 for step in "$@"; do
   kind=${step%%:*}; rest=${step#*:}
   case $kind in
-    tests) timeout 2400 python -m pytest tests -m gpu -x -q ${rest#tests} > gpurun_out/${tag}_pytest.log 2>&1; echo "pytest rc=$?"; tail -8 gpurun_out/${tag}_pytest.log;;
+    tests) eval "timeout 2400 python -m pytest tests -m gpu -x -q ${rest#tests}" > gpurun_out/${tag}_pytest.log 2>&1; echo "pytest rc=$?"; tail -8 gpurun_out/${tag}_pytest.log;;  # eval: -k "a or b" keeps its quotes
     smoke) timeout 300 python -c "import __graft_entry__ as g; g.smoke()" > gpurun_out/${tag}_smoke.log 2>&1; echo "smoke rc=$?"; tail -2 gpurun_out/${tag}_smoke.log;;
     bench) name=${rest%%:*}; args=${rest#*:}
       timeout 1200 python bench.py $args > gpurun_out/${tag}_bench_$name.json 2> gpurun_out/${tag}_bench_$name.err; echo "bench $name rc=$?"; tail -2 gpurun_out/${tag}_bench_$name.err
