@@ -775,7 +775,7 @@ class PairHmmEngine:
             new = lambda name, numel, dtype: self._pooled(slot, name, numel, dtype)
             if self._slot_free[slot] is not None:
                 torch.cuda.current_stream(self.device).wait_event(self._slot_free[slot])
-        st = dict(dplan=dplan, n=n, cap=cap, slot=slot, new=new,
+        st = dict(dplan=dplan, model=model, n=n, cap=cap, slot=slot, new=new,
                   d_off=new("d_off", n + 1, torch.int64),
                   d_np=torch.empty(1, dtype=torch.int64, device=self.device),
                   d_x=new("d_x", cap, torch.int32),
@@ -793,18 +793,24 @@ class PairHmmEngine:
         return st
 
     def posteriors_settle(self, st):
-        """Waits for the pair count of an async chunk; if the bound was too small the pairs are emitted again into
-        exactly sized buffers (the workspace is still alive).  Returns the number of pairs."""
+        """Waits for the pair count of an async chunk; if the bound was too small (more than PAIRS_PER_CELL_CAP pairs
+        per band cell: a threshold near 0) the chunk is computed again and its pairs are emitted into exactly sized
+        buffers.  Computed again, not just emitted again: the chunks of a call share the engine's workspace, and the
+        next chunk's kernels -- queued before this one is settled -- have overwritten it.  Returns the number of
+        pairs."""
         torch, L = self.torch, capi.load()
         st["counted"].synchronize()
         total = int(st["h_np"][0])
         if total > st["cap"]:
-            dplan = st["dplan"]
+            dplan, sp = st["dplan"], self._stream_ptr()
+            dplan.use_workspace(self._workspace(dplan.ws_bytes + 256))
             for k in ("d_x", "d_y", "d_p"):
                 st[k] = torch.empty(total, dtype=torch.int32, device=self.device)
+            capi.check(L.mab_posteriors_compute(st["model"]._h, dplan.plan._h, dplan.blob_ptr, dplan.ws_ptr,
+                                                dplan.ws_bytes, st["d_off"].data_ptr(), st["d_np"].data_ptr(), sp))
             capi.check(L.mab_posteriors_emit(dplan.plan._h, dplan.blob_ptr, dplan.ws_ptr, dplan.ws_bytes,
                                              st["d_x"].data_ptr(), st["d_y"].data_ptr(), st["d_p"].data_ptr(), total,
-                                             self._stream_ptr()))
+                                             sp))
             st["cap"] = total
             st["overflowed"] = True
         st["total"] = total

@@ -108,6 +108,27 @@ def test_repeated_calls_reuse_the_engine_buffers(models):
         assert np.array_equal(getattr(pairs[0], a), getattr(pairs[1], a)), a
 
 
+def test_pair_bound_overflow_recomputes_the_chunk(models):
+    """At threshold 0 nearly every band cell yields a pair, four times the bound the sync-free path sizes its pair
+    arrays by (PAIRS_PER_CELL_CAP): the chunk is then computed again with exact sizes -- after the NEXT chunk's kernels
+    have already run in the shared workspace.  Several chunks with the overflow == an engine whose bound is never
+    exceeded == the oracle."""
+    b = mab.synth.make_trna_batch(900, seed=37)
+    P = mab.AlignmentParameters(threshold=0.0)
+    tight = mab.PairHmmEngine(max_cells=400_000)
+    roomy = mab.PairHmmEngine(max_cells=400_000)
+    roomy.PAIRS_PER_CELL_CAP = 1.25
+    got = tight.realign(models[0], b, P, want_chain=True)
+    assert tight.last_stats["chunks"] >= 4 and tight.last_stats["pairs"] > 0.5 * tight.last_stats["cells"]
+    want = roomy.realign(models[0], b, P, want_chain=True)
+    for a in ("off_ops", "ops", "lens", "chain_off", "chain_x", "chain_y"):
+        assert np.array_equal(getattr(got, a), getattr(want, a)), a
+    oP = po.make_params(threshold=0.0, expansion=10, split=3000 ** 2)
+    for i in (0, 449, 899):
+        ops, chain = oracle_realign(models[1], b, i, oP, 0.5, 0.0)
+        assert_same(got, i, ops, chain, i)
+
+
 def test_full_size_properties(engine, models):
     """100 k reads: every cigar spans its two sequences, match runs equal the chain, chains strictly increase."""
     b = mab.synth.make_trna_batch(100_000, seed=35)
